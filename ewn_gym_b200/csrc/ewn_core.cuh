@@ -1,0 +1,654 @@
+// ewn_core.cuh -- EinStein wuerfelt nicht rules, leaf evaluation and Philox draw schedule on a
+// bit-packed piece list.  Every function here is the per-game body of a CUDA kernel in
+// ewn_kernels.cu; the functions are marked __host__ __device__ only so that tests/hostsim can
+// single-step the very same code under gdb / gcc sanitizers.  The shipped library has no host path.
+//
+// Reference semantics (jchen8tw/ewn-gym, cited as file:line relative to the reference root):
+//   envs/ewn.py:94-107   initial layout            envs/ewn.py:131-142  check_win
+//   envs/ewn.py:144-215  nearest cube / cube to move   envs/ewn.py:217-263  execute_move (captures ANY occupant)
+//   envs/ewn.py:325-375  legal directions / ordered legal list
+//   envs/ewn.py:436-486  step                       envs/training_ewn.py:40-99 shaped step
+//   envs/minimax_ewn.py:29-213 leaf heuristics      classical_policies/minimax.py:19-73 expectiminimax
+//   classical_policies/mcts.py:21-45 random playout
+//
+// State layout (DESIGN.md "Packed state"):
+//   P5 (board_size <= 5): one u64 per game. low u32 = TOP_LEFT side, high u32 = BOTTOM_RIGHT side.
+//        side word bits [5k,5k+5) = cell of cube k+1, cell = x*5+y, 31 = captured / not on this board.
+//        low[31:30] = (dice-1)&3, high[30] = (dice-1)>>2, high[31] = side to move (0 TL, 1 BR).
+//   P8 (board_size <= 9): two u64 per game (16-byte vector). word0 = TL side, word1 = BR side.
+//        side word bits [8k,8k+8) = cell of cube k+1, cell = (x<<4)|y, 0xFF = captured.
+//        word0[50:48] = dice-1, word1[48] = side to move.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define EWN_HD __host__ __device__ __forceinline__
+#else
+#define EWN_HD inline
+#endif
+
+namespace ewn {
+
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+// ------------------------------------------------------------------------------------------------
+// bit intrinsics (device instructions when compiled for the GPU)
+// ------------------------------------------------------------------------------------------------
+EWN_HD int ctz_nz(u32 x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+EWN_HD int ctz_nz(u64 x) {
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long)x) - 1;
+#else
+    return __builtin_ctzll(x);
+#endif
+}
+EWN_HD int msb_nz(u32 x) {
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)x);
+#else
+    return 31 - __builtin_clz(x);
+#endif
+}
+EWN_HD int msb_nz(u64 x) {
+#if defined(__CUDA_ARCH__)
+    return 63 - __clzll((long long)x);
+#else
+    return 63 - __builtin_clzll(x);
+#endif
+}
+EWN_HD int popc(u32 x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
+EWN_HD int popc(u64 x) {
+#if defined(__CUDA_ARCH__)
+    return __popcll(x);
+#else
+    return __builtin_popcountll(x);
+#endif
+}
+EWN_HD u32 mulhi(u32 a, u32 b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (u32)(((u64)a * (u64)b) >> 32);
+#endif
+}
+// IEEE-754 binary64 with round-to-nearest and NO fused contraction: the reference computes in CPython doubles.
+EWN_HD double f64_mul(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dmul_rn(a, b);
+#else
+    volatile double r = a * b; return r;
+#endif
+}
+EWN_HD double f64_add(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dadd_rn(a, b);
+#else
+    volatile double r = a + b; return r;
+#endif
+}
+EWN_HD double f64_sub(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __dsub_rn(a, b);
+#else
+    volatile double r = a - b; return r;
+#endif
+}
+EWN_HD double f64_div(double a, double b) {
+#if defined(__CUDA_ARCH__)
+    return __ddiv_rn(a, b);
+#else
+    volatile double r = a / b; return r;
+#endif
+}
+
+// ------------------------------------------------------------------------------------------------
+// geometry of one (board_size, cube_layer) configuration; filled on the host (ewn_kernels.cu make_geo)
+// ------------------------------------------------------------------------------------------------
+struct Geo {
+    int32_t N, L, cube_num;
+    int32_t corner;                          // packed cell of (N-1, N-1)
+    u32 tl_col, tl_row, br_col, br_row;      // P5 only: cells from which dir 0 / dir 1 leaves the board
+    u64 tl0, br0;                            // side words of the initial layout (envs/ewn.py:94-107)
+};
+
+enum { SIDE_TL = 0, SIDE_BR = 1 };
+enum { H_HYBRID = 0, H_MIN_DIST = 1, H_TWO_MIN_DIST = 2, H_ATTK = 3 };
+enum { CODE_ONGOING = 0, CODE_AGENT_ILLEGAL = 1, CODE_AGENT_WON = 2, CODE_OPP_ILLEGAL = 3, CODE_AGENT_LOST = 4,
+       CODE_ILLEGAL_TOLERATED = 5 };
+
+// ------------------------------------------------------------------------------------------------
+// codecs
+// ------------------------------------------------------------------------------------------------
+struct P5 {
+    typedef u32 W;
+    static constexpr int FB = 5, S = 5, WORDS = 1, MAXN = 5;
+    static constexpr W FM = 31u, ONES = 0x02108421u, ALL = 0x3FFFFFFFu;
+    static constexpr W LOWS = 0x02108421u * 15u, HIGHS = 0x02108421u << 4;
+    static EWN_HD int cell(int x, int y) { return x * 5 + y; }
+    static EWN_HD int x_of(int c) { return (c * 13) >> 6; }          // c / 5 for c < 32
+    static EWN_HD int y_of(int c) { return c - 5 * x_of(c); }
+    static EWN_HD W dead(W s) { W t = s & (s >> 1); W u = t & (t >> 2); return u & (s >> 4) & ONES; }
+    template <int BR> static EWN_HD int dirs(const Geo& g, int c) {
+        u32 e0 = BR ? g.br_col : g.tl_col, e1 = BR ? g.br_row : g.tl_row;
+        u32 ok0 = ~(e0 >> c) & 1u, ok1 = ~(e1 >> c) & 1u;
+        return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
+    }
+};
+
+struct P8 {
+    typedef u64 W;
+    static constexpr int FB = 8, S = 16, WORDS = 2, MAXN = 9;
+    static constexpr W FM = 0xFFull, ONES = 0x0000010101010101ull, ALL = 0x0000FFFFFFFFFFFFull;
+    static constexpr W LOWS = 0x0000010101010101ull * 0x7Full, HIGHS = 0x0000010101010101ull << 7;
+    static EWN_HD int cell(int x, int y) { return (x << 4) | y; }
+    static EWN_HD int x_of(int c) { return c >> 4; }
+    static EWN_HD int y_of(int c) { return c & 15; }
+    static EWN_HD W dead(W s) { W t = s & (s >> 4); t &= t >> 2; t &= t >> 1; return t & ONES; }
+    template <int BR> static EWN_HD int dirs(const Geo& g, int c) {
+        int x = c >> 4, y = c & 15;
+        u32 ok0 = BR ? (y > 0) : (y < g.N - 1), ok1 = BR ? (x > 0) : (x < g.N - 1);
+        return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
+    }
+};
+
+template <class C> struct Game {
+    typename C::W tl, br;
+    int dice;      // 1..6
+    int player;    // SIDE_TL / SIDE_BR: side to move
+};
+
+EWN_HD void unpack(Game<P5>& g, const u64* p, long i) {
+    u64 v = p[i];
+    u32 lo = (u32)v, hi = (u32)(v >> 32);
+    g.tl = lo & P5::ALL; g.br = hi & P5::ALL;
+    g.dice = 1 + (int)((lo >> 30) | ((hi >> 28) & 4u));
+    g.player = (int)(hi >> 31);
+}
+EWN_HD u64 pack_word(const Game<P5>& g) {
+    u32 d = (u32)(g.dice - 1);
+    u32 lo = g.tl | ((d & 3u) << 30);
+    u32 hi = g.br | ((d >> 2) << 30) | ((u32)g.player << 31);
+    return (u64)lo | ((u64)hi << 32);
+}
+EWN_HD void pack(const Game<P5>& g, u64* p, long i) { p[i] = pack_word(g); }
+
+EWN_HD void unpack_words(Game<P8>& g, u64 w0, u64 w1) {
+    g.tl = w0 & P8::ALL; g.br = w1 & P8::ALL;
+    g.dice = 1 + (int)((w0 >> 48) & 7u);
+    g.player = (int)((w1 >> 48) & 1u);
+}
+EWN_HD void pack_words(const Game<P8>& g, u64& w0, u64& w1) {
+    w0 = g.tl | ((u64)(g.dice - 1) << 48);
+    w1 = g.br | ((u64)g.player << 48);
+}
+EWN_HD void unpack(Game<P8>& g, const u64* p, long i) {
+#if defined(__CUDA_ARCH__)
+    ulonglong2 v = reinterpret_cast<const ulonglong2*>(p)[i];
+    unpack_words(g, v.x, v.y);
+#else
+    unpack_words(g, p[2 * i], p[2 * i + 1]);
+#endif
+}
+EWN_HD void pack(const Game<P8>& g, u64* p, long i) {
+    u64 w0, w1; pack_words(g, w0, w1);
+#if defined(__CUDA_ARCH__)
+    reinterpret_cast<ulonglong2*>(p)[i] = make_ulonglong2(w0, w1);
+#else
+    p[2 * i] = w0; p[2 * i + 1] = w1;
+#endif
+}
+
+template <class C> EWN_HD void setup(Game<C>& g, const Geo& geo, int dice) {   // envs/ewn.py:94-107
+    g.tl = (typename C::W)geo.tl0; g.br = (typename C::W)geo.br0; g.dice = dice; g.player = SIDE_TL;
+}
+
+// ------------------------------------------------------------------------------------------------
+// rules
+// ------------------------------------------------------------------------------------------------
+// flag per field (at the field's top bit) where the field of `w` equals the replicated cell `rep`; exact, carry-free
+template <class C> EWN_HD typename C::W match(typename C::W w, typename C::W rep) {
+    typename C::W x = w ^ rep;
+    typename C::W nz = (((x & C::LOWS) + C::LOWS) | x) & C::HIGHS;
+    return nz ^ C::HIGHS;
+}
+// envs/ewn.py:254-258: whatever stands on the target cell is captured (own cubes too)
+template <class C> EWN_HD typename C::W capture(typename C::W w, typename C::W rep) {
+    typename C::W z = match<C>(w, rep);
+    return w | ((z << 1) - (z >> (C::FB - 1)));
+}
+
+// envs/ewn.py:131-142 check_win on an arbitrary state
+template <class C> EWN_HD bool full_win(const Game<C>& g, const Geo& geo) {
+    typedef typename C::W W;
+    W at_corner = match<C>(g.tl, (W)geo.corner * C::ONES);     // board[-1,-1] > 0
+    W at_origin = match<C>(g.br, (W)0);                         // board[0,0] < 0
+    return (at_corner | at_origin) != 0 || g.tl == C::ALL || g.br == C::ALL;
+}
+// winner test used after a terminal state is known (mcts.py:39-41, minimax_ewn.py:42-47): did TOP_LEFT win?
+template <class C> EWN_HD bool tl_won(const Game<C>& g, const Geo& geo) {
+    typedef typename C::W W;
+    return match<C>(g.tl, (W)geo.corner * C::ONES) != 0 || g.br == C::ALL;
+}
+
+// Shifts (bit offsets of the cube's field) of the cubes the side may move with the current die.
+// envs/ewn.py:144-176 find_near_cube, :202-215 find_cube_to_move.
+struct Movers { int d, hi, lo; };   // d >= 0: the dice cube itself is alive; else hi / lo = nearest larger / smaller (or -1)
+template <class C> EWN_HD Movers movers(typename C::W side, int dice) {
+    typedef typename C::W W;
+    W alive = C::dead(side) ^ C::ONES;
+    int sh = C::FB * (dice - 1);
+    Movers m; m.d = -1; m.hi = -1; m.lo = -1;
+    if ((alive >> sh) & 1) { m.d = sh; return m; }
+    W above = alive & (~(W)0 << (sh + 1));
+    W below = alive & (((W)1 << sh) - 1);
+    if (above) m.hi = ctz_nz(above);
+    if (below) m.lo = msb_nz(below);
+    return m;
+}
+// envs/ewn.py:178-215: the flag is only consulted when the dice cube is gone, and falls back to the other side
+EWN_HD int cube_to_move(const Movers& m, bool larger) {
+    if (m.d >= 0) return m.d;
+    if (larger) return m.hi >= 0 ? m.hi : m.lo;
+    return m.lo >= 0 ? m.lo : m.hi;
+}
+
+template <class C> EWN_HD int cell_at(typename C::W side, int sh) { return (int)((side >> sh) & C::FM); }
+
+// Ordered legal list of envs/ewn.py:338-375 as two 3-bit direction sets: `first` is listed before `second`.
+//   dice cube alive : first = dirs(dice cube) with flag 0, second = empty
+//   otherwise       : first = dirs(larger neighbour) with flag 1, second = dirs(smaller neighbour) with flag 0
+struct Legal { int first, second, first_flag, sh_first, sh_second; };
+template <class C, int BR> EWN_HD Legal legal(const Game<C>& g, const Geo& geo, const Movers& m) {
+    typename C::W side = BR ? g.br : g.tl;
+    Legal l; l.first = 0; l.second = 0; l.first_flag = 0; l.sh_first = -1; l.sh_second = -1;
+    if (m.d >= 0) { l.first = C::template dirs<BR>(geo, cell_at<C>(side, m.d)); l.sh_first = m.d; return l; }
+    l.first_flag = 1;
+    if (m.hi >= 0) { l.first = C::template dirs<BR>(geo, cell_at<C>(side, m.hi)); l.sh_first = m.hi; }
+    if (m.lo >= 0) { l.second = C::template dirs<BR>(geo, cell_at<C>(side, m.lo)); l.sh_second = m.lo; }
+    return l;
+}
+// 6-bit mask, bit = larger*3 + dir (the action id convention of alpha_zero/ewn/EWNLogic.py:328)
+EWN_HD int legal_mask(const Legal& l) { return l.first_flag ? ((l.first << 3) | l.second) : l.first; }
+EWN_HD int legal_count(const Legal& l) { return popc((u32)(l.first | (l.second << 3))); }
+EWN_HD int nth_dir(int m, int j) {           // j-th (0-based) set bit of a 3-bit set
+    if (j >= 1) m &= m - 1;
+    if (j >= 2) m &= m - 1;
+    return ctz_nz((u32)(m | 8));
+}
+// idx-th entry of the ordered list -> (larger flag, dir, shift of the cube that moves)
+EWN_HD void legal_pick(const Legal& l, int idx, int& larger, int& dir, int& sh) {
+    int nf = popc((u32)l.first);
+    if (idx < nf) { larger = l.first_flag; dir = nth_dir(l.first, idx); sh = l.sh_first; }
+    else          { larger = 0;            dir = nth_dir(l.second, idx - nf); sh = l.sh_second; }
+}
+
+// envs/ewn.py:217-263 execute_move for a move already known to stay on the board. Returns the target cell.
+template <class C, int BR> EWN_HD int apply_move(Game<C>& g, int sh, int dir) {
+    typedef typename C::W W;
+    W own = BR ? g.br : g.tl;
+    int c = (int)((own >> sh) & C::FM);
+    int delta = (dir != 1) + C::S * (dir != 0);            // envs/ewn.py:301-319 update_position
+    int t = BR ? c - delta : c + delta;
+    W rep = (W)t * C::ONES;
+    g.tl = capture<C>(g.tl, rep);
+    g.br = capture<C>(g.br, rep);
+    if (BR) g.br = (g.br & ~(C::FM << sh)) | ((W)t << sh);
+    else    g.tl = (g.tl & ~(C::FM << sh)) | ((W)t << sh);
+    return t;
+}
+// check_win right after `BR ? BOTTOM_RIGHT : TOP_LEFT` moved to cell t from a non-terminal position
+template <class C, int BR> EWN_HD bool win_after(const Game<C>& g, const Geo& geo, int t) {
+    return BR ? (t == 0 || g.tl == C::ALL) : (t == geo.corner || g.br == C::ALL);
+}
+
+// One ply with an externally chosen action (find_cube_to_move + execute_move, envs/ewn.py:439-442).
+// Returns false (state untouched, :262-263) when the move leaves the board or the side has no cube.
+template <class C, int BR> EWN_HD bool ply_action(Game<C>& g, const Geo& geo, int larger, int dir, int& t_out, int& sh_out) {
+    typename C::W side = BR ? g.br : g.tl;
+    Movers m = movers<C>(side, g.dice);
+    int sh = cube_to_move(m, larger == 1);
+    sh_out = sh;
+    if (sh < 0 || dir < 0 || dir > 2) return false;
+    int ok = C::template dirs<BR>(geo, cell_at<C>(side, sh));
+    if (!((ok >> dir) & 1)) return false;
+    t_out = apply_move<C, BR>(g, sh, dir);
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// leaf evaluation, envs/minimax_ewn.py:29-213 (agent is always TOP_LEFT: minimax_ewn.py:17-19)
+// ------------------------------------------------------------------------------------------------
+struct SideStats { int cnt, best, second; };   // best/second = two largest values of min(x,y) over alive cubes (-1 if none)
+template <class C> EWN_HD SideStats side_stats(typename C::W side) {
+    SideStats s; s.cnt = 0; s.best = -1; s.second = -1;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        int c = (int)((side >> (C::FB * k)) & C::FM);
+        if (c != (int)C::FM) {
+            int x = C::x_of(c), y = C::y_of(c);
+            int mn = x < y ? x : y;
+            s.cnt++;
+            if (mn > s.best) { s.second = s.best; s.best = mn; }
+            else if (mn > s.second) s.second = mn;
+        }
+    }
+    return s;
+}
+EWN_HD double inv_count(int c) {   // 1.0 / c, correctly rounded (compile-time IEEE division)
+    switch (c) {
+        case 1: return 1.0; case 2: return 1.0 / 2.0; case 3: return 1.0 / 3.0;
+        case 4: return 1.0 / 4.0; case 5: return 1.0 / 5.0; default: return 1.0 / 6.0;
+    }
+}
+template <class C> EWN_HD double evaluate(const Game<C>& g, const Geo& geo, int heuristic) {
+    if (tl_won<C>(g, geo)) return 10.0;                                   // minimax_ewn.py:42-44
+    if (match<C>(g.br, (typename C::W)0) != 0 || g.tl == C::ALL) return -10.0;   // :45-47
+    SideStats p = side_stats<C>(g.tl), n = side_stats<C>(g.br);
+    // Both colours measure max(N-1-x, N-1-y), the distance to the BOTTOM-RIGHT corner (minimax_ewn.py:67-76),
+    // so N - min_dist = 1 + max over cubes of min(x, y).
+    int N = geo.N;
+    if (heuristic == H_HYBRID) {                                          // :79-86
+        double a = f64_mul((double)(1 + p.best), inv_count(p.cnt));
+        double b = f64_mul((double)(1 + n.best), inv_count(n.cnt));
+        return f64_sub(a, b);
+    }
+    if (heuristic == H_MIN_DIST) return (double)((1 + p.best) - (1 + n.best));     // :126-131
+    if (heuristic == H_TWO_MIN_DIST) {                                    // :168-178 sum of the (up to) two smallest distances
+        int sp = (N - 1 - p.best) + (p.cnt >= 2 ? (N - 1 - p.second) : 0);
+        int sn = (N - 1 - n.best) + (n.cnt >= 2 ? (N - 1 - n.second) : 0);
+        return (double)(sn - sp);
+    }
+    return (double)(-(p.cnt + n.cnt));                                     // :212-213
+}
+// classical_policies/minimax.py:65-73: expectation over six identical children, e = 0; e += v/6 six times
+EWN_HD double six_fold(double v) {
+    double q = f64_div(v, 6.0), e = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) e = f64_add(e, q);
+    return e;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11) and the draw schedule (DESIGN.md "RNG schedule")
+// ------------------------------------------------------------------------------------------------
+EWN_HD void philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1, u32 out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        u32 h0 = mulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        u32 h1 = mulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        u32 n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+EWN_HD u32 bounded(u32 r, u32 k) { return mulhi(r, k); }   // uniform on [0,k) up to a bias < k / 2^32
+
+enum { TAG_STEP = 0, TAG_RESET = 1, TAG_PLAYOUT = 2 };
+// per (env, step): [0] die for the opponent's ply (envs/ewn.py:458), [1] opponent's index into its legal list
+// (random_policy.py:12-14), [2] die for the next agent turn (:483) -- or, if this step ended the episode and the
+// env auto-resets, the first die of the new episode (:108) --, [3] the agent's index when the agent is random too.
+EWN_HD void env_block(u64 seed, u64 env_id, u64 step, u32 tag, u32 out[4]) {
+    philox4x32_10((u32)env_id, (u32)(env_id >> 32), (u32)step, ((u32)(step >> 32) & 0x0FFFFFFFu) | (tag << 28),
+                  (u32)seed, (u32)(seed >> 32), out);
+}
+// per (root, child, playout, j): plies 2j and 2j+1 of that playout; [0],[2] die, [1],[3] index into the legal list
+EWN_HD void playout_block(u64 seed, u32 root_id, u32 child, u32 playout, u32 j, u32 out[4]) {
+    philox4x32_10(playout, root_id, j, ((u32)TAG_PLAYOUT << 28) | child, (u32)seed, (u32)(seed >> 32), out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// one uniformly random ply (random_policy.py:11-15 / mcts.py:29-35). Returns true if the mover has won.
+// ------------------------------------------------------------------------------------------------
+template <class C, int BR> EWN_HD bool random_ply(Game<C>& g, const Geo& geo, u32 r_index, int* larger_out, int* dir_out) {
+    Movers m = movers<C>(BR ? g.br : g.tl, g.dice);
+    Legal l = legal<C, BR>(g, geo, m);
+    int idx = (int)bounded(r_index, (u32)legal_count(l));
+    int larger, dir, sh;
+    legal_pick(l, idx, larger, dir, sh);
+    if (larger_out) { *larger_out = larger; *dir_out = dir; }
+    int t = apply_move<C, BR>(g, sh, dir);
+    return win_after<C, BR>(g, geo, t);
+}
+
+// classical_policies/mcts.py:24-41: BOTTOM_RIGHT moves first, 6-face die, uniform over the legal list.
+// Returns 1 if TOP_LEFT won.
+template <class C> EWN_HD int playout(Game<C> g, const Geo& geo, u64 seed, u32 root_id, u32 child, u32 index, int* plies_out) {
+    int plies = 0;
+    bool over = full_win<C>(g, geo);
+    u32 j = 0;
+    while (!over) {
+        u32 blk[4];
+        playout_block(seed, root_id, child, index, j++, blk);
+        g.dice = 1 + (int)bounded(blk[0], 6u);
+        over = random_ply<C, SIDE_BR>(g, geo, blk[1], nullptr, nullptr);
+        plies++;
+        if (over) break;
+        g.dice = 1 + (int)bounded(blk[2], 6u);
+        over = random_ply<C, SIDE_TL>(g, geo, blk[3], nullptr, nullptr);
+        plies++;
+    }
+    if (plies_out) *plies_out = plies;
+    return tl_won<C>(g, geo) ? 1 : 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// env step, envs/ewn.py:436-486 (+ envs/training_ewn.py:40-99 when shaped). Agent = TOP_LEFT.
+// ------------------------------------------------------------------------------------------------
+struct StepParams {
+    Geo geo;
+    double reward;                 // goal reward (envs/ewn.py:38)
+    double illegal_move_reward;    // training_ewn.py:25
+    u64 seed, step, env_id0;
+    int32_t agent_random;          // agent = uniform over its legal list (blk[3])
+    int32_t autoreset;             // SB3 VecEnv contract: re-initialise finished games in the same call
+    int32_t shaped;                // MiniMaxHeuristicEnv semantics
+    int32_t replay;                // dice / opponent answers injected by the caller
+};
+struct StepInject { int dice_opp, o_larger, o_dir, dice_next; };
+struct StepOut {
+    double reward; int term, trunc, code;
+    int a_larger, a_dir;           // the action that was played (useful when agent_random)
+};
+
+// g: in = state at the agent's turn; out = next state (after auto-reset when the episode ended).
+// term_state: the terminal state (valid when out.term).
+template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const StepParams& p, long i, int a_larger, int a_dir,
+                                        const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
+    const Geo& geo = p.geo;
+    u32 blk[4] = {0, 0, 0, 0};
+    if (!p.replay || p.agent_random) env_block(p.seed, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
+    bool pre = full_win<C>(g, geo);        // stepping an already finished game keeps reporting a win (check_win is sticky)
+    out.reward = 0.0; out.term = 0; out.trunc = 0; out.code = CODE_ONGOING;
+    bool valid; int t = 0, sh = -1;
+    if (p.agent_random) {
+        Movers m = movers<C>(g.tl, g.dice);
+        Legal l = legal<C, SIDE_TL>(g, geo, m);
+        int cnt = legal_count(l);
+        valid = cnt > 0;
+        if (valid) {
+            legal_pick(l, (int)bounded(blk[3], (u32)cnt), a_larger, a_dir, sh);
+            t = apply_move<C, SIDE_TL>(g, sh, a_dir);
+        }
+    } else {
+        valid = ply_action<C, SIDE_TL>(g, geo, a_larger, a_dir, t, sh);
+    }
+    out.a_larger = a_larger; out.a_dir = a_dir;
+    if (!valid) {
+        if (p.shaped) {                                                   // training_ewn.py:48-56
+            int tol = *tolerance - 1; *tolerance = tol;
+            if (tol <= 0) { out.reward = -p.reward; out.term = 1; out.trunc = 1; out.code = CODE_AGENT_ILLEGAL; }
+            else { out.reward = p.illegal_move_reward; out.code = CODE_ILLEGAL_TOLERATED; }
+        } else { out.reward = -p.reward; out.term = 1; out.trunc = 1; out.code = CODE_AGENT_ILLEGAL; }   // ewn.py:445-448
+    } else if (pre || win_after<C, SIDE_TL>(g, geo, t)) {                 // :451-454
+        out.reward = p.reward; out.term = 1; out.code = CODE_AGENT_WON;
+    } else {
+        g.player = SIDE_BR;                                               // :457-458
+        g.dice = p.replay ? inj.dice_opp : 1 + (int)bounded(blk[0], (u32)geo.cube_num);
+        bool ovalid; int ot = 0, osh;
+        if (p.replay) ovalid = ply_action<C, SIDE_BR>(g, geo, inj.o_larger, inj.o_dir, ot, osh);   // :461-467
+        else {
+            Movers m = movers<C>(g.br, g.dice);
+            Legal l = legal<C, SIDE_BR>(g, geo, m);
+            int cnt = legal_count(l);
+            ovalid = cnt > 0;
+            if (ovalid) {
+                int ol, od;
+                legal_pick(l, (int)bounded(blk[1], (u32)cnt), ol, od, osh);
+                ot = apply_move<C, SIDE_BR>(g, osh, od);
+            }
+        }
+        if (!ovalid) { out.reward = 0.0; out.term = 1; out.trunc = 1; out.code = CODE_OPP_ILLEGAL; }       // :470-473
+        else if (win_after<C, SIDE_BR>(g, geo, ot)) { out.reward = -p.reward; out.term = 1; out.code = CODE_AGENT_LOST; }   // :475-478
+        else {
+            g.player = SIDE_TL;                                           // :481-483
+            g.dice = p.replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num);
+            if (p.shaped) {                                               // training_ewn.py:94-96
+                double s = evaluate<C>(g, geo, H_HYBRID);
+                out.reward = f64_sub(s, *prev_score); *prev_score = s;
+            }
+        }
+    }
+    if (out.term) {
+        term_state = g;
+        if (p.autoreset) setup<C>(g, geo, p.replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// expectiminimax tree bookkeeping (classical_policies/minimax.py:19-73), see ewn_kernels.cu
+// ------------------------------------------------------------------------------------------------
+// Move level k (1-based) holds the positions reached after k moves: 6 * 36^(k-1) slots per root,
+// slot index = ((..(a1)*6 + die2)*6 + a2)*6 + die3)*6 + a3 ...   (a = position in the ordered legal list, die 0..5)
+EWN_HD long emm_level_size(int k) { long s = 6; for (int i = 1; i < k; i++) s *= 36; return s; }
+EWN_HD long emm_level_offset(int k) { long o = 0; for (int i = 1; i < k; i++) o += emm_level_size(i); return o; }
+EWN_HD int emm_levels(int depth) { return (depth + 1) / 2; }
+// node records are doubles; two NaN payloads mark "no such child" and "non-terminal interior node"
+static constexpr u64 EMM_ABSENT = 0xFFFFFFFFFFFFFFFFull;
+static constexpr u64 EMM_INTERIOR = 0xFFF8000000000001ull;
+
+EWN_HD double bits_to_f64(u64 b) {
+#if defined(__CUDA_ARCH__)
+    return __longlong_as_double((long long)b);
+#else
+    double d; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
+EWN_HD u64 f64_to_bits(double d) {
+#if defined(__CUDA_ARCH__)
+    return (u64)__double_as_longlong(d);
+#else
+    u64 b; __builtin_memcpy(&b, &d, 8); return b;
+#endif
+}
+EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
+
+// Phase 1, one call per slot t of the deepest move level of one root (g = non-terminal root, TOP_LEFT to move):
+// walk the path root -> slot and write the record of every position this slot owns into v (the root's region).
+//   last level      : value of the chance node on that position (evaluate, six-folded when depth is even and the
+//                     game is not over: minimax.py:22-23 + :64-73 over six identical depth-0 leaves)
+//   earlier levels  : EMM_INTERIOR, or evaluate() if the game ended there (minimax.py:22-23)
+//   a >= #legal     : EMM_ABSENT
+template <class C> EWN_HD void emm_expand_slot(Game<C> g, const Geo& geo, int depth, int heuristic, u32 t, double* v) {
+    const int m = emm_levels(depth);
+    u32 pow36 = (u32)emm_level_size(m) / 6;        // 36^(m-k) at level k; t % pow36 == 0 <=> this slot owns its level-k node
+    long off = 0, lvl = 6;
+    for (int k = 1; k <= m; k++) {
+        const u32 idx = t / pow36;                 // node index at level k
+        const bool owner = (t - idx * pow36) == 0;
+        const int a = (int)(idx % 6);
+        if (k > 1) g.dice = 1 + (int)((idx / 6) % 6);
+        bool over = false; int cnt;
+        if (k & 1) {
+            Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+            cnt = legal_count(l);
+            if (a < cnt) { int la, di, sh; legal_pick(l, a, la, di, sh); int tc = apply_move<C, SIDE_TL>(g, sh, di); over = win_after<C, SIDE_TL>(g, geo, tc); }
+        } else {
+            Legal l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
+            cnt = legal_count(l);
+            if (a < cnt) { int la, di, sh; legal_pick(l, a, la, di, sh); int tc = apply_move<C, SIDE_BR>(g, sh, di); over = win_after<C, SIDE_BR>(g, geo, tc); }
+        }
+        if (a >= cnt) { if (owner) v[off + idx] = bits_to_f64(EMM_ABSENT); return; }
+        if (k == m) {
+            double e = evaluate<C>(g, geo, heuristic);
+            if (!(depth & 1) && !over) e = six_fold(e);
+            v[off + idx] = e;
+            return;
+        }
+        if (over) { if (owner) v[off + idx] = evaluate<C>(g, geo, heuristic); return; }
+        if (owner) v[off + idx] = bits_to_f64(EMM_INTERIOR);
+        off += lvl; lvl *= 36; pow36 /= 36;
+    }
+}
+
+// Phase 2: classical_policies/minimax.py:19-73 replayed over the stored records of one root.
+template <int K, int M> struct Emm {
+    static constexpr long OFF = (K == 1) ? 0 : (K == 2) ? 6 : (K == 3) ? 222 : 7998;
+    // value of the chance node sitting on position `idx` of level K
+    static EWN_HD double chance(const double* v, long idx, double alpha, double beta, int pruned) {
+        double rec = v[OFF + idx];
+        if (K == M) return rec;
+        if (f64_to_bits(rec) != EMM_INTERIOR) return rec;             // finished game: minimax.py:22-23
+        double e = 0.0;
+        for (int die = 0; die < 6; die++) {                           // minimax.py:64-73
+            double val = Emm<K + 1, M>::move(v, idx * 6 + die, alpha, beta, pruned, nullptr);
+            e = f64_add(e, f64_div(val, 6.0));
+        }
+        return e;
+    }
+    // value of the move node whose children are positions base*6 + a of level K (K odd: TOP_LEFT maximises)
+    static EWN_HD double move(const double* v, long base, double alpha, double beta, int pruned, int* best_a) {
+        if (K & 1) {                                                  // minimax.py:26-43
+            double best = -f64_inf();
+            for (int a = 0; a < 6; a++) {
+                if (f64_to_bits(v[OFF + base * 6 + a]) == EMM_ABSENT) break;
+                double val = chance(v, base * 6 + a, alpha, beta, pruned);
+                if (val > best) { best = val; if (best_a) *best_a = a; }
+                alpha = alpha > best ? alpha : best;
+                if (pruned && beta <= alpha) break;
+            }
+            return best;
+        } else {                                                      // minimax.py:45-62
+            double worst = f64_inf();
+            for (int a = 0; a < 6; a++) {
+                if (f64_to_bits(v[OFF + base * 6 + a]) == EMM_ABSENT) break;
+                double val = chance(v, base * 6 + a, alpha, beta, pruned);
+                if (val < worst) worst = val;
+                beta = beta < worst ? beta : worst;
+                if (pruned && beta <= alpha) break;
+            }
+            return worst;
+        }
+    }
+};
+template <int M> struct Emm<5, M> {
+    static EWN_HD double chance(const double*, long, double, double, int) { return 0.0; }
+    static EWN_HD double move(const double*, long, double, double, int, int*) { return 0.0; }
+};
+
+// ExpectiMinimaxAgent.predict (minimax.py:89-93) for one root; (la, di) = (-1,-1) when the root is finished (action None)
+template <class C, int M> EWN_HD double emm_root(const Game<C>& g, const Geo& geo, int heuristic, int pruned, const double* v,
+                                                  int& la, int& di) {
+    la = -1; di = -1;
+    if (full_win<C>(g, geo)) return evaluate<C>(g, geo, heuristic);   // minimax.py:22-23
+    int best_a = 0;
+    double val = Emm<1, M>::move(v, 0, -f64_inf(), f64_inf(), pruned, &best_a);
+    Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+    int sh; legal_pick(l, best_a, la, di, sh);
+    return val;
+}
+
+}  // namespace ewn

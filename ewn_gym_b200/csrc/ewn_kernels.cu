@@ -1,0 +1,960 @@
+// ewn_kernels.cu -- sm_100a kernels and the C ABI (include/ewn_b200.h) of the EinStein-wuerfelt-nicht engine.
+//
+//   K0  k_reset / k_encode / k_decode     packed-state codec                        (envs/ewn.py:94-108, minimax.py:75-87)
+//   K1  k_step                            fused env step, one thread per game       (envs/ewn.py:436-486, training_ewn.py:40-99)
+//   K2  k_legal / k_ply / k_random_action legal list, single ply, random agent      (envs/ewn.py:338-375, random_policy.py:11-15)
+//   K3  k_mc_expand / k_playouts          flat Monte-Carlo playouts, lane per game  (classical_policies/mcts.py:21-84)
+//   K4  k_emm_expand / k_emm_replay       expectiminimax, level-parallel expansion  (classical_policies/minimax.py:19-93)
+//
+// All of it is integer / bit manipulation on the packed piece list of ewn_core.cuh; nothing here is a contraction,
+// so there is no tensor-core path.  K1 streams 8 (5x5) or 16 (<=9x9) bytes of state per game with fully coalesced
+// vector accesses and stages observation rows through shared memory so that global stores are full 16-byte vectors.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <atomic>
+#include <new>
+
+#include "../../include/ewn_b200.h"
+#include "ewn_core.cuh"
+
+using namespace ewn;
+
+namespace {
+
+constexpr int TPB = 256;               // threads per block for the per-game kernels
+constexpr int WARPS = TPB / 32;
+
+thread_local char g_err[256] = "";
+std::atomic<long long> g_launches{0};
+
+inline int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return EWN_ECUDA;
+}
+#define CU(call)                                            \
+    do {                                                    \
+        cudaError_t e__ = (call);                           \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+#define LAUNCHED(name)                                      \
+    do {                                                    \
+        g_launches.fetch_add(1, std::memory_order_relaxed); \
+        cudaError_t e__ = cudaGetLastError();               \
+        if (e__ != cudaSuccess) return cuda_fail(e__, name); \
+    } while (0)
+
+inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L <= 3 && L < N - 1; }
+inline bool use_p5(int N) { return N <= 5; }
+inline unsigned blocks_for(int64_t n) { return (unsigned)((n + TPB - 1) / TPB); }
+
+// geometry + initial layout (envs/ewn.py:94-107)
+Geo make_geo(int N, int L) {
+    Geo g;
+    memset(&g, 0, sizeof(g));
+    g.N = N; g.L = L; g.cube_num = L * (L + 1) / 2;
+    const bool p5 = use_p5(N);
+    auto cell = [&](int x, int y) { return p5 ? P5::cell(x, y) : P8::cell(x, y); };
+    g.corner = cell(N - 1, N - 1);
+    if (p5) {
+        for (int k = 0; k < N; k++) {
+            g.tl_col |= 1u << cell(k, N - 1);   // y == N-1: TL cannot go dir 0
+            g.tl_row |= 1u << cell(N - 1, k);   // x == N-1: TL cannot go dir 1
+            g.br_col |= 1u << cell(k, 0);       // y == 0  : BR cannot go dir 0
+            g.br_row |= 1u << cell(0, k);       // x == 0  : BR cannot go dir 1
+        }
+    }
+    const int fb = p5 ? P5::FB : P8::FB;
+    u64 tl = p5 ? (u64)P5::ALL : P8::ALL, br = tl;
+    const u64 fm = p5 ? (u64)P5::FM : P8::FM;
+    int cnt = 1;
+    for (int i = 1; i <= L; i++)
+        for (int j = 0; j < i; j++) {
+            int sh = fb * (cnt - 1);
+            tl = (tl & ~(fm << sh)) | ((u64)cell(j, i - j - 1) << sh);
+            br = (br & ~(fm << sh)) | ((u64)cell(N - 1 - j, N - i + j) << sh);
+            cnt++;
+        }
+    g.tl0 = tl; g.br0 = br;
+    return g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// warp-cooperative observation writer: lanes hold one game each, rows leave as coalesced 16-byte vectors
+// ------------------------------------------------------------------------------------------------
+template <class C> __device__ __forceinline__ int lin_cell(const Geo& geo, int c) { return C::x_of(c) * geo.N + C::y_of(c); }
+
+template <class C> __device__ __forceinline__ void stage_rows(const Game<C>& g, bool mine, const Geo& geo, int16_t* sm, int lane) {
+    const int NN = geo.N * geo.N;
+    uint4* v = reinterpret_cast<uint4*>(sm);
+    const int nvec = 4 * NN;                     // 32 rows * NN * 2 bytes / 16
+    for (int k = lane; k < nvec; k += 32) v[k] = make_uint4(0, 0, 0, 0);
+    __syncwarp();
+    if (mine) {
+        int16_t* row = sm + lane * NN;
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            int c = (int)((g.tl >> (C::FB * k)) & C::FM);
+            if (c != (int)C::FM) row[lin_cell<C>(geo, c)] = (int16_t)(k + 1);
+            int d = (int)((g.br >> (C::FB * k)) & C::FM);
+            if (d != (int)C::FM) row[lin_cell<C>(geo, d)] = (int16_t)(-(k + 1));
+        }
+    }
+    __syncwarp();
+}
+// dense: rows of all lanes with env index < n.  warp_env0 = env index of lane 0 (a multiple of 32).
+template <class C> __device__ __forceinline__ void write_rows_dense(int16_t* out, int64_t warp_env0, int64_t n, const Geo& geo,
+                                                                    const int16_t* sm, int lane) {
+    const int NN = geo.N * geo.N;
+    int64_t rows = n - warp_env0; if (rows > 32) rows = 32;
+    int16_t* dst = out + warp_env0 * NN;
+    if (rows == 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        const uint4* v = reinterpret_cast<const uint4*>(sm);
+        uint4* d = reinterpret_cast<uint4*>(dst);
+        for (int k = lane; k < 4 * NN; k += 32) d[k] = v[k];
+    } else {
+        const int total = (int)rows * NN;
+        for (int k = lane; k < total; k += 32) dst[k] = sm[k];
+    }
+    __syncwarp();
+}
+// sparse: only rows whose bit is set in `rows`
+template <class C> __device__ __forceinline__ void write_rows_sparse(int16_t* out, int64_t warp_env0, unsigned rows, const Geo& geo,
+                                                                     const int16_t* sm, int lane) {
+    const int NN = geo.N * geo.N;
+    while (rows) {
+        int r = __ffs((int)rows) - 1; rows &= rows - 1;
+        int16_t* dst = out + (warp_env0 + r) * NN;
+        for (int k = lane; k < NN; k += 32) dst[k] = sm[r * NN + k];
+    }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
+// K0 codec
+// ------------------------------------------------------------------------------------------------
+template <class C> __global__ void __launch_bounds__(TPB) k_reset(u64* state, const int32_t* dice_in, int64_t n, Geo geo, u64 seed,
+                                                                  u64 step, u64 env_id0) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    int dice;
+    if (dice_in) dice = dice_in[i];
+    else { u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_RESET, blk); dice = 1 + (int)bounded(blk[0], (u32)geo.cube_num); }
+    Game<C> g; setup<C>(g, geo, dice);
+    pack(g, state, i);
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_encode(const int16_t* board, const int32_t* dice, const int32_t* player,
+                                                                   u64* state, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    typedef typename C::W W;
+    const int N = geo.N, NN = N * N;
+    Game<C> g; g.tl = C::ALL; g.br = C::ALL;
+    const int16_t* b = board + i * NN;
+    for (int x = 0; x < N; x++)
+        for (int y = 0; y < N; y++) {
+            int v = b[x * N + y];
+            if (v > 0 && v <= 6) { int sh = C::FB * (v - 1); g.tl = (g.tl & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+            else if (v < 0 && v >= -6) { int sh = C::FB * (-v - 1); g.br = (g.br & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+        }
+    int d = dice ? dice[i] : 1;
+    g.dice = d < 1 ? 1 : (d > 6 ? 6 : d);
+    g.player = (player && player[i] == EWN_BOTTOM_RIGHT) ? SIDE_BR : SIDE_TL;
+    pack(g, state, i);
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_decode(const u64* state, int16_t* board, int64_t* dice, int32_t* player,
+                                                                   int64_t n, Geo geo) {
+    extern __shared__ uint4 smem_raw[];
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool mine = i < n;
+    Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0;
+    if (mine) {
+        unpack(g, state, i);
+        if (dice) dice[i] = g.dice;
+        if (player) player[i] = g.player == SIDE_BR ? EWN_BOTTOM_RIGHT : EWN_TOP_LEFT;
+    }
+    if (board) {
+        const int NN = geo.N * geo.N;
+        int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
+        const int64_t warp_env0 = i - lane;
+        if (warp_env0 < n) {
+            stage_rows<C>(g, mine, geo, sm, lane);
+            write_rows_dense<C>(board, warp_env0, n, geo, sm, lane);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 rules
+// ------------------------------------------------------------------------------------------------
+template <class C> __global__ void __launch_bounds__(TPB) k_legal(const u64* state, int player, uint8_t* mask, int8_t* list,
+                                                                  int32_t* count, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
+    Legal l;
+    if (side == SIDE_BR) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
+    else                 l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+    int c = legal_count(l);
+    if (mask) mask[i] = (uint8_t)legal_mask(l);
+    if (count) count[i] = c;
+    if (list) {
+        int8_t* o = list + i * 12;
+        for (int j = 0; j < 6; j++) {
+            int la = -1, di = -1, sh;
+            if (j < c) legal_pick(l, j, la, di, sh);
+            o[2 * j] = (int8_t)la; o[2 * j + 1] = (int8_t)di;
+        }
+    }
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_check_win(const u64* state, uint8_t* win, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    win[i] = full_win<C>(g, geo) ? 1 : 0;
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_ply(u64* state, int player, const int32_t* action, uint8_t* valid,
+                                                                uint8_t* win, int32_t* moved, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
+    int t = 0, sh = -1;
+    bool ok;
+    if (side == SIDE_BR) ok = ply_action<C, SIDE_BR>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
+    else                 ok = ply_action<C, SIDE_TL>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
+    if (ok) g.player = side ^ 1;
+    pack(g, state, i);
+    if (valid) valid[i] = ok ? 1 : 0;
+    if (win) win[i] = full_win<C>(g, geo) ? 1 : 0;
+    if (moved) moved[i] = sh < 0 ? 0 : sh / C::FB + 1;
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_set_dice(u64* state, const int32_t* dice, const int32_t* player, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    if (dice) { int d = dice[i]; g.dice = d < 1 ? 1 : (d > 6 ? 6 : d); }
+    if (player) g.player = player[i] == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL;
+    pack(g, state, i);
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_random_action(const u64* state, int64_t* action, int64_t n, Geo geo,
+                                                                          u64 seed, u64 step, u64 env_id0) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_STEP, blk);
+    Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+    int c = legal_count(l);
+    int la = 0, di = 0, sh;
+    if (c > 0) legal_pick(l, (int)bounded(blk[3], (u32)c), la, di, sh);
+    reinterpret_cast<longlong2*>(action)[i] = make_longlong2(la, di);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 env step
+// ------------------------------------------------------------------------------------------------
+struct StepKArgs {
+    ewn_step_args a;
+    StepParams p;
+};
+
+template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(TPB) k_step(const __grid_constant__ StepKArgs ka) {
+    extern __shared__ uint4 smem_raw[];
+    const ewn_step_args& a = ka.a;
+    const int64_t n = a.n;
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool mine = i < n;
+    const Geo& geo = ka.p.geo;
+
+    Game<C> g, term;
+    g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
+    StepOut out; out.term = 0;
+    if (mine) {
+        StepParams p = ka.p;
+        p.replay = REPLAY; p.shaped = SHAPED;
+        unpack(g, a.state, i);
+        int al = 0, ad = 0;
+        if (!p.agent_random) {
+            if (a.action_i64) { longlong2 v = reinterpret_cast<const longlong2*>(a.action_i64)[i]; al = (int)v.x; ad = (v.y < 0 || v.y > 2) ? 3 : (int)v.y; }
+            else if (a.action_i32) { int2 v = reinterpret_cast<const int2*>(a.action_i32)[i]; al = v.x; ad = v.y; }
+            else { int v = a.action_u8[i]; al = v >= 3; ad = v - 3 * al; }
+        }
+        StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
+        if (REPLAY) {
+            inj.dice_opp = a.inject_dice_opp[i]; inj.dice_next = a.inject_dice_next[i];
+            int2 o = reinterpret_cast<const int2*>(a.inject_opp_action)[i]; inj.o_larger = o.x; inj.o_dir = o.y;
+        }
+        int tol = 0; double prev = 0.0;
+        if (SHAPED) { tol = a.tolerance[i]; prev = a.prev_score[i]; }
+        step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
+        if (SHAPED) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
+        pack(g, a.state, i);
+        if (a.reward_f32) a.reward_f32[i] = (float)out.reward;
+        if (a.reward_f64) a.reward_f64[i] = out.reward;
+        if (a.terminated) a.terminated[i] = (uint8_t)out.term;
+        if (a.truncated) a.truncated[i] = (uint8_t)out.trunc;
+        if (a.code) a.code[i] = out.code;
+        if (a.action_out) a.action_out[i] = (uint8_t)(out.a_larger * 3 + out.a_dir);
+        if (a.obs_dice) a.obs_dice[i] = g.dice;
+        if (a.term_dice && out.term) a.term_dice[i] = term.dice;
+    }
+    const int64_t warp_env0 = i - lane;
+    if (warp_env0 >= n) return;
+    const int NN = geo.N * geo.N;
+    int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
+    if (a.obs_board) {
+        stage_rows<C>(g, mine, geo, sm, lane);
+        write_rows_dense<C>(a.obs_board, warp_env0, n, geo, sm, lane);
+    }
+    if (a.term_board) {
+        const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
+        if (done) {
+            stage_rows<C>(term, mine && out.term, geo, sm, lane);
+            write_rows_sparse<C>(a.term_board, warp_env0, done, geo, sm, lane);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// evaluate
+// ------------------------------------------------------------------------------------------------
+template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* state, double* value, int64_t n, Geo geo, int heuristic) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    value[i] = evaluate<C>(g, geo, heuristic);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4 expectiminimax.  Phase 1 (k_emm_expand): one thread per slot of the deepest move level walks its path from the
+// root (<= 4 plies), writes the value of every position it owns; all positions of a level are produced in parallel,
+// no inter-thread communication.  Phase 2 (k_emm_replay): one thread per root replays minimax.py:19-73 over the
+// stored values, so the reference's window hand-through at chance nodes is reproduced bit for bit.
+// ------------------------------------------------------------------------------------------------
+template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, double* vals, int64_t n_roots, Geo geo,
+                                                                       int depth, int heuristic) {
+    const int m = emm_levels(depth);
+    const u32 slots = (u32)emm_level_size(m);
+    const u32 gid = blockIdx.x * (u32)TPB + threadIdx.x;          // host keeps n_roots * slots below 2^31
+    if (gid >= (u32)n_roots * slots) return;
+    const u32 root = gid / slots, t = gid - root * slots;
+    Game<C> g; unpack(g, state, (long)root);
+    g.player = SIDE_TL;
+    if (full_win<C>(g, geo)) return;               // finished root: phase 2 evaluates it directly
+    emm_expand_slot<C>(g, geo, depth, heuristic, t, vals + (int64_t)root * emm_level_offset(m + 1));
+}
+
+template <class C, int M> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const double* vals, int64_t n_roots,
+                                                                               int64_t root0, Geo geo, int heuristic, int pruned,
+                                                                               double* value, int8_t* action) {
+    int64_t r = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    if (r >= n_roots) return;
+    Game<C> g; unpack(g, state, root0 + r);
+    g.player = SIDE_TL;
+    int la, di;
+    value[root0 + r] = emm_root<C, M>(g, geo, heuristic, pruned, vals + r * emm_level_offset(M + 1), la, di);
+    if (action) { action[2 * (root0 + r)] = (int8_t)la; action[2 * (root0 + r) + 1] = (int8_t)di; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3 flat Monte-Carlo.  k_mc_expand turns roots into (root, child) pairs; k_playouts plays `count` random games
+// per pair with one lane per game.  Lanes that finish pull the next game of their warp's contiguous range, so a
+// warp stays full until its range is exhausted; results depend only on (seed, root id, child, playout index).
+// ------------------------------------------------------------------------------------------------
+struct PairBuf {
+    u64* state;          // [pairs][WORDS]
+    u32* root_id;        // [pairs]
+    u32* slot;           // [pairs]  index into wins; low 3 bits of child kept in child[]
+    u32* child;          // [pairs]
+    int* n_pairs;        // device counter
+};
+
+template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64* state, const u32* root_ids, int64_t n, Geo geo,
+                                                                      PairBuf pb, int32_t* n_children) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    g.player = SIDE_TL;
+    int cnt = 0;
+    if (!full_win<C>(g, geo)) {
+        Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        cnt = legal_count(l);
+        const u32 rid = root_ids ? root_ids[i] : (u32)i;
+        for (int j = 0; j < cnt; j++) {
+            Game<C> c = g;
+            int la, di, sh; legal_pick(l, j, la, di, sh);
+            apply_move<C, SIDE_TL>(c, sh, di);
+            c.player = SIDE_BR;
+            int s = atomicAdd(pb.n_pairs, 1);
+            pack(c, pb.state, s);
+            pb.root_id[s] = rid; pb.child[s] = (u32)j; pb.slot[s] = (u32)(i * 6 + j);
+        }
+    }
+    if (n_children) n_children[i] = cnt;
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* pair_state, const u32* pair_root, const u32* pair_child,
+                                                                     const u32* pair_slot, const int* n_pairs_dev, int64_t n_pairs_host,
+                                                                     u32 first, u32 count, u32* wins, unsigned long long* plies,
+                                                                     Geo geo, u64 seed) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_id = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * TPB) >> 5;
+    const int64_t n_pairs = n_pairs_dev ? (int64_t)*n_pairs_dev : n_pairs_host;
+    const int64_t total = n_pairs * (int64_t)count;
+    int64_t chunk = (total + n_warps - 1) / n_warps;
+    chunk = (chunk + 31) & ~(int64_t)31;
+    int64_t next = warp_id * chunk;
+    int64_t hi = next + chunk; if (hi > total) hi = total;
+    if (next >= hi) return;
+
+    Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
+    bool busy = false;
+    u32 rid = 0, child = 0, slot = 0, pidx = 0, j = 0;
+    unsigned long long my_plies = 0;
+    const unsigned lt = (1u << lane) - 1u;
+    int64_t base_pair = next / count;                          // warp-uniform cursor: game `next` = (base_pair, base_off)
+    u32 base_off = (u32)(next - base_pair * count);
+    for (;;) {
+        const unsigned need = __ballot_sync(0xffffffffu, !busy);
+        if (need) {
+            const u32 rank = (u32)__popc(need & lt), taken = (u32)__popc(need);
+            const int64_t mine = next + rank;
+            if (!busy && mine < hi) {
+                u32 off = base_off + rank;                     // < count + 32
+                const u32 q = off / count;
+                off -= q * count;
+                const int64_t pair = base_pair + q;
+                pidx = first + off;
+                unpack(g, pair_state, pair);
+                rid = pair_root ? pair_root[pair] : (u32)pair;
+                child = pair_child ? pair_child[pair] : 7u;
+                slot = pair_slot ? pair_slot[pair] : (u32)pair;
+                j = 0;
+                busy = true;
+                if (full_win<C>(g, geo)) {                       // mcts.py:28: the loop body never runs
+                    if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
+                    busy = false;
+                }
+            }
+            next += taken;
+            { u32 off = base_off + taken; const u32 q = off / count; base_off = off - q * count; base_pair += q; }
+            if (!__ballot_sync(0xffffffffu, busy) && next >= hi) break;
+        }
+        if (busy) {
+            u32 blk[4];
+            playout_block(seed, rid, child, pidx, j++, blk);
+            g.dice = 1 + (int)bounded(blk[0], 6u);
+            bool over = random_ply<C, SIDE_BR>(g, geo, blk[1], nullptr, nullptr);
+            my_plies++;
+            if (!over) {
+                g.dice = 1 + (int)bounded(blk[2], 6u);
+                over = random_ply<C, SIDE_TL>(g, geo, blk[3], nullptr, nullptr);
+                my_plies++;
+            }
+            if (over) {
+                if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
+                busy = false;
+            }
+        }
+    }
+    if (plies) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) my_plies += __shfl_xor_sync(0xffffffffu, my_plies, o);
+        if (lane == 0) atomicAdd(plies, my_plies);
+    }
+}
+
+template <class C> __global__ void __launch_bounds__(TPB) k_mc_best(const u64* state, const u32* wins, int8_t* action, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    int la = -1, di = -1;
+    if (!full_win<C>(g, geo)) {
+        Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        int cnt = legal_count(l), best = 0;
+        for (int j = 1; j < cnt; j++) if (wins[i * 6 + j] > wins[i * 6 + best]) best = j;      // np.argmax: first maximum
+        int sh; legal_pick(l, best, la, di, sh);
+    }
+    action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di;
+}
+
+// ------------------------------------------------------------------------------------------------
+// library-owned scratch (one per device), grown on demand; used when the caller passes no workspace
+// ------------------------------------------------------------------------------------------------
+struct Scratch { void* p = nullptr; size_t bytes = 0; };
+Scratch g_scratch[64];
+
+int scratch_get(size_t bytes, void** out) {
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return EWN_EARG;
+    Scratch& s = g_scratch[dev];
+    if (s.bytes < bytes) {
+        if (s.p) { CU(cudaDeviceSynchronize()); CU(cudaFree(s.p)); s.p = nullptr; s.bytes = 0; }
+        CU(cudaMalloc(&s.p, bytes));
+        s.bytes = bytes;
+    }
+    *out = s.p;
+    return EWN_OK;
+}
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (!cached[dev]) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cached[dev] = v;
+    }
+    return cached[dev];
+}
+
+template <class C> size_t obs_smem(const Geo& geo) { return (size_t)WARPS * 32 * geo.N * geo.N * sizeof(int16_t); }
+
+#define DISPATCH(N, expr_p5, expr_p8) \
+    do { if (use_p5(N)) { typedef P5 C; expr_p5; } else { typedef P8 C; expr_p8; } } while (0)
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+int ewn_version(void) { return 100; }
+
+const char* ewn_strerror(int code) {
+    switch (code) {
+        case EWN_OK: return "ok";
+        case EWN_EARG: return "bad argument";
+        case EWN_ECUDA: return "CUDA error";
+        case EWN_ENOSUP: return "not supported";
+        case EWN_ESPACE: return "workspace too small";
+        default: return "unknown error";
+    }
+}
+const char* ewn_last_cuda_error(void) { return g_err; }
+
+int ewn_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    return n;
+}
+int ewn_state_words(int N) { return (N >= 3 && N <= EWN_MAX_BOARD) ? (use_p5(N) ? 1 : 2) : EWN_EARG; }
+int64_t ewn_launch_count(void) { return g_launches.load(); }
+
+int ewn_reset(uint64_t* state, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void* stream) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_reset<P5><<<blocks_for(n), TPB, 0, st>>>(state, nullptr, n, geo, seed, step, env_id0);
+    else           k_reset<P8><<<blocks_for(n), TPB, 0, st>>>(state, nullptr, n, geo, seed, step, env_id0);
+    LAUNCHED("k_reset");
+    return EWN_OK;
+}
+
+int ewn_reset_dice(uint64_t* state, const int32_t* dice, int64_t n, int N, int L, void* stream) {
+    if (!state || !dice || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_reset<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, n, geo, 0, 0, 0);
+    else           k_reset<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, n, geo, 0, 0, 0);
+    LAUNCHED("k_reset");
+    return EWN_OK;
+}
+
+int ewn_encode(const int16_t* board, const int32_t* dice, const int32_t* player, uint64_t* state, int64_t n, int N, int L, void* stream) {
+    if (!board || !state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_encode<P5><<<blocks_for(n), TPB, 0, st>>>(board, dice, player, state, n, geo);
+    else           k_encode<P8><<<blocks_for(n), TPB, 0, st>>>(board, dice, player, state, n, geo);
+    LAUNCHED("k_encode");
+    return EWN_OK;
+}
+
+int ewn_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* player, int64_t n, int N, int L, void* stream) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_decode<P5><<<blocks_for(n), TPB, obs_smem<P5>(geo), st>>>(state, board, dice, player, n, geo);
+    else           k_decode<P8><<<blocks_for(n), TPB, obs_smem<P8>(geo), st>>>(state, board, dice, player, n, geo);
+    LAUNCHED("k_decode");
+    return EWN_OK;
+}
+
+int ewn_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, int32_t* count, int64_t n, int N, int L, void* stream) {
+    if (!state || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_legal<P5><<<blocks_for(n), TPB, 0, st>>>(state, player, mask, list, count, n, geo);
+    else           k_legal<P8><<<blocks_for(n), TPB, 0, st>>>(state, player, mask, list, count, n, geo);
+    LAUNCHED("k_legal");
+    return EWN_OK;
+}
+
+int ewn_check_win(const uint64_t* state, uint8_t* win, int64_t n, int N, int L, void* stream) {
+    if (!state || !win || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_check_win<P5><<<blocks_for(n), TPB, 0, st>>>(state, win, n, geo);
+    else           k_check_win<P8><<<blocks_for(n), TPB, 0, st>>>(state, win, n, geo);
+    LAUNCHED("k_check_win");
+    return EWN_OK;
+}
+
+int ewn_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, uint8_t* win, int32_t* moved_cube, int64_t n, int N, int L,
+            void* stream) {
+    if (!state || !action || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_ply<P5><<<blocks_for(n), TPB, 0, st>>>(state, player, action, valid, win, moved_cube, n, geo);
+    else           k_ply<P8><<<blocks_for(n), TPB, 0, st>>>(state, player, action, valid, win, moved_cube, n, geo);
+    LAUNCHED("k_ply");
+    return EWN_OK;
+}
+
+int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, int64_t n, int N, int L, void* stream) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_set_dice<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
+    else           k_set_dice<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
+    LAUNCHED("k_set_dice");
+    return EWN_OK;
+}
+
+int ewn_random_action(const uint64_t* state, int64_t* action, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0,
+                      void* stream) {
+    if (!state || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_random_action<P5><<<blocks_for(n), TPB, 0, st>>>(state, action, n, geo, seed, step, env_id0);
+    else           k_random_action<P8><<<blocks_for(n), TPB, 0, st>>>(state, action, n, geo, seed, step, env_id0);
+    LAUNCHED("k_random_action");
+    return EWN_OK;
+}
+
+int ewn_step(const ewn_step_args* a, void* stream) {
+    if (!a || !a->state || a->n < 0 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
+    if (a->n == 0) return EWN_OK;
+    if (!a->agent_random && !a->action_i64 && !a->action_i32 && !a->action_u8) return EWN_EARG;
+    const bool replay = a->inject_dice_opp || a->inject_opp_action || a->inject_dice_next;
+    if (replay && !(a->inject_dice_opp && a->inject_opp_action && a->inject_dice_next)) return EWN_EARG;
+    if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
+    StepKArgs ka;
+    ka.a = *a;
+    memset(&ka.p, 0, sizeof(ka.p));
+    ka.p.geo = make_geo(a->board_size, a->cube_layer);
+    ka.p.reward = a->reward; ka.p.illegal_move_reward = a->illegal_move_reward;
+    ka.p.seed = a->seed; ka.p.step = a->step; ka.p.env_id0 = a->env_id0;
+    ka.p.agent_random = a->agent_random != 0; ka.p.autoreset = a->autoreset != 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = blocks_for(a->n);
+    const bool need_smem = a->obs_board || a->term_board;
+#define LAUNCH_STEP(C)                                                                               \
+    do {                                                                                             \
+        size_t sm = need_smem ? obs_smem<C>(ka.p.geo) : 0;                                           \
+        if (replay) { if (a->shaped) k_step<C, true, true><<<grid, TPB, sm, st>>>(ka); else k_step<C, true, false><<<grid, TPB, sm, st>>>(ka); } \
+        else        { if (a->shaped) k_step<C, false, true><<<grid, TPB, sm, st>>>(ka); else k_step<C, false, false><<<grid, TPB, sm, st>>>(ka); } \
+    } while (0)
+    if (use_p5(a->board_size)) LAUNCH_STEP(P5); else LAUNCH_STEP(P8);
+#undef LAUNCH_STEP
+    LAUNCHED("k_step");
+    return EWN_OK;
+}
+
+int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void* stream) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_evaluate<P5><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo, heuristic);
+    else           k_evaluate<P8><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo, heuristic);
+    LAUNCHED("k_evaluate");
+    return EWN_OK;
+}
+
+size_t ewn_expectiminimax_workspace(int64_t n, int depth) {
+    if (n <= 0 || depth < 1 || depth > EWN_MAX_DEPTH) return 0;
+    return (size_t)n * (size_t)emm_level_offset(emm_levels(depth) + 1) * sizeof(double);
+}
+
+int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth, int heuristic, int pruned, double* value, int8_t* action,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
+    if (depth < 1 || depth > EWN_MAX_DEPTH) return EWN_ENOSUP;
+    if (L != 3) return EWN_ENOSUP;      // the reference's search hard-codes a six-face die (minimax.py:68)
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int m = emm_levels(depth);
+    const size_t per_root = (size_t)emm_level_offset(m + 1) * sizeof(double);
+    if (!workspace || workspace_bytes == 0) {
+        size_t want = per_root * (size_t)n;
+        const size_t cap = (size_t)1 << 30;
+        if (want > cap) want = cap > per_root ? cap : per_root;
+        int rc = scratch_get(want, &workspace);
+        if (rc) return rc;
+        workspace_bytes = want;
+    }
+    int64_t chunk = (int64_t)(workspace_bytes / per_root);
+    if (chunk < 1) return EWN_ESPACE;
+    const int64_t slots = emm_level_size(m);
+    if (chunk > ((int64_t)1 << 31) / slots - 1) chunk = ((int64_t)1 << 31) / slots - 1;   // 32-bit thread ids in k_emm_expand
+    for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+        const int64_t nr = (n - r0 < chunk) ? (n - r0) : chunk;
+        const uint64_t* s0 = state + r0 * (use_p5(N) ? 1 : 2);
+        const unsigned grid1 = blocks_for(nr * slots);
+        const unsigned grid2 = (unsigned)((nr + 127) / 128);
+        double* vals = (double*)workspace;
+#define LAUNCH_EMM(C)                                                                                              \
+    do {                                                                                                           \
+        k_emm_expand<C><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic);                               \
+        LAUNCHED("k_emm_expand");                                                                                  \
+        switch (m) {                                                                                               \
+            case 1: k_emm_replay<C, 1><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
+            case 2: k_emm_replay<C, 2><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
+            case 3: k_emm_replay<C, 3><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
+            default: k_emm_replay<C, 4><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
+        }                                                                                                          \
+        LAUNCHED("k_emm_replay");                                                                                  \
+    } while (0)
+        if (use_p5(N)) LAUNCH_EMM(P5); else LAUNCH_EMM(P8);
+#undef LAUNCH_EMM
+    }
+    return EWN_OK;
+}
+
+size_t ewn_mc_workspace(int64_t n) {
+    if (n <= 0) return 0;
+    return 256 + (size_t)n * 6 * (16 + 4 + 4 + 4);
+}
+
+static int playout_grid(int64_t total_games) {
+    int64_t warps_needed = (total_games + 31) / 32;
+    int64_t blocks = (warps_needed + WARPS - 1) / WARPS;
+    int64_t cap = (int64_t)sm_count() * 8;       // 8 resident blocks of 256 threads per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                 uint32_t* wins, unsigned long long* plies, void* stream) {
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;      // six-face die hard-coded in the reference's playouts (mcts.py:29)
+    if (n == 0 || count == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = playout_grid(n * (int64_t)count);
+    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, seed);
+    else           k_playouts<P8><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, seed);
+    LAUNCHED("k_playouts");
+    return EWN_OK;
+}
+
+int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                     uint32_t* wins, int32_t* n_children, unsigned long long* plies, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
+    if (n == 0) return EWN_OK;
+    const size_t need = ewn_mc_workspace(n);
+    if (!workspace || workspace_bytes == 0) {
+        int rc = scratch_get(need, &workspace);
+        if (rc) return rc;
+    } else if (workspace_bytes < need) return EWN_ESPACE;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    char* w = (char*)workspace;
+    PairBuf pb;
+    pb.n_pairs = (int*)w;
+    pb.state = (u64*)(w + 256);
+    pb.root_id = (u32*)(w + 256 + (size_t)n * 6 * 16);
+    pb.child = pb.root_id + (size_t)n * 6;
+    pb.slot = pb.child + (size_t)n * 6;
+    CU(cudaMemsetAsync(pb.n_pairs, 0, sizeof(int), st));
+    if (use_p5(N)) k_mc_expand<P5><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children);
+    else           k_mc_expand<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children);
+    LAUNCHED("k_mc_expand");
+    if (count == 0) return EWN_OK;
+    const int grid = playout_grid(n * 6 * (int64_t)count);
+    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, seed);
+    else           k_playouts<P8><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, seed);
+    LAUNCHED("k_playouts");
+    return EWN_OK;
+}
+
+int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void* stream) {
+    if (!state || !wins || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_mc_best<P5><<<blocks_for(n), TPB, 0, st>>>(state, wins, action, n, geo);
+    else           k_mc_best<P8><<<blocks_for(n), TPB, 0, st>>>(state, wins, action, n, geo);
+    LAUNCHED("k_mc_best");
+    return EWN_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-buffer vector environment
+// ------------------------------------------------------------------------------------------------
+struct ewn_vec {
+    ewn_vec_config cfg;
+    int words;
+    int n_streams;
+    cudaStream_t streams[4];
+    uint64_t step;
+    uint64_t* state;
+    int64_t* action;
+    int16_t* obs_board; int64_t* obs_dice; float* reward; uint8_t* done; uint8_t* trunc;
+    int16_t* term_board; int64_t* term_dice;
+    int32_t* tolerance; double* prev_score;
+};
+
+static void vec_free(ewn_vec* v) {
+    if (!v) return;
+    cudaSetDevice(v->cfg.device);
+    for (int i = 0; i < v->n_streams; i++) if (v->streams[i]) cudaStreamDestroy(v->streams[i]);
+    cudaFree(v->state); cudaFree(v->action); cudaFree(v->obs_board); cudaFree(v->obs_dice); cudaFree(v->reward);
+    cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->tolerance); cudaFree(v->prev_score);
+    delete v;
+}
+
+int ewn_vec_create(const ewn_vec_config* cfg, ewn_vec** out) {
+    if (!cfg || !out || cfg->n <= 0 || !config_ok(cfg->board_size, cfg->cube_layer)) return EWN_EARG;
+    ewn_vec* v = new (std::nothrow) ewn_vec();
+    if (!v) return EWN_EARG;
+    memset(v, 0, sizeof(*v));
+    v->cfg = *cfg;
+    if (v->cfg.chunks <= 0) v->cfg.chunks = 8;
+    if (v->cfg.chunks > 64) v->cfg.chunks = 64;
+    v->words = use_p5(cfg->board_size) ? 1 : 2;
+    v->n_streams = 3;
+    const int64_t n = cfg->n;
+    const int NN = cfg->board_size * cfg->board_size;
+    cudaError_t e = cudaSetDevice(cfg->device);
+    if (e != cudaSuccess) { delete v; return cuda_fail(e, "cudaSetDevice"); }
+#define VEC_TRY(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { int rc = cuda_fail(e__, #call); vec_free(v); return rc; } } while (0)
+    for (int i = 0; i < v->n_streams; i++) VEC_TRY(cudaStreamCreateWithFlags(&v->streams[i], cudaStreamNonBlocking));
+    VEC_TRY(cudaMalloc(&v->state, (size_t)n * v->words * 8));
+    VEC_TRY(cudaMalloc(&v->action, (size_t)n * 16));
+    VEC_TRY(cudaMalloc(&v->obs_board, (size_t)n * NN * 2));
+    VEC_TRY(cudaMalloc(&v->obs_dice, (size_t)n * 8));
+    VEC_TRY(cudaMalloc(&v->reward, (size_t)n * 4));
+    VEC_TRY(cudaMalloc(&v->done, (size_t)n));
+    VEC_TRY(cudaMalloc(&v->trunc, (size_t)n));
+    VEC_TRY(cudaMalloc(&v->term_board, (size_t)n * NN * 2));
+    VEC_TRY(cudaMalloc(&v->term_dice, (size_t)n * 8));
+    if (cfg->shaped) {
+        VEC_TRY(cudaMalloc(&v->tolerance, (size_t)n * 4));
+        VEC_TRY(cudaMalloc(&v->prev_score, (size_t)n * 8));
+    }
+#undef VEC_TRY
+    *out = v;
+    return EWN_OK;
+}
+
+void ewn_vec_destroy(ewn_vec* v) { vec_free(v); }
+uint64_t* ewn_vec_state(ewn_vec* v) { return v ? v->state : nullptr; }
+uint64_t ewn_vec_step_index(const ewn_vec* v) { return v ? v->step : 0; }
+
+// fills an int32 / f64 array with a constant (shaped-env bookkeeping at creation time)
+__global__ void k_fill_i32(int32_t* p, int32_t v, int64_t n) { int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x; if (i < n) p[i] = v; }
+
+int ewn_vec_reset(ewn_vec* v, int16_t* obs_board, int64_t* obs_dice) {
+    if (!v) return EWN_EARG;
+    CU(cudaSetDevice(v->cfg.device));
+    const ewn_vec_config& c = v->cfg;
+    cudaStream_t st = v->streams[0];
+    const int NN = c.board_size * c.board_size;
+    int rc = ewn_reset(v->state, c.n, c.board_size, c.cube_layer, c.seed, v->step, c.env_id0, st);
+    if (rc) return rc;
+    if (c.shaped && v->step == 0) {
+        // training_ewn.py:35-38: tolerance budget and prev_score are set once, at construction
+        k_fill_i32<<<blocks_for(c.n), TPB, 0, st>>>(v->tolerance, c.illegal_move_tolerance, c.n);
+        LAUNCHED("k_fill_i32");
+        rc = ewn_evaluate(v->state, v->prev_score, c.n, c.board_size, c.cube_layer, EWN_H_HYBRID, st);
+        if (rc) return rc;
+    }
+    rc = ewn_decode(v->state, v->obs_board, v->obs_dice, nullptr, c.n, c.board_size, c.cube_layer, st);
+    if (rc) return rc;
+    if (obs_board) CU(cudaMemcpyAsync(obs_board, v->obs_board, (size_t)c.n * NN * 2, cudaMemcpyDeviceToHost, st));
+    if (obs_dice) CU(cudaMemcpyAsync(obs_dice, v->obs_dice, (size_t)c.n * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    v->step++;
+    return EWN_OK;
+}
+
+int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t* obs_dice, float* reward, uint8_t* done, uint8_t* truncated,
+                 int16_t* term_board, int64_t* term_dice) {
+    if (!v || !action) return EWN_EARG;
+    CU(cudaSetDevice(v->cfg.device));
+    const ewn_vec_config& c = v->cfg;
+    const int NN = c.board_size * c.board_size;
+    // chunk boundaries are multiples of 1024 games so that every chunk starts 16-byte aligned in every array
+    int64_t per = (c.n + c.chunks - 1) / c.chunks;
+    per = (per + 1023) & ~(int64_t)1023;
+    int k = 0;
+    for (int64_t lo = 0; lo < c.n; lo += per, k++) {
+        const int64_t m = (c.n - lo < per) ? (c.n - lo) : per;
+        cudaStream_t st = v->streams[k % v->n_streams];
+        CU(cudaMemcpyAsync(v->action + 2 * lo, action + 2 * lo, (size_t)m * 16, cudaMemcpyHostToDevice, st));
+        ewn_step_args a;
+        memset(&a, 0, sizeof(a));
+        a.state = v->state + lo * v->words; a.n = m; a.board_size = c.board_size; a.cube_layer = c.cube_layer;
+        a.action_i64 = v->action + 2 * lo;
+        a.reward_f32 = v->reward + lo; a.terminated = v->done + lo; a.truncated = v->trunc + lo;
+        a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
+        if (term_board) a.term_board = v->term_board + lo * NN;
+        if (term_dice) a.term_dice = v->term_dice + lo;
+        if (c.shaped) { a.tolerance = v->tolerance + lo; a.prev_score = v->prev_score + lo; a.shaped = 1; }
+        a.reward = c.reward; a.illegal_move_reward = c.illegal_move_reward;
+        a.seed = c.seed; a.step = v->step; a.env_id0 = c.env_id0 + (uint64_t)lo;
+        a.autoreset = 1;
+        int rc = ewn_step(&a, st);
+        if (rc) return rc;
+        if (obs_board) CU(cudaMemcpyAsync(obs_board + lo * NN, v->obs_board + lo * NN, (size_t)m * NN * 2, cudaMemcpyDeviceToHost, st));
+        if (obs_dice) CU(cudaMemcpyAsync(obs_dice + lo, v->obs_dice + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        if (reward) CU(cudaMemcpyAsync(reward + lo, v->reward + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        if (done) CU(cudaMemcpyAsync(done + lo, v->done + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
+        if (truncated) CU(cudaMemcpyAsync(truncated + lo, v->trunc + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
+        if (term_board) CU(cudaMemcpyAsync(term_board + lo * NN, v->term_board + lo * NN, (size_t)m * NN * 2, cudaMemcpyDeviceToHost, st));
+        if (term_dice) CU(cudaMemcpyAsync(term_dice + lo, v->term_dice + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+    }
+    for (int i = 0; i < v->n_streams; i++) CU(cudaStreamSynchronize(v->streams[i]));
+    v->step++;
+    return EWN_OK;
+}
+
+int ewn_host_alloc(void** ptr, size_t bytes) {
+    if (!ptr) return EWN_EARG;
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return EWN_OK;
+}
+int ewn_host_free(void* ptr) {
+    if (ptr) CU(cudaFreeHost(ptr));
+    return EWN_OK;
+}
+
+}  // extern "C"

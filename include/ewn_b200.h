@@ -1,0 +1,211 @@
+/* ewn_b200.h -- C ABI of libewn_b200.so: the B200 (sm_100a) engine behind the ewn-gym surface.
+ *
+ * The reference (jchen8tw/ewn-gym) is pure Python and has no FFI of its own; the boundary it exposes for this
+ * path is three Python interfaces.  Each entry point below states which reference code it
+ * replaces (file:line relative to the reference root).  INTEGRATION.md shows the ctypes binding a maintainer of
+ * the reference would add.
+ *
+ * Conventions
+ *   - plain C, no torch types: device pointers + sizes + an explicit cudaStream_t (passed as void*; NULL = the
+ *     legacy default stream).  Entry points only enqueue work on `stream`; they never synchronise, except the
+ *     ewn_vec_* host-buffer calls, which return after the outputs are in the caller's host buffers.
+ *   - every function returns 0 on success or a negative EWN_E* code; nothing throws; no hidden global state.
+ *   - `state` is the packed game array: ewn_state_words(N) u64 per game (1 for N<=5, 2 for N<=9), game-major.
+ *     Layout is documented in DESIGN.md "Packed state" and ewn_gym_b200/csrc/ewn_core.cuh.
+ *   - boards are int16 [n][N][N] exactly as the reference's observation (envs/ewn.py:63-69): +k TOP_LEFT cube k,
+ *     -k BOTTOM_RIGHT cube k, 0 empty.  Players: 1 = TOP_LEFT, 2 = BOTTOM_RIGHT (constants/player.py:5-6).
+ *   - actions are [larger, direction] pairs (envs/ewn.py:61-62).
+ *   - legal masks use bit (larger*3 + direction).
+ *   - there is no CPU fallback: without a CUDA device every compute entry point returns EWN_ECUDA.
+ */
+#ifndef EWN_B200_H
+#define EWN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define EWN_API __attribute__((visibility("default")))
+#else
+#define EWN_API
+#endif
+
+#define EWN_OK 0
+#define EWN_EARG (-1)      /* bad argument (NULL pointer, size, board_size / cube_layer out of range) */
+#define EWN_ECUDA (-2)     /* CUDA runtime error; ewn_last_cuda_error() has the text */
+#define EWN_ENOSUP (-3)    /* combination not supported (e.g. search with cube_layer != 3, depth > EWN_MAX_DEPTH) */
+#define EWN_ESPACE (-4)    /* workspace too small */
+
+#define EWN_MAX_BOARD 9
+#define EWN_MAX_DEPTH 8
+
+#define EWN_TOP_LEFT 1
+#define EWN_BOTTOM_RIGHT 2
+
+/* step result codes (info["message"] of envs/ewn.py:448,454,473,478 and training_ewn.py:56) */
+#define EWN_CODE_ONGOING 0
+#define EWN_CODE_AGENT_ILLEGAL 1      /* "Illegal move!"            reward -R, terminated, truncated */
+#define EWN_CODE_AGENT_WON 2          /* "You won!"                 reward +R, terminated            */
+#define EWN_CODE_OPP_ILLEGAL 3        /* "Opponent illegal move!"   reward 0,  terminated, truncated */
+#define EWN_CODE_AGENT_LOST 4         /* "You lost!"                reward -R, terminated            */
+#define EWN_CODE_ILLEGAL_TOLERATED 5  /* training_ewn.py:48-56      reward illegal_move_reward, state unchanged */
+
+#define EWN_H_HYBRID 0        /* envs/minimax_ewn.py:39-86   */
+#define EWN_H_MIN_DIST 1      /* envs/minimax_ewn.py:88-131  */
+#define EWN_H_TWO_MIN_DIST 2  /* envs/minimax_ewn.py:133-178 */
+#define EWN_H_ATTK 3          /* envs/minimax_ewn.py:180-213 */
+
+EWN_API int ewn_version(void);
+EWN_API const char *ewn_strerror(int code);
+EWN_API const char *ewn_last_cuda_error(void);
+/* number of CUDA devices visible, or EWN_ECUDA */
+EWN_API int ewn_device_count(void);
+/* u64 words per game for this board size (1 or 2), or EWN_EARG */
+EWN_API int ewn_state_words(int board_size);
+/* total kernels launched by this library in this process (bench.py reports it as gpu_launches) */
+EWN_API int64_t ewn_launch_count(void);
+
+/* ---- state codec ----------------------------------------------------------------------------------------- */
+
+/* setup_game + first roll_dice (envs/ewn.py:94-108, :488-494).  Die = Philox(seed; env_id0+i, step, RESET). */
+EWN_API int ewn_reset(uint64_t *state, int64_t n, int board_size, int cube_layer, uint64_t seed, uint64_t step, uint64_t env_id0,
+              void *stream);
+/* Same layout, dice supplied by the caller (int32[n], values 1..cube_num). */
+EWN_API int ewn_reset_dice(uint64_t *state, const int32_t *dice, int64_t n, int board_size, int cube_layer, void *stream);
+
+/* observation -> packed state: the piece-list rebuild of classical_policies/minimax.py:75-87 restore_env_with_obs.
+ * dice: int32[n] or NULL (=1); player: int32[n] (1/2) or NULL (= TOP_LEFT). */
+EWN_API int ewn_encode(const int16_t *board, const int32_t *dice, const int32_t *player, uint64_t *state, int64_t n, int board_size,
+               int cube_layer, void *stream);
+/* packed state -> observation (envs/ewn.py:485: {"board", "dice_roll"}); any output pointer may be NULL. */
+EWN_API int ewn_decode(const uint64_t *state, int16_t *board, int64_t *dice, int32_t *player, int64_t n, int board_size, int cube_layer,
+               void *stream);
+
+/* ---- rules ----------------------------------------------------------------------------------------------- */
+
+/* envs/ewn.py:338-375 get_legal_actions(player).  player: 0 = the state's side to move, 1 / 2 = forced.
+ * mask: u8[n]; list: int8[n][6][2] in the reference's list order, padded with -1 (or NULL); count: int32[n] (or NULL). */
+EWN_API int ewn_legal(const uint64_t *state, int player, uint8_t *mask, int8_t *list, int32_t *count, int64_t n, int board_size,
+              int cube_layer, void *stream);
+/* envs/ewn.py:131-142 check_win -> u8[n] */
+EWN_API int ewn_check_win(const uint64_t *state, uint8_t *win, int64_t n, int board_size, int cube_layer, void *stream);
+/* One ply for `player` (0 = side to move): find_cube_to_move + execute_move + check_win (envs/ewn.py:439-451, :377-412
+ * make_simulated_action).  action: int32[n][2].  Does not roll the die; flips the side to move when the move was valid.
+ * valid / win: u8[n] (or NULL); moved_cube: int32[n] 1-based cube number, 0 if none (or NULL). */
+EWN_API int ewn_ply(uint64_t *state, int player, const int32_t *action, uint8_t *valid, uint8_t *win, int32_t *moved_cube, int64_t n,
+            int board_size, int cube_layer, void *stream);
+/* MinimaxEnv.set_dice_roll (envs/minimax_ewn.py:26-27): overwrite the die (int32[n]) and optionally the side to move. */
+EWN_API int ewn_set_dice(uint64_t *state, const int32_t *dice, const int32_t *player, int64_t n, int board_size, int cube_layer,
+                 void *stream);
+/* classical_policies/random_policy.py:11-15 RandomAgent.predict for the TOP_LEFT side of every game:
+ * action int64[n][2] = uniform over the ordered legal list, index = bounded(Philox(seed; env_id0+i, step, STEP)[3]). */
+EWN_API int ewn_random_action(const uint64_t *state, int64_t *action, int64_t n, int board_size, int cube_layer, uint64_t seed,
+                      uint64_t step, uint64_t env_id0, void *stream);
+
+/* ---- env step (envs/ewn.py:436-486; envs/training_ewn.py:40-99 when shaped) ------------------------------ */
+
+typedef struct ewn_step_args {
+    uint64_t *state;              /* in/out, n games, agent (TOP_LEFT) to move                                  */
+    int64_t n;
+    int32_t board_size, cube_layer;
+    /* agent action: exactly one of the three, or none when agent_random != 0                                   */
+    const int64_t *action_i64;    /* [n][2]  (SB3 VecEnv.step_async dtype)                                      */
+    const int32_t *action_i32;    /* [n][2]                                                                     */
+    const uint8_t *action_u8;     /* [n]     packed larger*3+dir (engine-native)                                */
+    /* outputs (any may be NULL)                                                                                */
+    float *reward_f32;            /* [n]                                                                        */
+    double *reward_f64;           /* [n]  bit-exact shaped rewards                                              */
+    uint8_t *terminated;          /* [n]  "done"                                                                */
+    uint8_t *truncated;           /* [n]                                                                        */
+    int32_t *code;                /* [n]  EWN_CODE_*                                                            */
+    uint8_t *action_out;          /* [n]  larger*3+dir actually played (useful with agent_random)               */
+    int16_t *obs_board;           /* [n][N][N] observation after the step (after auto-reset for finished games) */
+    int64_t *obs_dice;            /* [n]                                                                        */
+    int16_t *term_board;          /* [n][N][N] rows written only where terminated: info["terminal_observation"] */
+    int64_t *term_dice;           /* [n]       likewise                                                         */
+    /* MiniMaxHeuristicEnv state (required when shaped != 0), persists across resets: training_ewn.py:35-38     */
+    int32_t *tolerance;           /* [n] in/out                                                                 */
+    double *prev_score;           /* [n] in/out                                                                 */
+    /* replay mode: dice and opponent answers recorded from the reference instead of Philox (all int32)         */
+    const int32_t *inject_dice_opp;   /* [n]     roll at envs/ewn.py:458                                        */
+    const int32_t *inject_opp_action; /* [n][2]  opponent_action() at :461                                      */
+    const int32_t *inject_dice_next;  /* [n]     roll at :483 (or the first roll after an auto-reset)           */
+    double reward;                /* goal reward, envs/ewn.py:38                                                */
+    double illegal_move_reward;   /* training_ewn.py:25                                                         */
+    uint64_t seed, step, env_id0; /* Philox key / counter: env i uses (env_id0+i, step)                         */
+    int32_t agent_random;         /* TOP_LEFT plays uniformly over its legal list inside the kernel             */
+    int32_t autoreset;            /* SB3 VecEnv contract                                                        */
+    int32_t shaped;               /* MiniMaxHeuristicEnv.step                                                   */
+    int32_t reserved;
+} ewn_step_args;
+
+EWN_API int ewn_step(const ewn_step_args *args, void *stream);
+
+/* ---- search ---------------------------------------------------------------------------------------------- */
+
+/* envs/minimax_ewn.py:29-213 evaluate(heuristic) -> f64[n] */
+EWN_API int ewn_evaluate(const uint64_t *state, double *value, int64_t n, int board_size, int cube_layer, int heuristic, void *stream);
+
+/* classical_policies/minimax.py:19-93 ExpectiMinimaxAgent.predict on n roots (TOP_LEFT to move, die from the state).
+ * pruned != 0 reproduces the reference's alpha/beta hand-through at chance nodes bit for bit; 0 = textbook.
+ * value: f64[n]; action: int8[n][2] (-1,-1 = None for a finished root).
+ * workspace: device scratch of at least ewn_expectiminimax_workspace(n, depth) bytes, or NULL / 0 to let the library
+ * use its own cached allocation. */
+EWN_API size_t ewn_expectiminimax_workspace(int64_t n, int depth);
+EWN_API int ewn_expectiminimax(const uint64_t *state, int64_t n, int board_size, int cube_layer, int depth, int heuristic, int pruned,
+                       double *value, int8_t *action, void *workspace, size_t workspace_bytes, void *stream);
+
+/* classical_policies/mcts.py:21-45 simulate: random playouts from n states with BOTTOM_RIGHT to move.
+ * wins[i] += number of playouts with index in [first, first+count) that TOP_LEFT wins (u32[n], caller zeroes).
+ * root_ids: u32[n] Philox stream ids (NULL = 0..n-1). plies: optional u64[1] accumulator of plies played. */
+EWN_API int ewn_playouts(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
+                 uint32_t first, uint32_t count, uint32_t *wins, unsigned long long *plies, void *stream);
+/* classical_policies/mcts.py:47-84 flat Monte-Carlo over the root's legal actions: for every root i (TOP_LEFT to move)
+ * and list position c, wins[i][c] += TL wins of playouts [first, first+count) started after playing that action.
+ * wins: u32[n][6] (caller zeroes); n_children: int32[n] (or NULL).
+ * workspace: at least ewn_mc_workspace(n) bytes of device scratch, or NULL / 0 for the library's cached allocation. */
+EWN_API size_t ewn_mc_workspace(int64_t n);
+EWN_API int ewn_mc_root_wins(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
+                     uint32_t first, uint32_t count, uint32_t *wins, int32_t *n_children, unsigned long long *plies,
+                     void *workspace, size_t workspace_bytes, void *stream);
+/* first arg-max over the legal children (np.argmax, mcts.py:68) -> action int8[n][2] */
+EWN_API int ewn_mc_best_action(const uint64_t *state, const uint32_t *wins, int8_t *action, int64_t n, int board_size, int cube_layer,
+                       void *stream);
+
+/* ---- host-buffer vector environment (the call a numpy / SB3 user makes) ----------------------------------- */
+/* Owns device state, pinned staging buffers and streams for n games on the current device.  step: actions come from
+ * host memory, observations / rewards / dones land in host memory; copies and the kernel are pipelined in chunks. */
+typedef struct ewn_vec ewn_vec;
+typedef struct ewn_vec_config {
+    int64_t n;
+    int32_t board_size, cube_layer;
+    double reward, illegal_move_reward;
+    uint64_t seed, env_id0;
+    int32_t shaped, illegal_move_tolerance;
+    int32_t chunks;               /* pipeline depth (0 = default)                                               */
+    int32_t device;               /* CUDA device ordinal                                                        */
+} ewn_vec_config;
+
+EWN_API int ewn_vec_create(const ewn_vec_config *cfg, ewn_vec **out);
+EWN_API void ewn_vec_destroy(ewn_vec *v);
+/* VecEnv.reset(): obs_board int16[n][N][N], obs_dice int64[n] (host) */
+EWN_API int ewn_vec_reset(ewn_vec *v, int16_t *obs_board, int64_t *obs_dice);
+/* VecEnv.step(actions int64[n][2]) with auto-reset. term_board/term_dice (host, may be NULL) receive the terminal
+ * observation rows of finished games (all n rows are copied; only rows with done != 0 are meaningful). */
+EWN_API int ewn_vec_step(ewn_vec *v, const int64_t *action, int16_t *obs_board, int64_t *obs_dice, float *reward, uint8_t *done,
+                 uint8_t *truncated, int16_t *term_board, int64_t *term_dice);
+/* pinned host memory helpers so that callers can hand in page-locked numpy buffers */
+EWN_API int ewn_host_alloc(void **ptr, size_t bytes);
+EWN_API int ewn_host_free(void *ptr);
+/* device pointer to the packed state owned by the vec env (for zero-copy use from torch) */
+EWN_API uint64_t *ewn_vec_state(ewn_vec *v);
+EWN_API uint64_t ewn_vec_step_index(const ewn_vec *v);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EWN_B200_H */
