@@ -1,0 +1,134 @@
+"""ctypes binding of libewn_b200.so (include/ewn_b200.h).
+
+The library is built in-tree (``ewn_gym_b200/csrc/Makefile`` or ``__graft_entry__.build()``).  There is no CPU
+fallback: a missing library raises ``ImportError`` with the build command, and compute calls without a CUDA
+device return ``EWN_ECUDA`` which ``check()`` turns into ``RuntimeError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "libewn_b200.so")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xlinker", "--exclude-libs,ALL"]
+
+EWN_OK, EWN_EARG, EWN_ECUDA, EWN_ENOSUP, EWN_ESPACE = 0, -1, -2, -3, -4
+
+p_void = C.c_void_p
+i64, i32, u64, u32 = C.c_int64, C.c_int32, C.c_uint64, C.c_uint32
+
+
+class StepArgs(C.Structure):
+    """struct ewn_step_args"""
+    _fields_ = [
+        ("state", p_void), ("n", i64), ("board_size", i32), ("cube_layer", i32),
+        ("action_i64", p_void), ("action_i32", p_void), ("action_u8", p_void),
+        ("reward_f32", p_void), ("reward_f64", p_void), ("terminated", p_void), ("truncated", p_void), ("code", p_void),
+        ("action_out", p_void), ("obs_board", p_void), ("obs_dice", p_void), ("term_board", p_void), ("term_dice", p_void),
+        ("tolerance", p_void), ("prev_score", p_void),
+        ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
+        ("reward", C.c_double), ("illegal_move_reward", C.c_double),
+        ("seed", u64), ("step", u64), ("env_id0", u64),
+        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("reserved", i32),
+    ]
+
+
+class VecConfig(C.Structure):
+    """struct ewn_vec_config"""
+    _fields_ = [
+        ("n", i64), ("board_size", i32), ("cube_layer", i32), ("reward", C.c_double), ("illegal_move_reward", C.c_double),
+        ("seed", u64), ("env_id0", u64), ("shaped", i32), ("illegal_move_tolerance", i32), ("chunks", i32), ("device", i32),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/ewn_b200.h declares
+PROTOTYPES = {
+    "ewn_version": (C.c_int, []),
+    "ewn_strerror": (C.c_char_p, [C.c_int]),
+    "ewn_last_cuda_error": (C.c_char_p, []),
+    "ewn_device_count": (C.c_int, []),
+    "ewn_state_words": (C.c_int, [C.c_int]),
+    "ewn_launch_count": (i64, []),
+    "ewn_reset": (C.c_int, [p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
+    "ewn_reset_dice": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_encode": (C.c_int, [p_void, p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_decode": (C.c_int, [p_void, p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_legal": (C.c_int, [p_void, C.c_int, p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_check_win": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_ply": (C.c_int, [p_void, C.c_int, p_void, p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_set_dice": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_random_action": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
+    "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),
+    "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
+    "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
+    "ewn_expectiminimax": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void, p_void, C.c_size_t, p_void]),
+    "ewn_playouts": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void]),
+    "ewn_mc_workspace": (C.c_size_t, [i64]),
+    "ewn_mc_root_wins": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
+    "ewn_mc_best_action": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_vec_create": (C.c_int, [C.POINTER(VecConfig), C.POINTER(p_void)]),
+    "ewn_vec_destroy": (None, [p_void]),
+    "ewn_vec_reset": (C.c_int, [p_void, p_void, p_void]),
+    "ewn_vec_step": (C.c_int, [p_void, p_void, p_void, p_void, p_void, p_void, p_void, p_void, p_void]),
+    "ewn_host_alloc": (C.c_int, [C.POINTER(p_void), C.c_size_t]),
+    "ewn_host_free": (C.c_int, [p_void]),
+    "ewn_vec_state": (p_void, [p_void]),
+    "ewn_vec_step_index": (u64, [p_void]),
+}
+# entry points a host simulator (tests/hostsim) does not provide
+_VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_host_alloc", "ewn_host_free",
+             "ewn_vec_state", "ewn_vec_step_index"}
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile libewn_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    srcs = [os.path.join(CSRC, "ewn_kernels.cu"), os.path.join(CSRC, "ewn_core.cuh"),
+            os.path.join(os.path.dirname(_HERE), "include", "ewn_b200.h")]
+    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
+        return LIB_PATH
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH, srcs[0]]
+    subprocess.run(cmd, check=True, cwd=CSRC)
+    return LIB_PATH
+
+
+def bind(path: str, optional=()):
+    """dlopen `path` and attach the prototypes above. Raises if a required symbol is missing."""
+    lib = C.CDLL(path)
+    for name, (res, args) in PROTOTYPES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            if name in optional:
+                continue
+            raise ImportError(f"{path} does not export {name} (include/ewn_b200.h)")
+        fn.restype, fn.argtypes = res, args
+    return lib
+
+
+_lib = None
+
+
+def lib():
+    """The product library. Never falls back to anything else."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `make -C {CSRC}` or `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). ewn_gym_b200 has no CPU fallback.")
+        _lib = bind(LIB_PATH)
+    return _lib
+
+
+def check(rc: int, what: str = "ewn call", library=None):
+    if rc == EWN_OK:
+        return
+    l = library or lib()
+    msg = l.ewn_strerror(rc).decode()
+    if rc == EWN_ECUDA:
+        msg += ": " + l.ewn_last_cuda_error().decode()
+    raise RuntimeError(f"{what} failed ({rc}): {msg}")

@@ -215,6 +215,38 @@ template <class C> EWN_HD void setup(Game<C>& g, const Geo& geo, int dice) {   /
     g.tl = (typename C::W)geo.tl0; g.br = (typename C::W)geo.br0; g.dice = dice; g.player = SIDE_TL;
 }
 
+inline bool use_p5(int N) { return N <= 5; }
+// host side: geometry + initial layout (envs/ewn.py:94-107)
+inline Geo make_geo(int N, int L) {
+    Geo g;
+    g = Geo();
+    g.N = N; g.L = L; g.cube_num = L * (L + 1) / 2;
+    const bool p5 = use_p5(N);
+    auto cell = [&](int x, int y) { return p5 ? P5::cell(x, y) : P8::cell(x, y); };
+    g.corner = cell(N - 1, N - 1);
+    if (p5) {
+        for (int k = 0; k < N; k++) {
+            g.tl_col |= 1u << cell(k, N - 1);   // y == N-1: TL cannot go dir 0
+            g.tl_row |= 1u << cell(N - 1, k);   // x == N-1: TL cannot go dir 1
+            g.br_col |= 1u << cell(k, 0);       // y == 0  : BR cannot go dir 0
+            g.br_row |= 1u << cell(0, k);       // x == 0  : BR cannot go dir 1
+        }
+    }
+    const int fb = p5 ? P5::FB : P8::FB;
+    u64 tl = p5 ? (u64)P5::ALL : P8::ALL, br = tl;
+    const u64 fm = p5 ? (u64)P5::FM : P8::FM;
+    int cnt = 1;
+    for (int i = 1; i <= L; i++)
+        for (int j = 0; j < i; j++) {
+            int sh = fb * (cnt - 1);
+            tl = (tl & ~(fm << sh)) | ((u64)cell(j, i - j - 1) << sh);
+            br = (br & ~(fm << sh)) | ((u64)cell(N - 1 - j, N - i + j) << sh);
+            cnt++;
+        }
+    g.tl0 = tl; g.br0 = br;
+    return g;
+}
+
 // ------------------------------------------------------------------------------------------------
 // rules
 // ------------------------------------------------------------------------------------------------

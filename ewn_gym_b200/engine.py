@@ -1,0 +1,259 @@
+"""Batched engine calls over device-resident tensors: a thin, typed veneer over the C ABI (include/ewn_b200.h).
+
+PyTorch is used for what it is good at here -- device memory, streams, torch.distributed -- and nothing else:
+every operation below is one or two launches of the hand-written sm_100a kernels in csrc/ewn_kernels.cu.
+Tensors that hold packed states are ``int64`` with shape ``[n]`` (board_size <= 5) or ``[n, 2]`` (<= 9).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+from . import _lib
+from ._lib import StepArgs
+
+HEURISTICS = {"hybrid": 0, "min_dist": 1, "two_min_dist": 2, "attk": 3}
+TOP_LEFT, BOTTOM_RIGHT = 1, 2
+CODE_ONGOING, CODE_AGENT_ILLEGAL, CODE_AGENT_WON, CODE_OPP_ILLEGAL, CODE_AGENT_LOST, CODE_ILLEGAL_TOLERATED = range(6)
+MESSAGES = {  # info["message"] strings of envs/ewn.py:448,454,473,478
+    CODE_AGENT_ILLEGAL: "Illegal move!", CODE_AGENT_WON: "You won!", CODE_OPP_ILLEGAL: "Opponent illegal move!",
+    CODE_AGENT_LOST: "You lost!",
+}
+
+
+class TorchCuda:
+    """Array provider: CUDA tensors on one device, work enqueued on torch's current stream."""
+
+    def __init__(self, device=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("ewn_gym_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.torch = torch
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else torch.device(device).index or 0)
+        t = torch
+        self._dt = {"i8": t.int8, "u8": t.uint8, "i16": t.int16, "i32": t.int32, "u32": t.int32, "i64": t.int64, "u64": t.int64,
+                    "f32": t.float32, "f64": t.float64}
+
+    def empty(self, shape, dt):
+        return self.torch.empty(shape, dtype=self._dt[dt], device=self.device)
+
+    def zeros(self, shape, dt):
+        return self.torch.zeros(shape, dtype=self._dt[dt], device=self.device)
+
+    def asarray(self, x, dt):
+        t = self.torch
+        if isinstance(x, t.Tensor):
+            return x.to(device=self.device, dtype=self._dt[dt]).contiguous()
+        import numpy as np
+        a = np.ascontiguousarray(x)
+        if a.dtype == np.uint32:
+            a = a.view(np.int32)
+        elif a.dtype == np.uint64:
+            a = a.view(np.int64)
+        return t.as_tensor(a).to(device=self.device, dtype=self._dt[dt]).contiguous()
+
+    def ptr(self, a):
+        return None if a is None else a.data_ptr()
+
+    def stream(self):
+        return self.torch.cuda.current_stream(self.device).cuda_stream
+
+    def guard(self):
+        return self.torch.cuda.device(self.device)
+
+
+class Engine:
+    """One (board_size, cube_layer) configuration bound to a library and an array provider."""
+
+    def __init__(self, board_size: int = 5, cube_layer: int = 3, device=None, arrays=None, library=None):
+        assert cube_layer < board_size - 1, "envs/ewn.py:47"
+        self.N, self.L = int(board_size), int(cube_layer)
+        self.cube_num = self.L * (self.L + 1) // 2
+        self.lib = library if library is not None else _lib.lib()
+        self.xp = arrays if arrays is not None else TorchCuda(device)
+        self.words = self.lib.ewn_state_words(self.N)
+        if self.words < 1:
+            raise ValueError(f"board_size {board_size} not supported (3..9)")
+
+    # ------------------------------------------------------------------ helpers
+    def _chk(self, rc, what):
+        _lib.check(rc, what, self.lib)
+
+    def _state_shape(self, n):
+        return (n,) if self.words == 1 else (n, 2)
+
+    def new_state(self, n):
+        return self.xp.empty(self._state_shape(n), "u64")
+
+    def _n(self, state):
+        return int(state.shape[0])
+
+    def _opt(self, x, dt):
+        return None if x is None else self.xp.asarray(x, dt)
+
+    # ------------------------------------------------------------------ codec
+    def reset(self, n: int, seed: int = 0, step: int = 0, env_id0: int = 0, out=None):
+        """setup_game + first die (envs/ewn.py:94-108) from the Philox RESET block."""
+        st = self.new_state(n) if out is None else out
+        self._chk(self.lib.ewn_reset(self.xp.ptr(st), n, self.N, self.L, seed, step, env_id0, self.xp.stream()), "ewn_reset")
+        return st
+
+    def reset_dice(self, dice, out=None):
+        d = self.xp.asarray(dice, "i32")
+        n = int(d.shape[0])
+        st = self.new_state(n) if out is None else out
+        self._chk(self.lib.ewn_reset_dice(self.xp.ptr(st), self.xp.ptr(d), n, self.N, self.L, self.xp.stream()), "ewn_reset_dice")
+        return st
+
+    def encode(self, board, dice=None, player=None):
+        b = self.xp.asarray(board, "i16").reshape(-1, self.N, self.N)
+        n = int(b.shape[0])
+        d, p = self._opt(dice, "i32"), self._opt(player, "i32")
+        if d is not None:
+            d = d.reshape(n)
+        if p is not None:
+            p = p.reshape(-1)
+            if int(p.shape[0]) == 1 and n != 1:
+                p = self.xp.asarray([int(p[0])] * n, "i32")
+        st = self.new_state(n)
+        self._chk(self.lib.ewn_encode(self.xp.ptr(b), self.xp.ptr(d), self.xp.ptr(p), self.xp.ptr(st), n, self.N, self.L,
+                                      self.xp.stream()), "ewn_encode")
+        return st
+
+    def decode(self, state, want_player=False):
+        n = self._n(state)
+        board, dice = self.xp.empty((n, self.N, self.N), "i16"), self.xp.empty((n,), "i64")
+        player = self.xp.empty((n,), "i32") if want_player else None
+        self._chk(self.lib.ewn_decode(self.xp.ptr(state), self.xp.ptr(board), self.xp.ptr(dice), self.xp.ptr(player), n, self.N, self.L,
+                                      self.xp.stream()), "ewn_decode")
+        return (board, dice, player) if want_player else (board, dice)
+
+    # ------------------------------------------------------------------ rules
+    def legal(self, state, player: int = 0, want_list=True):
+        n = self._n(state)
+        mask, cnt = self.xp.empty((n,), "u8"), self.xp.empty((n,), "i32")
+        lst = self.xp.empty((n, 6, 2), "i8") if want_list else None
+        self._chk(self.lib.ewn_legal(self.xp.ptr(state), player, self.xp.ptr(mask), self.xp.ptr(lst), self.xp.ptr(cnt), n, self.N, self.L,
+                                     self.xp.stream()), "ewn_legal")
+        return mask, lst, cnt
+
+    def check_win(self, state):
+        n = self._n(state)
+        win = self.xp.empty((n,), "u8")
+        self._chk(self.lib.ewn_check_win(self.xp.ptr(state), self.xp.ptr(win), n, self.N, self.L, self.xp.stream()), "ewn_check_win")
+        return win
+
+    def ply(self, state, action, player: int = 0):
+        """In place. -> (valid u8[n], win u8[n], moved_cube i32[n])"""
+        n = self._n(state)
+        a = self.xp.asarray(action, "i32").reshape(n, 2)
+        valid, win, moved = self.xp.empty((n,), "u8"), self.xp.empty((n,), "u8"), self.xp.empty((n,), "i32")
+        self._chk(self.lib.ewn_ply(self.xp.ptr(state), player, self.xp.ptr(a), self.xp.ptr(valid), self.xp.ptr(win), self.xp.ptr(moved), n,
+                                   self.N, self.L, self.xp.stream()), "ewn_ply")
+        return valid, win, moved
+
+    def set_dice(self, state, dice=None, player=None):
+        n = self._n(state)
+        d, p = self._opt(dice, "i32"), self._opt(player, "i32")
+        self._chk(self.lib.ewn_set_dice(self.xp.ptr(state), self.xp.ptr(d), self.xp.ptr(p), n, self.N, self.L, self.xp.stream()),
+                  "ewn_set_dice")
+        return state
+
+    def random_action(self, state, seed: int, step: int, env_id0: int = 0, out=None):
+        n = self._n(state)
+        a = self.xp.empty((n, 2), "i64") if out is None else out
+        self._chk(self.lib.ewn_random_action(self.xp.ptr(state), self.xp.ptr(a), n, self.N, self.L, seed, step, env_id0,
+                                             self.xp.stream()), "ewn_random_action")
+        return a
+
+    # ------------------------------------------------------------------ env step
+    def step(self, state, action=None, *, seed=0, step=0, env_id0=0, reward=1.0, agent_random=False, autoreset=True,
+             shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None,
+             want=("reward_f32", "terminated", "truncated"), out: Optional[dict] = None):
+        """One env step for every game (envs/ewn.py:436-486), in place on `state`.
+
+        action : int64[n,2] / int32[n,2] / uint8[n] tensor, or None with agent_random.
+        inject : (dice_opp i32[n], opp_action i32[n,2], dice_next i32[n]) for replay mode.
+        want   : names of ewn_step_args outputs to allocate; `out` may carry pre-allocated ones.
+        Returns the dict of output tensors.
+        """
+        n = self._n(state)
+        xp = self.xp
+        res = dict(out or {})
+        shapes = {"reward_f32": ((n,), "f32"), "reward_f64": ((n,), "f64"), "terminated": ((n,), "u8"), "truncated": ((n,), "u8"),
+                  "code": ((n,), "i32"), "action_out": ((n,), "u8"), "obs_board": ((n, self.N, self.N), "i16"), "obs_dice": ((n,), "i64"),
+                  "term_board": ((n, self.N, self.N), "i16"), "term_dice": ((n,), "i64")}
+        for name in want:
+            if name not in res:
+                res[name] = xp.empty(*shapes[name])
+        a = StepArgs()
+        a.state, a.n, a.board_size, a.cube_layer = xp.ptr(state), n, self.N, self.L
+        keep = []
+        if action is not None:
+            import numpy as np
+            dtn = str(action.dtype).replace("torch.", "")
+            if dtn == "int64":
+                a.action_i64 = xp.ptr(action)
+            elif dtn == "int32":
+                a.action_i32 = xp.ptr(action)
+            elif dtn == "uint8":
+                a.action_u8 = xp.ptr(action)
+            else:
+                act = xp.asarray(action, "i64")
+                keep.append(act)
+                a.action_i64 = xp.ptr(act)
+        for name in shapes:
+            if name in res and res[name] is not None:
+                setattr(a, name, xp.ptr(res[name]))
+        if shaped:
+            a.tolerance, a.prev_score = xp.ptr(tolerance), xp.ptr(prev_score)
+        if inject is not None:
+            d0, oa, d1 = (xp.asarray(inject[0], "i32"), xp.asarray(inject[1], "i32"), xp.asarray(inject[2], "i32"))
+            keep += [d0, oa, d1]
+            a.inject_dice_opp, a.inject_opp_action, a.inject_dice_next = xp.ptr(d0), xp.ptr(oa), xp.ptr(d1)
+        a.reward, a.illegal_move_reward = float(reward), float(illegal_move_reward)
+        a.seed, a.step, a.env_id0 = seed, step, env_id0
+        a.agent_random, a.autoreset, a.shaped = int(agent_random), int(autoreset), int(shaped)
+        self._chk(self.lib.ewn_step(C.byref(a), xp.stream()), "ewn_step")
+        return res
+
+    # ------------------------------------------------------------------ search
+    def evaluate(self, state, heuristic="hybrid"):
+        n = self._n(state)
+        v = self.xp.empty((n,), "f64")
+        self._chk(self.lib.ewn_evaluate(self.xp.ptr(state), self.xp.ptr(v), n, self.N, self.L, HEURISTICS[heuristic], self.xp.stream()),
+                  "ewn_evaluate")
+        return v
+
+    def expectiminimax(self, state, depth: int, heuristic="hybrid", pruned=True):
+        """-> (value f64[n], action i8[n,2]); action (-1,-1) = None for finished roots (minimax.py:22-23)."""
+        n = self._n(state)
+        v, a = self.xp.empty((n,), "f64"), self.xp.empty((n, 2), "i8")
+        self._chk(self.lib.ewn_expectiminimax(self.xp.ptr(state), n, self.N, self.L, depth, HEURISTICS[heuristic], int(bool(pruned)),
+                                              self.xp.ptr(v), self.xp.ptr(a), None, 0, self.xp.stream()), "ewn_expectiminimax")
+        return v, a
+
+    def playouts(self, state, seed: int, first: int, count: int, root_ids=None, wins=None, plies=None):
+        n = self._n(state)
+        w = self.xp.zeros((n,), "u32") if wins is None else wins
+        rid = self._opt(root_ids, "u32")
+        self._chk(self.lib.ewn_playouts(self.xp.ptr(state), self.xp.ptr(rid), n, self.N, self.L, seed, first, count, self.xp.ptr(w),
+                                        self.xp.ptr(plies), self.xp.stream()), "ewn_playouts")
+        return w
+
+    def mc_root_wins(self, state, seed: int, first: int, count: int, root_ids=None, wins=None, plies=None):
+        """-> (wins i32[n,6] by legal-list position, n_children i32[n])"""
+        n = self._n(state)
+        w = self.xp.zeros((n, 6), "u32") if wins is None else wins
+        nch = self.xp.empty((n,), "i32")
+        rid = self._opt(root_ids, "u32")
+        self._chk(self.lib.ewn_mc_root_wins(self.xp.ptr(state), self.xp.ptr(rid), n, self.N, self.L, seed, first, count, self.xp.ptr(w),
+                                            self.xp.ptr(nch), self.xp.ptr(plies), None, 0, self.xp.stream()), "ewn_mc_root_wins")
+        return w, nch
+
+    def mc_best_action(self, state, wins):
+        n = self._n(state)
+        a = self.xp.empty((n, 2), "i8")
+        self._chk(self.lib.ewn_mc_best_action(self.xp.ptr(state), self.xp.ptr(wins), self.xp.ptr(a), n, self.N, self.L, self.xp.stream()),
+                  "ewn_mc_best_action")
+        return a

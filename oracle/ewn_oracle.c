@@ -479,7 +479,8 @@ API void orc_playouts(const int16_t *board, const uint32_t *root_ids, long n, in
  *   blk = philox(seed; env_id, step, TAG_STEP):  blk[0] die for the opponent (:458), blk[1] opponent's index
  *   into its legal list (random_policy.py:12-14), blk[2] die for the next agent turn (:483), blk[3] the agent's
  *   index into its legal list when agent_random != 0.
- *   reset: die = 1 + bounded(philox(seed; env_id, step, TAG_RESET)[0], cube_num)      (:108)
+ *   explicit reset (orc_reset_philox): die = 1 + bounded(philox(seed; env_id, step, TAG_RESET)[0], cube_num)  (:108)
+ *   auto-reset inside a step: die = 1 + bounded(blk[2], cube_num) (blk[2] is unused by a step that ends the game)
  * shaped != 0 follows envs/training_ewn.py:40-99 (tolerance and prev_score persist across resets).
  * autoreset != 0 follows the SB3 VecEnv contract: terminal board/dice are saved, the env is re-initialised.
  * ---------------------------------------------------------------------------------------------- */
@@ -548,8 +549,9 @@ API void orc_step_philox(int16_t *board, int32_t *dice, const int32_t *action /*
         if (te && cfg->autoreset) {
             if (term_board) g_to_board(&g, term_board + i * N * N);
             if (term_dice) term_dice[i] = g.dice;
-            uint32_t rb[4]; env_block(cfg->seed, env_id, cfg->step, TAG_RESET, rb);
-            g_setup(&g, N, L); g.dice = 1 + (int)bounded(rb[0], (uint32_t)g.cube_num);
+            /* the episode ended, so blk[2] (the "next agent turn" die) was not consumed: it becomes the first die of
+             * the new episode (envs/ewn.py:108) -- one Philox block per env step, never two */
+            g_setup(&g, N, L); g.dice = 1 + (int)bounded(blk[2], (uint32_t)g.cube_num);
         }
         g_to_board(&g, board + i * N * N); dice[i] = g.dice;
     }

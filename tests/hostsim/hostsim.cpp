@@ -1,0 +1,352 @@
+// hostsim.cpp -- TEST INFRASTRUCTURE ONLY.  Compiles ewn_gym_b200/csrc/ewn_core.cuh (the per-game bodies of the
+// CUDA kernels) with g++ and drives them with plain loops behind the SAME C signatures as include/ewn_b200.h, so
+// the CPU-only test tier can check the packed-state logic against the oracle before GPU time is spent, and so the
+// kernel bodies can be stepped in gdb / run under sanitizers.  Never loaded by the ewn_gym_b200 package; the
+// product has no CPU path (libewn_b200.so returns EWN_ECUDA without a device).
+#include <stdint.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/ewn_b200.h"
+#include "../../ewn_gym_b200/csrc/ewn_core.cuh"
+
+using namespace ewn;
+
+namespace {
+inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L <= 3 && L < N - 1; }
+
+template <class C> void decode_one(const Game<C>& g, const Geo& geo, int16_t* row) {
+    const int N = geo.N;
+    memset(row, 0, sizeof(int16_t) * N * N);
+    for (int k = 0; k < 6; k++) {
+        int c = (int)((g.tl >> (C::FB * k)) & C::FM);
+        if (c != (int)C::FM) row[C::x_of(c) * N + C::y_of(c)] = (int16_t)(k + 1);
+        int d = (int)((g.br >> (C::FB * k)) & C::FM);
+        if (d != (int)C::FM) row[C::x_of(d) * N + C::y_of(d)] = (int16_t)(-(k + 1));
+    }
+}
+
+template <class C> int t_reset(uint64_t* state, const int32_t* dice_in, int64_t n, const Geo& geo, u64 seed, u64 step, u64 env_id0) {
+    for (int64_t i = 0; i < n; i++) {
+        int dice;
+        if (dice_in) dice = dice_in[i];
+        else { u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_RESET, blk); dice = 1 + (int)bounded(blk[0], (u32)geo.cube_num); }
+        Game<C> g; setup<C>(g, geo, dice);
+        pack(g, state, i);
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_encode(const int16_t* board, const int32_t* dice, const int32_t* player, uint64_t* state, int64_t n, const Geo& geo) {
+    typedef typename C::W W;
+    const int N = geo.N, NN = N * N;
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; g.tl = C::ALL; g.br = C::ALL;
+        const int16_t* b = board + i * NN;
+        for (int x = 0; x < N; x++)
+            for (int y = 0; y < N; y++) {
+                int v = b[x * N + y];
+                if (v > 0 && v <= 6) { int sh = C::FB * (v - 1); g.tl = (g.tl & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+                else if (v < 0 && v >= -6) { int sh = C::FB * (-v - 1); g.br = (g.br & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+            }
+        int d = dice ? dice[i] : 1;
+        g.dice = d < 1 ? 1 : (d > 6 ? 6 : d);
+        g.player = (player && player[i] == EWN_BOTTOM_RIGHT) ? SIDE_BR : SIDE_TL;
+        pack(g, state, i);
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* player, int64_t n, const Geo& geo) {
+    const int NN = geo.N * geo.N;
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i);
+        if (dice) dice[i] = g.dice;
+        if (player) player[i] = g.player == SIDE_BR ? EWN_BOTTOM_RIGHT : EWN_TOP_LEFT;
+        if (board) decode_one<C>(g, geo, board + i * NN);
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, int32_t* count, int64_t n, const Geo& geo) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i);
+        int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
+        Legal l;
+        if (side == SIDE_BR) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
+        else                 l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        int c = legal_count(l);
+        if (mask) mask[i] = (uint8_t)legal_mask(l);
+        if (count) count[i] = c;
+        if (list) {
+            int8_t* o = list + i * 12;
+            for (int j = 0; j < 6; j++) {
+                int la = -1, di = -1, sh;
+                if (j < c) legal_pick(l, j, la, di, sh);
+                o[2 * j] = (int8_t)la; o[2 * j + 1] = (int8_t)di;
+            }
+        }
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, uint8_t* win, int32_t* moved, int64_t n,
+                             const Geo& geo) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i);
+        int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
+        int t = 0, sh = -1; bool ok;
+        if (side == SIDE_BR) ok = ply_action<C, SIDE_BR>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
+        else                 ok = ply_action<C, SIDE_TL>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
+        if (ok) g.player = side ^ 1;
+        pack(g, state, i);
+        if (valid) valid[i] = ok ? 1 : 0;
+        if (win) win[i] = full_win<C>(g, geo) ? 1 : 0;
+        if (moved) moved[i] = sh < 0 ? 0 : sh / C::FB + 1;
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
+    const int NN = geo.N * geo.N;
+    const bool replay = a.inject_dice_opp != nullptr;
+    StepParams p; memset(&p, 0, sizeof(p));
+    p.geo = geo; p.reward = a.reward; p.illegal_move_reward = a.illegal_move_reward;
+    p.seed = a.seed; p.step = a.step; p.env_id0 = a.env_id0;
+    p.agent_random = a.agent_random != 0; p.autoreset = a.autoreset != 0; p.shaped = a.shaped != 0; p.replay = replay;
+    for (int64_t i = 0; i < a.n; i++) {
+        Game<C> g, term; unpack(g, a.state, i); term = g;
+        int al = 0, ad = 0;
+        if (!p.agent_random) {
+            if (a.action_i64) { al = (int)a.action_i64[2 * i]; int64_t y = a.action_i64[2 * i + 1]; ad = (y < 0 || y > 2) ? 3 : (int)y; }
+            else if (a.action_i32) { al = a.action_i32[2 * i]; ad = a.action_i32[2 * i + 1]; }
+            else { int v = a.action_u8[i]; al = v >= 3; ad = v - 3 * al; }
+        }
+        StepInject inj = {1, 0, 0, 1};
+        if (replay) { inj.dice_opp = a.inject_dice_opp[i]; inj.dice_next = a.inject_dice_next[i]; inj.o_larger = a.inject_opp_action[2 * i]; inj.o_dir = a.inject_opp_action[2 * i + 1]; }
+        int tol = 0; double prev = 0.0;
+        if (p.shaped) { tol = a.tolerance[i]; prev = a.prev_score[i]; }
+        StepOut out;
+        step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
+        if (p.shaped) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
+        pack(g, a.state, i);
+        if (a.reward_f32) a.reward_f32[i] = (float)out.reward;
+        if (a.reward_f64) a.reward_f64[i] = out.reward;
+        if (a.terminated) a.terminated[i] = (uint8_t)out.term;
+        if (a.truncated) a.truncated[i] = (uint8_t)out.trunc;
+        if (a.code) a.code[i] = out.code;
+        if (a.action_out) a.action_out[i] = (uint8_t)(out.a_larger * 3 + out.a_dir);
+        if (a.obs_dice) a.obs_dice[i] = g.dice;
+        if (a.obs_board) decode_one<C>(g, geo, a.obs_board + i * NN);
+        if (out.term) {
+            if (a.term_dice) a.term_dice[i] = term.dice;
+            if (a.term_board) decode_one<C>(term, geo, a.term_board + i * NN);
+        }
+    }
+    return EWN_OK;
+}
+
+template <class C, int M> void emm_replay_all(const uint64_t* state, const double* vals, int64_t n, const Geo& geo, int heuristic, int pruned,
+                                              double* value, int8_t* action) {
+    for (int64_t r = 0; r < n; r++) {
+        Game<C> g; unpack(g, state, r); g.player = SIDE_TL;
+        int la, di;
+        value[r] = emm_root<C, M>(g, geo, heuristic, pruned, vals + r * emm_level_offset(M + 1), la, di);
+        if (action) { action[2 * r] = (int8_t)la; action[2 * r + 1] = (int8_t)di; }
+    }
+}
+
+template <class C> int t_emm(const uint64_t* state, int64_t n, const Geo& geo, int depth, int heuristic, int pruned, double* value, int8_t* action) {
+    const int m = emm_levels(depth);
+    const long slots = emm_level_size(m), per_root = emm_level_offset(m + 1);
+    const int64_t chunk = 256;
+    std::vector<double> vals((size_t)chunk * per_root);
+    for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+        const int64_t nr = n - r0 < chunk ? n - r0 : chunk;
+        for (int64_t r = 0; r < nr; r++) {
+            Game<C> g; unpack(g, state, r0 + r); g.player = SIDE_TL;
+            if (full_win<C>(g, geo)) continue;
+            for (long t = 0; t < slots; t++) emm_expand_slot<C>(g, geo, depth, heuristic, (u32)t, vals.data() + r * per_root);
+        }
+        const uint64_t* s0 = state + r0 * C::WORDS;
+        double* v0 = value + r0; int8_t* a0 = action ? action + 2 * r0 : nullptr;
+        switch (m) {
+            case 1: emm_replay_all<C, 1>(s0, vals.data(), nr, geo, heuristic, pruned, v0, a0); break;
+            case 2: emm_replay_all<C, 2>(s0, vals.data(), nr, geo, heuristic, pruned, v0, a0); break;
+            case 3: emm_replay_all<C, 3>(s0, vals.data(), nr, geo, heuristic, pruned, v0, a0); break;
+            default: emm_replay_all<C, 4>(s0, vals.data(), nr, geo, heuristic, pruned, v0, a0); break;
+        }
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, const Geo& geo, u64 seed, u32 first, u32 count,
+                                  uint32_t* wins, unsigned long long* plies) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i);
+        for (u32 p = first; p < first + count; p++) {
+            int pl = 0;
+            wins[i] += (u32)playout<C>(g, geo, seed, root_ids ? root_ids[i] : (u32)i, 7u, p, &pl);
+            if (plies) *plies += (unsigned long long)pl;
+        }
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_mc(const uint64_t* state, const uint32_t* root_ids, int64_t n, const Geo& geo, u64 seed, u32 first, u32 count,
+                            uint32_t* wins, int32_t* n_children, unsigned long long* plies) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i); g.player = SIDE_TL;
+        int cnt = 0;
+        if (!full_win<C>(g, geo)) {
+            Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+            cnt = legal_count(l);
+            for (int j = 0; j < cnt; j++) {
+                Game<C> c = g; int la, di, sh; legal_pick(l, j, la, di, sh);
+                apply_move<C, SIDE_TL>(c, sh, di);
+                for (u32 p = first; p < first + count; p++) {
+                    int pl = 0;
+                    wins[i * 6 + j] += (u32)playout<C>(c, geo, seed, root_ids ? root_ids[i] : (u32)i, (u32)j, p, &pl);
+                    if (plies) *plies += (unsigned long long)pl;
+                }
+            }
+        }
+        if (n_children) n_children[i] = cnt;
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_mc_best(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, const Geo& geo) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i);
+        int la = -1, di = -1;
+        if (!full_win<C>(g, geo)) {
+            Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+            int cnt = legal_count(l), best = 0;
+            for (int j = 1; j < cnt; j++) if (wins[i * 6 + j] > wins[i * 6 + best]) best = j;
+            int sh; legal_pick(l, best, la, di, sh);
+        }
+        action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di;
+    }
+    return EWN_OK;
+}
+}  // namespace
+
+#define BY_CODEC(N, call_p5, call_p8) (use_p5(N) ? (call_p5) : (call_p8))
+
+extern "C" {
+int ewn_version(void) { return -100; }   // negative: this is the host simulator, not the product library
+const char* ewn_strerror(int) { return "hostsim"; }
+const char* ewn_last_cuda_error(void) { return ""; }
+int ewn_device_count(void) { return 0; }
+int ewn_state_words(int N) { return (N >= 3 && N <= EWN_MAX_BOARD) ? (use_p5(N) ? 1 : 2) : EWN_EARG; }
+int64_t ewn_launch_count(void) { return 0; }
+
+int ewn_reset(uint64_t* state, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void*) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_reset<P5>(state, nullptr, n, geo, seed, step, env_id0), t_reset<P8>(state, nullptr, n, geo, seed, step, env_id0));
+}
+int ewn_reset_dice(uint64_t* state, const int32_t* dice, int64_t n, int N, int L, void*) {
+    if (!state || !dice || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_reset<P5>(state, dice, n, geo, 0, 0, 0), t_reset<P8>(state, dice, n, geo, 0, 0, 0));
+}
+int ewn_encode(const int16_t* board, const int32_t* dice, const int32_t* player, uint64_t* state, int64_t n, int N, int L, void*) {
+    if (!board || !state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_encode<P5>(board, dice, player, state, n, geo), t_encode<P8>(board, dice, player, state, n, geo));
+}
+int ewn_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* player, int64_t n, int N, int L, void*) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_decode<P5>(state, board, dice, player, n, geo), t_decode<P8>(state, board, dice, player, n, geo));
+}
+int ewn_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, int32_t* count, int64_t n, int N, int L, void*) {
+    if (!state || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_legal<P5>(state, player, mask, list, count, n, geo), t_legal<P8>(state, player, mask, list, count, n, geo));
+}
+int ewn_check_win(const uint64_t* state, uint8_t* win, int64_t n, int N, int L, void*) {
+    if (!state || !win || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    for (int64_t i = 0; i < n; i++) {
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); win[i] = full_win<P5>(g, geo); }
+        else { Game<P8> g; unpack(g, state, i); win[i] = full_win<P8>(g, geo); }
+    }
+    return EWN_OK;
+}
+int ewn_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, uint8_t* win, int32_t* moved, int64_t n, int N, int L, void*) {
+    if (!state || !action || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_ply<P5>(state, player, action, valid, win, moved, n, geo), t_ply<P8>(state, player, action, valid, win, moved, n, geo));
+}
+int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, int64_t n, int N, int L, void*) {
+    if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    for (int64_t i = 0; i < n; i++) {
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); if (dice) g.dice = dice[i]; if (player) g.player = player[i] == EWN_BOTTOM_RIGHT; pack(g, state, i); }
+        else { Game<P8> g; unpack(g, state, i); if (dice) g.dice = dice[i]; if (player) g.player = player[i] == EWN_BOTTOM_RIGHT; pack(g, state, i); }
+    }
+    return EWN_OK;
+}
+int ewn_random_action(const uint64_t* state, int64_t* action, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void*) {
+    if (!state || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    for (int64_t i = 0; i < n; i++) {
+        u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_STEP, blk);
+        Legal l;
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); l = legal<P5, SIDE_TL>(g, geo, movers<P5>(g.tl, g.dice)); }
+        else { Game<P8> g; unpack(g, state, i); l = legal<P8, SIDE_TL>(g, geo, movers<P8>(g.tl, g.dice)); }
+        int c = legal_count(l), la = 0, di = 0, sh;
+        if (c > 0) legal_pick(l, (int)bounded(blk[3], (u32)c), la, di, sh);
+        action[2 * i] = la; action[2 * i + 1] = di;
+    }
+    return EWN_OK;
+}
+int ewn_step(const ewn_step_args* a, void*) {
+    if (!a || !a->state || a->n < 0 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
+    if (!a->agent_random && !a->action_i64 && !a->action_i32 && !a->action_u8) return EWN_EARG;
+    const bool replay = a->inject_dice_opp || a->inject_opp_action || a->inject_dice_next;
+    if (replay && !(a->inject_dice_opp && a->inject_opp_action && a->inject_dice_next)) return EWN_EARG;
+    if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
+    Geo geo = make_geo(a->board_size, a->cube_layer);
+    return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
+}
+int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void*) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    for (int64_t i = 0; i < n; i++) {
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); value[i] = evaluate<P5>(g, geo, heuristic); }
+        else { Game<P8> g; unpack(g, state, i); value[i] = evaluate<P8>(g, geo, heuristic); }
+    }
+    return EWN_OK;
+}
+size_t ewn_expectiminimax_workspace(int64_t, int) { return 0; }
+int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth, int heuristic, int pruned, double* value, int8_t* action,
+                       void*, size_t, void*) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
+    if (depth < 1 || depth > EWN_MAX_DEPTH || L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_emm<P5>(state, n, geo, depth, heuristic, pruned, value, action), t_emm<P8>(state, n, geo, depth, heuristic, pruned, value, action));
+}
+int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                 uint32_t* wins, unsigned long long* plies, void*) {
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_playouts<P5>(state, root_ids, n, geo, seed, first, count, wins, plies), t_playouts<P8>(state, root_ids, n, geo, seed, first, count, wins, plies));
+}
+size_t ewn_mc_workspace(int64_t) { return 0; }
+int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                     uint32_t* wins, int32_t* n_children, unsigned long long* plies, void*, size_t, void*) {
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_mc<P5>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies), t_mc<P8>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies));
+}
+int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void*) {
+    if (!state || !wins || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_mc_best<P5>(state, wins, action, n, geo), t_mc_best<P8>(state, wins, action, n, geo));
+}
+}  // extern "C"
