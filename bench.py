@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric on B200: env steps/s (and random playouts/s) for 5x5 EinStein wuerfelt nicht.
+
+  python bench.py --gpus N --steps K --warmup W            # our arm (one rank per GPU under torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference algorithm on the host cores (CPU port)
+
+A "step" is one VecEnv.step over `--envs` concurrent games per GPU (BASELINE.json configs[1]: 1,048,576 games, random
+actions): one launch of the fused kernel k_step (agent ply, Philox die, random opponent ply, die, win tests, auto-reset,
+reward / done, int16 board + int64 dice observation, terminal observations).  `value` is timed with CUDA events on the
+launching stream with inputs resident in HBM and L2 flushed between steps; `e2e` goes through EWNVecEnv.step with host
+(page-locked) action and observation buffers.  DESIGN.md "Measurement" has the byte accounting.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+N_BOARD, N_LAYER = 5, 3
+SEED = 9487
+# algorithmic bytes per env step, 5x5 gym surface: state 8 R + 8 W, action int64x2 16 R, reward f32 4 W,
+# terminated + truncated 2 W, board int16[25] 50 W, dice int64 8 W.  Terminal-observation rows are extra, uncounted.
+BYTES_PER_STEP = 8 + 8 + 16 + 4 + 2 + 50 + 8
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_steps(n_envs, min_seconds, threads):
+    """The reference algorithm (envs/ewn.py:436-486 with a random opponent) as restated in oracle/ewn_oracle.c, all host
+    threads, uniform random actions, auto-reset: env steps per second."""
+    from oracle import oracle as O
+    board, dice = O.reset_philox(n_envs, SEED, 0)
+    rng = np.random.default_rng(1)
+    acts = [np.stack([rng.integers(0, 2, n_envs), rng.integers(0, 3, n_envs)], 1).astype(np.int64) for _ in range(4)]
+    O.step_philox(board[:1024], dice[:1024], acts[0][:1024], SEED, 0)          # build + warm
+    steps, t0, t = 0, time.perf_counter(), 0
+    while True:
+        out = O.step_philox(board, dice, acts[t % 4], SEED, t + 1, threads=threads)
+        board, dice = out["board"], out["dice"]
+        t += 1; steps += n_envs
+        el = time.perf_counter() - t0
+        if el >= min_seconds:
+            return steps / el, t, el
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm for the same workload on the box's host cores (C port of the
+    pure-Python reference; the Python original cannot travel to the GPU box). Rank 0 only."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_s = 1 << 18
+    from oracle import oracle as O
+    board, dice = O.reset_philox(n_s, SEED, 0)
+    rng = np.random.default_rng(1)
+    acts = [np.stack([rng.integers(0, 2, n_s), rng.integers(0, 3, n_s)], 1).astype(np.int64) for _ in range(4)]
+    t_all = []
+    for k in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        out = O.step_philox(board, dice, acts[k % 4], SEED, k + 1, threads=cores)
+        board, dice = out["board"], out["dice"]
+        if k >= args.warmup:
+            t_all.append(time.perf_counter() - t0)
+    ms = 1e3 * float(np.mean(t_all))
+    v = n_s / (ms / 1e3)
+    line = {"impl": "reference", "metric": "env_steps_per_sec", "value": v, "unit": "env steps/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+            "data": "synthetic", "config": workload_config(args, n_s),
+            "cpu_baseline": {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port",
+                             "sample": f"{n_s} concurrent 5x5 games per step, uniform random actions, auto-reset, {args.steps} steps"},
+            "e2e": {"value": v, "unit": "env steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n_envs):
+    return {"workload": "5x5 batched env step (BASELINE.json configs[1]): concurrent games per GPU, uniform random actions over "
+                        "MultiDiscrete([2,3]), random opponent in-kernel, auto-reset, VecEnv observation surface",
+            "board_size": N_BOARD, "cube_layer": N_LAYER, "envs_per_gpu": n_envs, "l2": "flushed between timed steps (256 MiB write)",
+            "bytes_per_env_step": BYTES_PER_STEP}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from ewn_gym_b200 import _lib
+    from ewn_gym_b200.engine import Engine
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: there is no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.lib()
+    e = Engine(N_BOARD, N_LAYER, device=dev)
+    n = args.envs
+    env_id0 = rank * n
+    state = e.reset(n, seed=SEED, step=0, env_id0=env_id0)
+    g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
+    acts = [torch.stack([torch.randint(0, 2, (n,), generator=g, device=dev), torch.randint(0, 3, (n,), generator=g, device=dev)], 1).contiguous()
+            for _ in range(4)]
+    out = {k: e.xp.empty(s, d) for k, (s, d) in {
+        "reward_f32": ((n,), "f32"), "terminated": ((n,), "u8"), "truncated": ((n,), "u8"), "obs_board": ((n, N_BOARD, N_BOARD), "i16"),
+        "obs_dice": ((n,), "i64"), "term_board": ((n, N_BOARD, N_BOARD), "i16"), "term_dice": ((n,), "i64")}.items()}
+    stats = torch.zeros(4, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.int8, device=dev)
+    want = tuple(out)
+
+    def one_step(t):
+        e.step(state, acts[t % 4], seed=SEED, step=t, env_id0=env_id0, autoreset=True, stats=stats, want=want, out=out)
+
+    t = 1
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_(); one_step(t); t += 1
+    torch.cuda.synchronize()
+    if dist: dist.barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = lib.ewn_launch_count()
+    wall0 = time.perf_counter()
+    with ClockSampler(local_rank) as clk:
+        for k in range(args.steps):
+            flush.zero_()                         # L2 flush, outside the event pair
+            ev[k][0].record(); one_step(t); ev[k][1].record(); t += 1
+        torch.cuda.synchronize()
+        if args.steps * 1 < 40:                    # keep the GPU busy long enough for the sampler to see load clocks
+            t_end = time.perf_counter() + 1.0
+            while time.perf_counter() < t_end:
+                one_step(t); t += 1
+            torch.cuda.synchronize()
+    wall = time.perf_counter() - wall0
+    launches = lib.ewn_launch_count() - launches0
+    if dist: dist.barrier()
+    ms = np.array([a.elapsed_time(b) for a, b in ev])
+    ms_step = float(ms.mean())
+    if dist:
+        tt = torch.tensor([ms_step], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_step = float(tt.item())
+        dist.all_reduce(stats)                    # the only data-path collective: win / loss / episode counters
+    value = world * n / (ms_step / 1e3)
+
+    # ---- secondary metric: random playouts/s (BASELINE.json configs[2], flat Monte-Carlo, 1024 playouts per root child)
+    playout = None
+    if not args.skip_playouts:
+        roots_n = 4096
+        roots = e.reset(roots_n, seed=SEED + 1)
+        for s in range(1, 5):                     # a few random plies so that roots are mid-game positions
+            e.step(roots, None, seed=SEED + 1, step=s, agent_random=True, autoreset=True, want=())
+        per = 1024 // world
+        wins = torch.zeros(roots_n, 6, dtype=torch.int32, device=dev)
+        plies = torch.zeros(1, dtype=torch.int64, device=dev)
+        e.mc_root_wins(roots, seed=SEED, first=rank * per, count=8, wins=wins.clone())          # warm-up
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if dist: dist.barrier()
+        a0.record()
+        _, nch = e.mc_root_wins(roots, seed=SEED, first=rank * per, count=per, wins=wins, plies=plies)
+        if dist: dist.all_reduce(wins)            # root statistics merge
+        best = e.mc_best_action(roots, wins)
+        a1.record(); torch.cuda.synchronize()
+        pms = a0.elapsed_time(a1)
+        if dist:
+            tt = torch.tensor([pms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); pms = float(tt.item())
+            dist.all_reduce(plies)
+        n_pairs = int(nch.sum().item())
+        playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
+                   "playouts_per_child": 1024, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024)}
+
+    # ---- secondary: expectiminimax depth 4 (configs[3])
+    emm = None
+    if not args.skip_search:
+        roots_n = 65536
+        roots = e.reset(roots_n, seed=SEED + 2)
+        for s in range(1, 5):
+            e.step(roots, None, seed=SEED + 2, step=s, agent_random=True, autoreset=True, want=())
+        e.expectiminimax(roots[:1024], 4)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); a0.record()
+        v, a = e.expectiminimax(roots, 4)
+        a1.record(); torch.cuda.synchronize()
+        ems = a0.elapsed_time(a1)
+        emm = {"value": roots_n / (ems / 1e3), "unit": "roots/s (depth 4, hybrid, pruned semantics)", "ms": ems, "roots": roots_n, "per_gpu": True}
+
+    if rank != 0:
+        if dist: dist.destroy_process_group()
+        return
+
+    # ---- e2e through the public host-buffer API (EWNVecEnv.step: pinned host actions in, host observations out)
+    from ewn_gym_b200.vec_env import EWNVecEnv
+    e2e = None
+    if not args.skip_e2e:
+        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank)
+        env.reset()
+        rng = np.random.default_rng(7)
+        pool = [np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64) for _ in range(2)]
+        abuf = env.action_buffer
+        for k in range(3):
+            abuf[...] = pool[k % 2]; env.step(abuf)
+        ksteps = max(3, min(args.steps, 20))
+        tot = 0.0
+        for k in range(ksteps):
+            abuf[...] = pool[k % 2]                  # the policy's output lands in page-locked memory (untimed)
+            t0 = time.perf_counter()
+            obs, rew, done, infos = env.step(abuf)   # H2D actions + kernel + D2H obs/reward/done/terminal obs, synchronous
+            tot += time.perf_counter() - t0
+        nn = N_BOARD * N_BOARD
+        e2e = {"value": n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n,
+               "d2h_bytes_per_step": (2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8) * n, "ms_per_step": 1e3 * tot / ksteps, "steps": ksteps,
+               "n_gpus": 1, "note": "one GPU, host wall clock around EWNVecEnv.step; PCIe-bound"}
+        env.close()
+
+    hbm, peak_src = peaks()
+    kernel_ms = float(ms.mean())
+    achieved = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_step<P5,false,false>", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": BYTES_PER_STEP * n}
+    prof = os.path.join(ROOT, "profiles", "k_step_traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    cpu = None
+    if not args.skip_cpu:
+        cores = os.cpu_count() or 1
+        v, nsteps, el = cpu_port_steps(1 << 18, 10.0, cores)
+        cpu = {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port",
+               "sample": f"{1 << 18} concurrent 5x5 games x {nsteps} steps ({el:.1f} s) of oracle/ewn_oracle.c, uniform random actions, auto-reset"}
+    st = stats.cpu().tolist()
+    line = {"metric": "env_steps_per_sec", "value": value, "unit": "env steps/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm,
+            "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3]},
+            "wall_s_timed_region": wall}
+    print(json.dumps(line), flush=True)
+    if dist: dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=1 << 20, help="concurrent games per GPU")
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-playouts", action="store_true")
+    ap.add_argument("--skip-search", action="store_true")
+    args = ap.parse_args()
+    rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

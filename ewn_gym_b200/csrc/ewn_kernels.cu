@@ -245,7 +245,7 @@ template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(T
 
     Game<C> g, term;
     g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
-    StepOut out; out.term = 0;
+    StepOut out; out.term = 0; out.code = CODE_ONGOING;
     if (mine) {
         StepParams p = ka.p;
         p.replay = REPLAY; p.shaped = SHAPED;
@@ -277,6 +277,17 @@ template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(T
     }
     const int64_t warp_env0 = i - lane;
     if (warp_env0 >= n) return;
+    if (a.stats) {                                  // one atomic per warp and counter, only when non-zero
+        const unsigned won = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_WON);
+        const unsigned lost = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_LOST);
+        const unsigned fin = __ballot_sync(0xffffffffu, mine && out.term);
+        if (lane == 0 && fin) {
+            if (won) atomicAdd(a.stats + 0, (unsigned long long)__popc(won));
+            if (lost) atomicAdd(a.stats + 1, (unsigned long long)__popc(lost));
+            if (fin & ~(won | lost)) atomicAdd(a.stats + 2, (unsigned long long)__popc(fin & ~(won | lost)));
+            atomicAdd(a.stats + 3, (unsigned long long)__popc(fin));
+        }
+    }
     const int NN = geo.N * geo.N;
     int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
     if (a.obs_board) {

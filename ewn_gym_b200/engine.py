@@ -168,12 +168,13 @@ class Engine:
 
     # ------------------------------------------------------------------ env step
     def step(self, state, action=None, *, seed=0, step=0, env_id0=0, reward=1.0, agent_random=False, autoreset=True,
-             shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None,
+             shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None, stats=None,
              want=("reward_f32", "terminated", "truncated"), out: Optional[dict] = None):
         """One env step for every game (envs/ewn.py:436-486), in place on `state`.
 
         action : int64[n,2] / int32[n,2] / uint8[n] tensor, or None with agent_random.
         inject : (dice_opp i32[n], opp_action i32[n,2], dice_next i32[n]) for replay mode.
+        stats  : int64[4] accumulator {agent wins, agent losses, illegal-move endings, finished episodes}.
         want   : names of ewn_step_args outputs to allocate; `out` may carry pre-allocated ones.
         Returns the dict of output tensors.
         """
@@ -205,6 +206,8 @@ class Engine:
         for name in shapes:
             if name in res and res[name] is not None:
                 setattr(a, name, xp.ptr(res[name]))
+        if stats is not None:
+            a.stats = xp.ptr(stats)
         if shaped:
             a.tolerance, a.prev_score = xp.ptr(tolerance), xp.ptr(prev_score)
         if inject is not None:

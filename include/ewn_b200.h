@@ -127,6 +127,8 @@ typedef struct ewn_step_args {
     int64_t *obs_dice;            /* [n]                                                                        */
     int16_t *term_board;          /* [n][N][N] rows written only where terminated: info["terminal_observation"] */
     int64_t *term_dice;           /* [n]       likewise                                                         */
+    unsigned long long *stats;    /* [4] += {agent wins, agent losses, illegal-move endings, finished episodes}: the  */
+                                  /*     counters that are all-reduced across GPUs (eval_random.py:101-108 win rate)   */
     /* MiniMaxHeuristicEnv state (required when shaped != 0), persists across resets: training_ewn.py:35-38     */
     int32_t *tolerance;           /* [n] in/out                                                                 */
     double *prev_score;           /* [n] in/out                                                                 */

@@ -138,6 +138,10 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
         if (a.action_out) a.action_out[i] = (uint8_t)(out.a_larger * 3 + out.a_dir);
         if (a.obs_dice) a.obs_dice[i] = g.dice;
         if (a.obs_board) decode_one<C>(g, geo, a.obs_board + i * NN);
+        if (out.term && a.stats) {
+            if (out.code == CODE_AGENT_WON) a.stats[0]++; else if (out.code == CODE_AGENT_LOST) a.stats[1]++; else a.stats[2]++;
+            a.stats[3]++;
+        }
         if (out.term) {
             if (a.term_dice) a.term_dice[i] = term.dice;
             if (a.term_board) decode_one<C>(term, geo, a.term_board + i * NN);

@@ -160,10 +160,11 @@ def test_step_philox_vs_oracle(backend, N, L, agent_random):
     ob, od = O.reset_philox(n, seed, 0, env_id0, N, L)
     rng = np.random.default_rng(5)
     wins = losses = illegal = 0
+    stats = e.xp.zeros((4,), "i64")
     for t in range(1, 41):
         act = None if agent_random else np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
         out = e.step(state, None if act is None else e.xp.asarray(act, "i64"), seed=seed, step=t, env_id0=env_id0, agent_random=agent_random,
-                     autoreset=True, want=("reward_f32", "reward_f64", "terminated", "truncated", "code", "action_out", "obs_board",
+                     autoreset=True, stats=stats, want=("reward_f32", "reward_f64", "terminated", "truncated", "code", "action_out", "obs_board",
                                            "obs_dice", "term_board", "term_dice"))
         ref = O.step_philox(ob, od, act, seed, t, env_id0, N, L, agent_random=agent_random, autoreset=True, threads=4)
         assert np.array_equal(to_np(out["code"]), ref["code"]), t
@@ -182,6 +183,7 @@ def test_step_philox_vs_oracle(backend, N, L, agent_random):
         wins += int((ref["code"] == O.CODE_AGENT_WON).sum()); losses += int((ref["code"] == O.CODE_AGENT_LOST).sum())
         illegal += int((ref["code"] == O.CODE_AGENT_ILLEGAL).sum())
     assert wins > 300 and losses > 300
+    assert to_np(stats).tolist()[:2] == [wins, losses] and to_np(stats)[2] == illegal and to_np(stats)[3] == wins + losses + illegal
     assert (illegal == 0) if agent_random else (illegal > 300)
 
 
