@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 N_BOARD, N_LAYER = 5, 3
+N_SETS = 4
 SEED = 9487
 # algorithmic bytes per env step, 5x5 gym surface: state 8 R + 8 W, action int64x2 16 R, reward f32 4 W,
 # terminated + truncated 2 W, board int16[25] 50 W, dice int64 8 W.  Terminal-observation rows are extra, uncounted.
@@ -46,7 +47,7 @@ class ClockSampler:
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.proc, self.index, self.t0 = [], None, index, 0.0
 
     def __enter__(self):
         try:
@@ -60,7 +61,10 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def mark(self):
+        self.t0 = time.perf_counter()
 
     def __exit__(self, *a):
         if self.proc:
@@ -72,7 +76,9 @@ class ClockSampler:
 
     def summary(self):
         sm, mx, reasons = [], 0, set()
-        for r in self.rows:
+        for ts, r in self.rows:
+            if ts < self.t0 + 0.15:                 # a sample reports the period before it
+                continue
             try:
                 sm.append(float(r[0])); mx = max(mx, float(r[1]))
             except Exception:
@@ -133,7 +139,7 @@ def run_reference(args, rank, world):
 def workload_config(args, n_envs):
     return {"workload": "5x5 batched env step (BASELINE.json configs[1]): concurrent games per GPU, uniform random actions over "
                         "MultiDiscrete([2,3]), random opponent in-kernel, auto-reset, VecEnv observation surface",
-            "board_size": N_BOARD, "cube_layer": N_LAYER, "envs_per_gpu": n_envs, "l2": "flushed between timed steps (256 MiB write)",
+            "board_size": N_BOARD, "cube_layer": N_LAYER, "envs_per_gpu": n_envs, "l2": f"no flush: {N_SETS} independent env sets of envs_per_gpu games stepped round-robin, working set {N_SETS} x ~154 MB > 126 MB L2",
             "bytes_per_env_step": BYTES_PER_STEP}
 
 
@@ -150,46 +156,55 @@ def run_ours(args, rank, world, local_rank):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.lib()
+    clk = ClockSampler(local_rank).__enter__()      # nvidia-smi takes ~1 s to start: launch it before the set-up work
     e = Engine(N_BOARD, N_LAYER, device=dev)
     n = args.envs
     env_id0 = rank * n
-    state = e.reset(n, seed=SEED, step=0, env_id0=env_id0)
     g = torch.Generator(device=dev); g.manual_seed(1234 + rank)
-    acts = [torch.stack([torch.randint(0, 2, (n,), generator=g, device=dev), torch.randint(0, 3, (n,), generator=g, device=dev)], 1).contiguous()
-            for _ in range(4)]
-    out = {k: e.xp.empty(s, d) for k, (s, d) in {
-        "reward_f32": ((n,), "f32"), "terminated": ((n,), "u8"), "truncated": ((n,), "u8"), "obs_board": ((n, N_BOARD, N_BOARD), "i16"),
-        "obs_dice": ((n,), "i64"), "term_board": ((n, N_BOARD, N_BOARD), "i16"), "term_dice": ((n,), "i64")}.items()}
+    # N_SETS independent env sets stepped round-robin: a step never finds its inputs in L2 (N_SETS x ~154 MB >> 126 MB)
+    shapes = {"reward_f32": ((n,), "f32"), "terminated": ((n,), "u8"), "truncated": ((n,), "u8"), "obs_board": ((n, N_BOARD, N_BOARD), "i16"),
+              "obs_dice": ((n,), "i64"), "term_board": ((n, N_BOARD, N_BOARD), "i16"), "term_dice": ((n,), "i64")}
+    sets = []
+    for s_i in range(N_SETS):
+        sets.append({
+            "state": e.reset(n, seed=SEED + s_i, step=0, env_id0=env_id0),
+            "act": torch.stack([torch.randint(0, 2, (n,), generator=g, device=dev), torch.randint(0, 3, (n,), generator=g, device=dev)], 1).contiguous(),
+            "out": {k: e.xp.empty(sh, d) for k, (sh, d) in shapes.items()}})
     stats = torch.zeros(4, dtype=torch.int64, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.int8, device=dev)
-    want = tuple(out)
+    want = tuple(shapes)
+
+    for s_i, S in enumerate(sets):          # pre-bound launches: one ctypes call per step in the timed loop
+        S["plan"] = e.step_plan(S["state"], S["act"], seed=SEED + s_i, step=0, env_id0=env_id0, autoreset=True, stats=stats, want=want, out=S["out"])
 
     def one_step(t):
-        e.step(state, acts[t % 4], seed=SEED, step=t, env_id0=env_id0, autoreset=True, stats=stats, want=want, out=out)
+        sets[t % N_SETS]["plan"].launch(t // N_SETS + 1)
 
-    t = 1
+    t = 0
     for _ in range(max(args.warmup, 3)):
-        flush.zero_(); one_step(t); t += 1
+        one_step(t); t += 1
     torch.cuda.synchronize()
     if dist: dist.barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = lib.ewn_launch_count()
     wall0 = time.perf_counter()
-    with ClockSampler(local_rank) as clk:
-        for k in range(args.steps):
-            flush.zero_()                         # L2 flush, outside the event pair
-            ev[k][0].record(); one_step(t); ev[k][1].record(); t += 1
-        torch.cuda.synchronize()
-        if args.steps * 1 < 40:                    # keep the GPU busy long enough for the sampler to see load clocks
-            t_end = time.perf_counter() + 1.0
-            while time.perf_counter() < t_end:
-                one_step(t); t += 1
-            torch.cuda.synchronize()
+    clk.mark()
+    ev0.record()
+    for k in range(args.steps):
+        one_step(t); t += 1
+    ev1.record()
+    torch.cuda.synchronize()
     wall = time.perf_counter() - wall0
     launches = lib.ewn_launch_count() - launches0
     if dist: dist.barrier()
-    ms = np.array([a.elapsed_time(b) for a, b in ev])
-    ms_step = float(ms.mean())
+    ms_step = ev0.elapsed_time(ev1) / args.steps
+    kernel_ms = ms_step
+    # the timed region is milliseconds long; keep the identical load running so that nvidia-smi (100 ms period) sees it
+    t_end = time.perf_counter() + (0.0 if args.skip_clocks else max(0.0, 1.5 - wall))
+    while time.perf_counter() < t_end:
+        for _ in range(50):
+            one_step(t); t += 1
+        torch.cuda.synchronize()
+    clk.__exit__()
     if dist:
         tt = torch.tensor([ms_step], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -255,20 +270,21 @@ def run_ours(args, rank, world, local_rank):
         for k in range(3):
             abuf[...] = pool[k % 2]; env.step(abuf)
         ksteps = max(3, min(args.steps, 20))
-        tot = 0.0
+        tot, term_rows = 0.0, 0
         for k in range(ksteps):
             abuf[...] = pool[k % 2]                  # the policy's output lands in page-locked memory (untimed)
             t0 = time.perf_counter()
             obs, rew, done, infos = env.step(abuf)   # H2D actions + kernel + D2H obs/reward/done/terminal obs, synchronous
             tot += time.perf_counter() - t0
+            term_rows += int(env._b["tcount"].array[0])
         nn = N_BOARD * N_BOARD
         e2e = {"value": n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n,
-               "d2h_bytes_per_step": (2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8) * n, "ms_per_step": 1e3 * tot / ksteps, "steps": ksteps,
-               "n_gpus": 1, "note": "one GPU, host wall clock around EWNVecEnv.step; PCIe-bound"}
+               "d2h_bytes_per_step": (2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8 + 4) * (term_rows // ksteps) + 4, "ms_per_step": 1e3 * tot / ksteps,
+               "steps": ksteps, "n_gpus": 1, "terminal_observations_per_step": term_rows // ksteps,
+               "note": "one GPU, host wall clock around EWNVecEnv.step (pinned host buffers, 8 chunks on 3 streams); PCIe-bound"}
         env.close()
 
     hbm, peak_src = peaks()
-    kernel_ms = float(ms.mean())
     achieved = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": "k_step<P5,false,false>", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                 "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": BYTES_PER_STEP * n}
@@ -306,6 +322,7 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-playouts", action="store_true")
     ap.add_argument("--skip-search", action="store_true")
+    ap.add_argument("--skip-clocks", action="store_true", help="no extended load phase for the clock sampler (profiling runs)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

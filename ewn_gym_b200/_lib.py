@@ -28,7 +28,8 @@ class StepArgs(C.Structure):
         ("state", p_void), ("n", i64), ("board_size", i32), ("cube_layer", i32),
         ("action_i64", p_void), ("action_i32", p_void), ("action_u8", p_void),
         ("reward_f32", p_void), ("reward_f64", p_void), ("terminated", p_void), ("truncated", p_void), ("code", p_void),
-        ("action_out", p_void), ("obs_board", p_void), ("obs_dice", p_void), ("term_board", p_void), ("term_dice", p_void), ("stats", p_void),
+        ("action_out", p_void), ("obs_board", p_void), ("obs_dice", p_void), ("term_board", p_void), ("term_dice", p_void),
+        ("term_count", p_void), ("term_index", p_void), ("term_index_base", i64), ("stats", p_void),
         ("tolerance", p_void), ("prev_score", p_void),
         ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
         ("reward", C.c_double), ("illegal_move_reward", C.c_double),
@@ -73,7 +74,7 @@ PROTOTYPES = {
     "ewn_vec_create": (C.c_int, [C.POINTER(VecConfig), C.POINTER(p_void)]),
     "ewn_vec_destroy": (None, [p_void]),
     "ewn_vec_reset": (C.c_int, [p_void, p_void, p_void]),
-    "ewn_vec_step": (C.c_int, [p_void, p_void, p_void, p_void, p_void, p_void, p_void, p_void, p_void]),
+    "ewn_vec_step": (C.c_int, [p_void] * 11),
     "ewn_host_alloc": (C.c_int, [C.POINTER(p_void), C.c_size_t]),
     "ewn_host_free": (C.c_int, [p_void]),
     "ewn_vec_state": (p_void, [p_void]),

@@ -427,6 +427,24 @@ EWN_HD void philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1, u32 ou
     }
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
+// same function with the ten round keys precomputed on the host (they depend on the seed only): the key schedule
+// leaves the per-thread instruction stream and the keys become constant-bank operands
+struct RoundKeys { u32 k[20]; };
+inline RoundKeys make_round_keys(u64 seed) {
+    RoundKeys r; u32 k0 = (u32)seed, k1 = (u32)(seed >> 32);
+    for (int i = 0; i < 10; i++) { r.k[2 * i] = k0; r.k[2 * i + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    return r;
+}
+EWN_HD void philox4x32_10_rk(u32 c0, u32 c1, u32 c2, u32 c3, const RoundKeys& rk, u32 out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        u32 h0 = mulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        u32 h1 = mulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        u32 n0 = h1 ^ c1 ^ rk.k[2 * r], n2 = h0 ^ c3 ^ rk.k[2 * r + 1];
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
 EWN_HD u32 bounded(u32 r, u32 k) { return mulhi(r, k); }   // uniform on [0,k) up to a bias < k / 2^32
 
 enum { TAG_STEP = 0, TAG_RESET = 1, TAG_PLAYOUT = 2 };
@@ -436,6 +454,12 @@ enum { TAG_STEP = 0, TAG_RESET = 1, TAG_PLAYOUT = 2 };
 EWN_HD void env_block(u64 seed, u64 env_id, u64 step, u32 tag, u32 out[4]) {
     philox4x32_10((u32)env_id, (u32)(env_id >> 32), (u32)step, ((u32)(step >> 32) & 0x0FFFFFFFu) | (tag << 28),
                   (u32)seed, (u32)(seed >> 32), out);
+}
+EWN_HD void env_block_rk(const RoundKeys& rk, u64 env_id, u64 step, u32 tag, u32 out[4]) {
+    philox4x32_10_rk((u32)env_id, (u32)(env_id >> 32), (u32)step, ((u32)(step >> 32) & 0x0FFFFFFFu) | (tag << 28), rk, out);
+}
+EWN_HD void playout_block_rk(const RoundKeys& rk, u32 root_id, u32 child, u32 playout, u32 j, u32 out[4]) {
+    philox4x32_10_rk(playout, root_id, j, ((u32)TAG_PLAYOUT << 28) | child, rk, out);
 }
 // per (root, child, playout, j): plies 2j and 2j+1 of that playout; [0],[2] die, [1],[3] index into the legal list
 EWN_HD void playout_block(u64 seed, u32 root_id, u32 child, u32 playout, u32 j, u32 out[4]) {
@@ -485,6 +509,7 @@ struct StepParams {
     double reward;                 // goal reward (envs/ewn.py:38)
     double illegal_move_reward;    // training_ewn.py:25
     u64 seed, step, env_id0;
+    RoundKeys rk;                  // make_round_keys(seed)
     int32_t agent_random;          // agent = uniform over its legal list (blk[3])
     int32_t autoreset;             // SB3 VecEnv contract: re-initialise finished games in the same call
     int32_t shaped;                // MiniMaxHeuristicEnv semantics
@@ -502,7 +527,7 @@ template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const S
                                         const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
     const Geo& geo = p.geo;
     u32 blk[4] = {0, 0, 0, 0};
-    if (!p.replay || p.agent_random) env_block(p.seed, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
+    if (!p.replay || p.agent_random) env_block_rk(p.rk, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
     bool pre = full_win<C>(g, geo);        // stepping an already finished game keeps reporting a win (check_win is sticky)
     out.reward = 0.0; out.term = 0; out.trunc = 0; out.code = CODE_ONGOING;
     bool valid; int t = 0, sh = -1;

@@ -50,50 +50,67 @@ inline unsigned blocks_for(int64_t n) { return (unsigned)((n + TPB - 1) / TPB); 
 // ------------------------------------------------------------------------------------------------
 // warp-cooperative observation writer: lanes hold one game each, rows leave as coalesced 16-byte vectors
 // ------------------------------------------------------------------------------------------------
-template <class C> __device__ __forceinline__ int lin_cell(const Geo& geo, int c) { return C::x_of(c) * geo.N + C::y_of(c); }
+// NT = board size known at compile time (0: read it from geo) -- the hot configurations (5x5, 7x7) get fully unrolled
+// staging loops and, for 5x5, a packed cell index that already is the row-major board index.
+template <class C, int NT> __device__ __forceinline__ int lin_cell(const Geo& geo, int c) {
+    const int N = NT ? NT : geo.N;
+    return (C::S == N) ? c : C::x_of(c) * N + C::y_of(c);
+}
 
-template <class C> __device__ __forceinline__ void stage_rows(const Game<C>& g, bool mine, const Geo& geo, int16_t* sm, int lane) {
-    const int NN = geo.N * geo.N;
+template <class C, int NT> __device__ __forceinline__ void stage_rows(const Game<C>& g, bool mine, const Geo& geo, int16_t* sm, int lane) {
+    const int NN = NT ? NT * NT : geo.N * geo.N;
     uint4* v = reinterpret_cast<uint4*>(sm);
     const int nvec = 4 * NN;                     // 32 rows * NN * 2 bytes / 16
-    for (int k = lane; k < nvec; k += 32) v[k] = make_uint4(0, 0, 0, 0);
+    if (NT) {
+#pragma unroll
+        for (int k = 0; k < (4 * NT * NT + 31) / 32; k++) if (lane + 32 * k < nvec) v[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+    } else {
+        for (int k = lane; k < nvec; k += 32) v[k] = make_uint4(0, 0, 0, 0);
+    }
     __syncwarp();
     if (mine) {
         int16_t* row = sm + lane * NN;
 #pragma unroll
         for (int k = 0; k < 6; k++) {
             int c = (int)((g.tl >> (C::FB * k)) & C::FM);
-            if (c != (int)C::FM) row[lin_cell<C>(geo, c)] = (int16_t)(k + 1);
+            if (c != (int)C::FM) row[lin_cell<C, NT>(geo, c)] = (int16_t)(k + 1);
             int d = (int)((g.br >> (C::FB * k)) & C::FM);
-            if (d != (int)C::FM) row[lin_cell<C>(geo, d)] = (int16_t)(-(k + 1));
+            if (d != (int)C::FM) row[lin_cell<C, NT>(geo, d)] = (int16_t)(-(k + 1));
         }
     }
     __syncwarp();
 }
 // dense: rows of all lanes with env index < n.  warp_env0 = env index of lane 0 (a multiple of 32).
-template <class C> __device__ __forceinline__ void write_rows_dense(int16_t* out, int64_t warp_env0, int64_t n, const Geo& geo,
-                                                                    const int16_t* sm, int lane) {
-    const int NN = geo.N * geo.N;
+template <class C, int NT> __device__ __forceinline__ void write_rows_dense(int16_t* out, int64_t warp_env0, int64_t n, const Geo& geo,
+                                                                            const int16_t* sm, int lane) {
+    const int NN = NT ? NT * NT : geo.N * geo.N;
     int64_t rows = n - warp_env0; if (rows > 32) rows = 32;
     int16_t* dst = out + warp_env0 * NN;
     if (rows == 32 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
         const uint4* v = reinterpret_cast<const uint4*>(sm);
         uint4* d = reinterpret_cast<uint4*>(dst);
-        for (int k = lane; k < 4 * NN; k += 32) d[k] = v[k];
+        if (NT) {
+#pragma unroll
+            for (int k = 0; k < (4 * NT * NT + 31) / 32; k++) if (lane + 32 * k < 4 * NN) __stcs(d + lane + 32 * k, v[lane + 32 * k]);
+        } else {
+            for (int k = lane; k < 4 * NN; k += 32) __stcs(d + k, v[k]);
+        }
     } else {
         const int total = (int)rows * NN;
         for (int k = lane; k < total; k += 32) dst[k] = sm[k];
     }
     __syncwarp();
 }
-// sparse: only rows whose bit is set in `rows`
-template <class C> __device__ __forceinline__ void write_rows_sparse(int16_t* out, int64_t warp_env0, unsigned rows, const Geo& geo,
-                                                                     const int16_t* sm, int lane) {
-    const int NN = geo.N * geo.N;
+// sparse: only rows whose bit is set in `rows`; the k-th such row goes to row dst_row0 + (compact ? k : its lane)
+template <class C, int NT> __device__ __forceinline__ void write_rows_sparse(int16_t* out, int64_t dst_row0, bool compact, unsigned rows,
+                                                                             const Geo& geo, const int16_t* sm, int lane) {
+    const int NN = NT ? NT * NT : geo.N * geo.N;
+    int k = 0;
     while (rows) {
         int r = __ffs((int)rows) - 1; rows &= rows - 1;
-        int16_t* dst = out + (warp_env0 + r) * NN;
-        for (int k = lane; k < NN; k += 32) dst[k] = sm[r * NN + k];
+        int16_t* dst = out + (dst_row0 + (compact ? k : r)) * NN;
+        for (int e = lane; e < NN; e += 32) dst[e] = sm[r * NN + e];
+        k++;
     }
     __syncwarp();
 }
@@ -149,8 +166,8 @@ template <class C> __global__ void __launch_bounds__(TPB) k_decode(const u64* st
         int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
         const int64_t warp_env0 = i - lane;
         if (warp_env0 < n) {
-            stage_rows<C>(g, mine, geo, sm, lane);
-            write_rows_dense<C>(board, warp_env0, n, geo, sm, lane);
+            stage_rows<C, 0>(g, mine, geo, sm, lane);
+            write_rows_dense<C, 0>(board, warp_env0, n, geo, sm, lane);
         }
     }
 }
@@ -234,14 +251,16 @@ struct StepKArgs {
     StepParams p;
 };
 
-template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(TPB) k_step(const __grid_constant__ StepKArgs ka) {
+// VEC = the VecEnv surface and nothing else (int64 actions in; f32 reward, terminated, truncated, int16 board and int64
+// dice out; Philox dice, random opponent): every optional-pointer test below folds away at compile time.
+template <class C, int NT, bool REPLAY, bool SHAPED, bool VEC> __global__ void __launch_bounds__(TPB)
+k_step(const __grid_constant__ StepKArgs ka) {
     extern __shared__ uint4 smem_raw[];
     const ewn_step_args& a = ka.a;
     const int64_t n = a.n;
     const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool mine = i < n;
-    const Geo& geo = ka.p.geo;
 
     Game<C> g, term;
     g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
@@ -249,10 +268,12 @@ template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(T
     if (mine) {
         StepParams p = ka.p;
         p.replay = REPLAY; p.shaped = SHAPED;
+        if (NT) { p.geo.N = NT; p.geo.corner = C::cell(NT - 1, NT - 1); }
+        if (VEC) p.agent_random = 0;
         unpack(g, a.state, i);
         int al = 0, ad = 0;
         if (!p.agent_random) {
-            if (a.action_i64) { longlong2 v = reinterpret_cast<const longlong2*>(a.action_i64)[i]; al = (int)v.x; ad = (v.y < 0 || v.y > 2) ? 3 : (int)v.y; }
+            if (VEC || a.action_i64) { longlong2 v = __ldcs(reinterpret_cast<const longlong2*>(a.action_i64) + i); al = (int)v.x; ad = (v.y < 0 || v.y > 2) ? 3 : (int)v.y; }
             else if (a.action_i32) { int2 v = reinterpret_cast<const int2*>(a.action_i32)[i]; al = v.x; ad = v.y; }
             else { int v = a.action_u8[i]; al = v >= 3; ad = v - 3 * al; }
         }
@@ -266,39 +287,58 @@ template <class C, bool REPLAY, bool SHAPED> __global__ void __launch_bounds__(T
         step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
         if (SHAPED) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
         pack(g, a.state, i);
-        if (a.reward_f32) a.reward_f32[i] = (float)out.reward;
-        if (a.reward_f64) a.reward_f64[i] = out.reward;
-        if (a.terminated) a.terminated[i] = (uint8_t)out.term;
-        if (a.truncated) a.truncated[i] = (uint8_t)out.trunc;
-        if (a.code) a.code[i] = out.code;
-        if (a.action_out) a.action_out[i] = (uint8_t)(out.a_larger * 3 + out.a_dir);
-        if (a.obs_dice) a.obs_dice[i] = g.dice;
-        if (a.term_dice && out.term) a.term_dice[i] = term.dice;
+        if (VEC) {
+            __stcs(a.reward_f32 + i, (float)out.reward);
+            __stcs(a.terminated + i, (uint8_t)out.term);
+            __stcs(a.truncated + i, (uint8_t)out.trunc);
+            __stcs(reinterpret_cast<long long*>(a.obs_dice) + i, (long long)g.dice);
+        } else {
+            if (a.reward_f32) a.reward_f32[i] = (float)out.reward;
+            if (a.reward_f64) a.reward_f64[i] = out.reward;
+            if (a.terminated) a.terminated[i] = (uint8_t)out.term;
+            if (a.truncated) a.truncated[i] = (uint8_t)out.trunc;
+            if (a.code) a.code[i] = out.code;
+            if (a.action_out) a.action_out[i] = (uint8_t)(out.a_larger * 3 + out.a_dir);
+            if (a.obs_dice) a.obs_dice[i] = g.dice;
+        }
     }
     const int64_t warp_env0 = i - lane;
     if (warp_env0 >= n) return;
-    if (a.stats) {                                  // one atomic per warp and counter, only when non-zero
+    Geo geo = ka.p.geo;
+    if (NT) geo.N = NT;
+    const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
+    if (a.stats && done) {                          // one atomic per warp and counter, only when non-zero
         const unsigned won = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_WON);
         const unsigned lost = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_LOST);
-        const unsigned fin = __ballot_sync(0xffffffffu, mine && out.term);
-        if (lane == 0 && fin) {
+        if (lane == 0) {
             if (won) atomicAdd(a.stats + 0, (unsigned long long)__popc(won));
             if (lost) atomicAdd(a.stats + 1, (unsigned long long)__popc(lost));
-            if (fin & ~(won | lost)) atomicAdd(a.stats + 2, (unsigned long long)__popc(fin & ~(won | lost)));
-            atomicAdd(a.stats + 3, (unsigned long long)__popc(fin));
+            if (done & ~(won | lost)) atomicAdd(a.stats + 2, (unsigned long long)__popc(done & ~(won | lost)));
+            atomicAdd(a.stats + 3, (unsigned long long)__popc(done));
         }
     }
     const int NN = geo.N * geo.N;
     int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
-    if (a.obs_board) {
-        stage_rows<C>(g, mine, geo, sm, lane);
-        write_rows_dense<C>(a.obs_board, warp_env0, n, geo, sm, lane);
+    if (VEC || a.obs_board) {
+        stage_rows<C, NT>(g, mine, geo, sm, lane);
+        write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
     }
-    if (a.term_board) {
-        const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
-        if (done) {
-            stage_rows<C>(term, mine && out.term, geo, sm, lane);
-            write_rows_sparse<C>(a.term_board, warp_env0, done, geo, sm, lane);
+    if (done && (a.term_board || a.term_dice || a.term_count)) {
+        const bool compact = a.term_count != nullptr;
+        int64_t row0 = warp_env0;
+        if (compact) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(a.term_count, (unsigned)__popc(done));
+            row0 = (int64_t)__shfl_sync(0xffffffffu, base, 0);
+        }
+        if (mine && out.term) {
+            const int64_t row = compact ? row0 + __popc(done & ((1u << lane) - 1u)) : i;
+            if (a.term_dice) a.term_dice[row] = term.dice;
+            if (compact && a.term_index) a.term_index[row] = (int32_t)(a.term_index_base + i);
+        }
+        if (a.term_board) {
+            stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
+            write_rows_sparse<C, NT>(a.term_board, row0, compact, done, geo, sm, lane);
         }
     }
 }
@@ -646,18 +686,23 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     memset(&ka.p, 0, sizeof(ka.p));
     ka.p.geo = make_geo(a->board_size, a->cube_layer);
     ka.p.reward = a->reward; ka.p.illegal_move_reward = a->illegal_move_reward;
-    ka.p.seed = a->seed; ka.p.step = a->step; ka.p.env_id0 = a->env_id0;
+    ka.p.seed = a->seed; ka.p.step = a->step; ka.p.env_id0 = a->env_id0; ka.p.rk = make_round_keys(a->seed);
     ka.p.agent_random = a->agent_random != 0; ka.p.autoreset = a->autoreset != 0;
     cudaStream_t st = (cudaStream_t)stream;
     const unsigned grid = blocks_for(a->n);
     const bool need_smem = a->obs_board || a->term_board;
-#define LAUNCH_STEP(C)                                                                               \
+    if (a->term_count && !a->term_index) return EWN_EARG;
+    const bool vec = a->action_i64 && a->reward_f32 && a->terminated && a->truncated && a->obs_board && a->obs_dice && !a->reward_f64 &&
+                     !a->code && !a->action_out && !a->agent_random && !replay && !a->shaped;
+#define LAUNCH_STEP(C, NT)                                                                           \
     do {                                                                                             \
         size_t sm = need_smem ? obs_smem<C>(ka.p.geo) : 0;                                           \
-        if (replay) { if (a->shaped) k_step<C, true, true><<<grid, TPB, sm, st>>>(ka); else k_step<C, true, false><<<grid, TPB, sm, st>>>(ka); } \
-        else        { if (a->shaped) k_step<C, false, true><<<grid, TPB, sm, st>>>(ka); else k_step<C, false, false><<<grid, TPB, sm, st>>>(ka); } \
+        if (vec) k_step<C, NT, false, false, true><<<grid, TPB, sm, st>>>(ka);                       \
+        else if (replay) { if (a->shaped) k_step<C, NT, true, true, false><<<grid, TPB, sm, st>>>(ka); else k_step<C, NT, true, false, false><<<grid, TPB, sm, st>>>(ka); } \
+        else        { if (a->shaped) k_step<C, NT, false, true, false><<<grid, TPB, sm, st>>>(ka); else k_step<C, NT, false, false, false><<<grid, TPB, sm, st>>>(ka); } \
     } while (0)
-    if (use_p5(a->board_size)) LAUNCH_STEP(P5); else LAUNCH_STEP(P8);
+    const int N = a->board_size;
+    if (N == 5) LAUNCH_STEP(P5, 5); else if (use_p5(N)) LAUNCH_STEP(P5, 0); else if (N == 7) LAUNCH_STEP(P8, 7); else LAUNCH_STEP(P8, 0);
 #undef LAUNCH_STEP
     LAUNCHED("k_step");
     return EWN_OK;
@@ -807,7 +852,8 @@ struct ewn_vec {
     uint64_t* state;
     int64_t* action;
     int16_t* obs_board; int64_t* obs_dice; float* reward; uint8_t* done; uint8_t* trunc;
-    int16_t* term_board; int64_t* term_dice;
+    int16_t* term_board; int64_t* term_dice; int32_t* term_index; uint32_t* term_count;
+    uint32_t* count_host;          // page-locked landing slot for *term_count
     int32_t* tolerance; double* prev_score;
 };
 
@@ -816,7 +862,9 @@ static void vec_free(ewn_vec* v) {
     cudaSetDevice(v->cfg.device);
     for (int i = 0; i < v->n_streams; i++) if (v->streams[i]) cudaStreamDestroy(v->streams[i]);
     cudaFree(v->state); cudaFree(v->action); cudaFree(v->obs_board); cudaFree(v->obs_dice); cudaFree(v->reward);
-    cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->tolerance); cudaFree(v->prev_score);
+    cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->term_index); cudaFree(v->term_count);
+    if (v->count_host) cudaFreeHost(v->count_host);
+    cudaFree(v->tolerance); cudaFree(v->prev_score);
     delete v;
 }
 
@@ -845,6 +893,10 @@ int ewn_vec_create(const ewn_vec_config* cfg, ewn_vec** out) {
     VEC_TRY(cudaMalloc(&v->trunc, (size_t)n));
     VEC_TRY(cudaMalloc(&v->term_board, (size_t)n * NN * 2));
     VEC_TRY(cudaMalloc(&v->term_dice, (size_t)n * 8));
+    VEC_TRY(cudaMalloc(&v->term_index, (size_t)n * 4));
+    VEC_TRY(cudaMalloc(&v->term_count, 256));
+    VEC_TRY(cudaMemset(v->term_count, 0, 256));
+    VEC_TRY(cudaHostAlloc((void**)&v->count_host, 64, cudaHostAllocDefault));
     if (cfg->shaped) {
         VEC_TRY(cudaMalloc(&v->tolerance, (size_t)n * 4));
         VEC_TRY(cudaMalloc(&v->prev_score, (size_t)n * 8));
@@ -886,8 +938,9 @@ int ewn_vec_reset(ewn_vec* v, int16_t* obs_board, int64_t* obs_dice) {
 }
 
 int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t* obs_dice, float* reward, uint8_t* done, uint8_t* truncated,
-                 int16_t* term_board, int64_t* term_dice) {
+                 int16_t* term_board, int64_t* term_dice, int32_t* term_index, uint32_t* term_count) {
     if (!v || !action) return EWN_EARG;
+    if (term_count && !term_index) return EWN_EARG;
     CU(cudaSetDevice(v->cfg.device));
     const ewn_vec_config& c = v->cfg;
     const int NN = c.board_size * c.board_size;
@@ -905,8 +958,10 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
         a.action_i64 = v->action + 2 * lo;
         a.reward_f32 = v->reward + lo; a.terminated = v->done + lo; a.truncated = v->trunc + lo;
         a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
-        if (term_board) a.term_board = v->term_board + lo * NN;
-        if (term_dice) a.term_dice = v->term_dice + lo;
+        if (term_count) {               // compacted terminal observations, one list for all chunks
+            a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr;
+            a.term_index = v->term_index; a.term_count = v->term_count; a.term_index_base = lo;
+        }
         if (c.shaped) { a.tolerance = v->tolerance + lo; a.prev_score = v->prev_score + lo; a.shaped = 1; }
         a.reward = c.reward; a.illegal_move_reward = c.illegal_move_reward;
         a.seed = c.seed; a.step = v->step; a.env_id0 = c.env_id0 + (uint64_t)lo;
@@ -918,10 +973,23 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
         if (reward) CU(cudaMemcpyAsync(reward + lo, v->reward + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
         if (done) CU(cudaMemcpyAsync(done + lo, v->done + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
         if (truncated) CU(cudaMemcpyAsync(truncated + lo, v->trunc + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
-        if (term_board) CU(cudaMemcpyAsync(term_board + lo * NN, v->term_board + lo * NN, (size_t)m * NN * 2, cudaMemcpyDeviceToHost, st));
-        if (term_dice) CU(cudaMemcpyAsync(term_dice + lo, v->term_dice + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
     }
-    for (int i = 0; i < v->n_streams; i++) CU(cudaStreamSynchronize(v->streams[i]));
+    // every kernel has run once the first two streams drain their kernels; the count is final after all streams sync
+    for (int i = 1; i < v->n_streams; i++) CU(cudaStreamSynchronize(v->streams[i]));
+    cudaStream_t s0 = v->streams[0];
+    if (term_count) {
+        CU(cudaMemcpyAsync(v->count_host, v->term_count, 4, cudaMemcpyDeviceToHost, s0));
+        CU(cudaStreamSynchronize(s0));
+        const uint32_t cnt = *v->count_host;
+        *term_count = cnt;
+        if (cnt) {
+            if (term_board) CU(cudaMemcpyAsync(term_board, v->term_board, (size_t)cnt * NN * 2, cudaMemcpyDeviceToHost, s0));
+            if (term_dice) CU(cudaMemcpyAsync(term_dice, v->term_dice, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s0));
+            CU(cudaMemcpyAsync(term_index, v->term_index, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s0));
+        }
+        CU(cudaMemsetAsync(v->term_count, 0, 4, s0));
+    }
+    CU(cudaStreamSynchronize(s0));
     v->step++;
     return EWN_OK;
 }

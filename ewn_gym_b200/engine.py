@@ -220,6 +220,11 @@ class Engine:
         self._chk(self.lib.ewn_step(C.byref(a), xp.stream()), "ewn_step")
         return res
 
+    def step_plan(self, state, action=None, **kw):
+        """Pre-bind a step (pointers, sizes, flags) so that a rollout loop pays one ctypes call per launch:
+        ``plan = e.step_plan(state, action, out=...); plan.launch(step)``.  Same keywords as ``step``."""
+        return StepPlan(self, state, action, **kw)
+
     # ------------------------------------------------------------------ search
     def evaluate(self, state, heuristic="hybrid"):
         n = self._n(state)
@@ -260,3 +265,37 @@ class Engine:
         self._chk(self.lib.ewn_mc_best_action(self.xp.ptr(state), self.xp.ptr(wins), self.xp.ptr(a), n, self.N, self.L, self.xp.stream()),
                   "ewn_mc_best_action")
         return a
+
+
+class StepPlan:
+    """A bound ``ewn_step`` call: everything but the step index is fixed.  Keeps its tensors alive."""
+
+    def __init__(self, engine, state, action=None, **kw):
+        self.engine = engine
+        captured = {}
+        real = engine.lib.ewn_step
+
+        class _Capture:                      # record the argument block Engine.step builds instead of launching
+            def __getattr__(self_inner, name):
+                return getattr(engine.lib, name)
+
+            def ewn_step(self_inner, args_ref, stream):
+                captured["args"] = args_ref._obj
+                captured["stream"] = stream
+                return 0
+
+        lib, engine.lib = engine.lib, _Capture()
+        try:
+            self.out = engine.step(state, action, **kw)
+        finally:
+            engine.lib = lib
+        self.args, self.stream = captured["args"], captured["stream"]
+        self._keep = (state, action, kw)
+        self._fn, self._ref = real, C.byref(self.args)
+
+    def launch(self, step: int):
+        self.args.step = step
+        rc = self._fn(self._ref, self.stream)
+        if rc:
+            _lib.check(rc, "ewn_step", self.engine.lib)
+        return self.out

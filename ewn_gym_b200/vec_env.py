@@ -47,12 +47,23 @@ class _Pinned:
 class LazyInfos(Sequence):
     """``infos`` of VecEnv.step_wait without building n dicts per step: dict i is made when it is asked for."""
 
-    def __init__(self, env, done, trunc, reward, term_board, term_dice):
+    def __init__(self, env, done, trunc, reward, term_board, term_dice, term_index, term_count):
         self._env, self._done, self._trunc, self._reward = env, done, trunc, reward
-        self._tb, self._td = term_board, term_dice
+        self._tb, self._td, self._ti, self._tc = term_board, term_dice, term_index, term_count
+        self._order = None
 
     def __len__(self):
         return len(self._done)
+
+    def _row(self, i):
+        """row of env i in the compacted terminal-observation list"""
+        if self._order is None:
+            idx = self._ti[: self._tc]
+            self._order = np.argsort(idx, kind="stable")
+            self._sorted = idx[self._order]
+        k = int(np.searchsorted(self._sorted, i))
+        assert k < self._tc and self._sorted[k] == i
+        return int(self._order[k])
 
     def __getitem__(self, i):
         if isinstance(i, slice):
@@ -62,16 +73,14 @@ class LazyInfos(Sequence):
         if not self._done[i]:
             return {}
         r = float(self._reward[i])
-        R = self._env.reward
         if self._trunc[i]:
             code = CODE_AGENT_ILLEGAL if r < 0 else 3
         else:
             code = CODE_AGENT_WON if r > 0 else CODE_AGENT_LOST
-        if self._env.shaped and not self._trunc[i]:
-            code = CODE_AGENT_WON if r == R else CODE_AGENT_LOST
         info = {"message": MESSAGES[code], "TimeLimit.truncated": False}
         if self._tb is not None:
-            info["terminal_observation"] = {"board": self._tb[i].copy(), "dice_roll": int(self._td[i])}
+            k = self._row(i)
+            info["terminal_observation"] = {"board": self._tb[k].copy(), "dice_roll": int(self._td[k])}
         return info
 
 
@@ -109,6 +118,8 @@ class EWNVecEnv:
         if self._want_term:
             self._b["tboard"] = mk((n, N, N), np.int16)
             self._b["tdice"] = mk((n,), np.int64)
+            self._b["tindex"] = mk((n,), np.int32)
+            self._b["tcount"] = mk((16,), np.uint32)
         self._actions = None
         self.reset_infos = [{} for _ in range(min(n, 1))]
         self.render_mode = None
@@ -128,13 +139,16 @@ class EWNVecEnv:
 
     def step_wait(self):
         b = self._b
-        tb = b["tboard"].ptr if self._want_term else None
-        td = b["tdice"].ptr if self._want_term else None
+        T = self._want_term
         _lib.check(self.lib.ewn_vec_step(self._h, b["action"].ptr, b["board"].ptr, b["dice"].ptr, b["reward"].ptr, b["done"].ptr,
-                                         b["trunc"].ptr, tb, td), "ewn_vec_step", self.lib)
+                                         b["trunc"].ptr, b["tboard"].ptr if T else None, b["tdice"].ptr if T else None,
+                                         b["tindex"].ptr if T else None, b["tcount"].ptr if T else None), "ewn_vec_step", self.lib)
         done = b["done"].array.view(np.bool_)
-        infos = LazyInfos(self, done, b["trunc"].array, b["reward"].array,
-                          b["tboard"].array if self._want_term else None, b["tdice"].array if self._want_term else None)
+        if T:
+            infos = LazyInfos(self, done, b["trunc"].array, b["reward"].array, b["tboard"].array, b["tdice"].array, b["tindex"].array,
+                              int(b["tcount"].array[0]))
+        else:
+            infos = LazyInfos(self, done, b["trunc"].array, b["reward"].array, None, None, None, 0)
         return self._obs(), b["reward"].array, done, infos
 
     def step(self, actions):

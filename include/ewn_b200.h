@@ -127,6 +127,12 @@ typedef struct ewn_step_args {
     int64_t *obs_dice;            /* [n]                                                                        */
     int16_t *term_board;          /* [n][N][N] rows written only where terminated: info["terminal_observation"] */
     int64_t *term_dice;           /* [n]       likewise                                                         */
+    /* compacted terminal observations: when term_count != NULL, finished games append their terminal observation  */
+    /* at row k = atomicAdd(term_count) of term_board / term_dice and record their env index in term_index[k]     */
+    /* (k order is arbitrary; the caller zeroes *term_count).  With term_count == NULL the rows are dense.        */
+    uint32_t *term_count;         /* [1] device counter                                                         */
+    int32_t *term_index;          /* [n] term_index[k] = term_index_base + position of the game in this call    */
+    int64_t term_index_base;
     unsigned long long *stats;    /* [4] += {agent wins, agent losses, illegal-move endings, finished episodes}: the  */
                                   /*     counters that are all-reduced across GPUs (eval_random.py:101-108 win rate)   */
     /* MiniMaxHeuristicEnv state (required when shaped != 0), persists across resets: training_ewn.py:35-38     */
@@ -196,10 +202,11 @@ EWN_API int ewn_vec_create(const ewn_vec_config *cfg, ewn_vec **out);
 EWN_API void ewn_vec_destroy(ewn_vec *v);
 /* VecEnv.reset(): obs_board int16[n][N][N], obs_dice int64[n] (host) */
 EWN_API int ewn_vec_reset(ewn_vec *v, int16_t *obs_board, int64_t *obs_dice);
-/* VecEnv.step(actions int64[n][2]) with auto-reset. term_board/term_dice (host, may be NULL) receive the terminal
- * observation rows of finished games (all n rows are copied; only rows with done != 0 are meaningful). */
+/* VecEnv.step(actions int64[n][2]) with auto-reset.  Terminal observations of the finished games come back
+ * COMPACTED: *term_count rows in term_board / term_dice, row k belonging to env term_index[k] (all host pointers, each
+ * sized for n rows; pass term_count == NULL to skip terminal observations altogether). */
 EWN_API int ewn_vec_step(ewn_vec *v, const int64_t *action, int16_t *obs_board, int64_t *obs_dice, float *reward, uint8_t *done,
-                 uint8_t *truncated, int16_t *term_board, int64_t *term_dice);
+                 uint8_t *truncated, int16_t *term_board, int64_t *term_dice, int32_t *term_index, uint32_t *term_count);
 /* pinned host memory helpers so that callers can hand in page-locked numpy buffers */
 EWN_API int ewn_host_alloc(void **ptr, size_t bytes);
 EWN_API int ewn_host_free(void *ptr);

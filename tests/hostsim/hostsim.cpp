@@ -112,7 +112,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
     const bool replay = a.inject_dice_opp != nullptr;
     StepParams p; memset(&p, 0, sizeof(p));
     p.geo = geo; p.reward = a.reward; p.illegal_move_reward = a.illegal_move_reward;
-    p.seed = a.seed; p.step = a.step; p.env_id0 = a.env_id0;
+    p.seed = a.seed; p.step = a.step; p.env_id0 = a.env_id0; p.rk = make_round_keys(a.seed);
     p.agent_random = a.agent_random != 0; p.autoreset = a.autoreset != 0; p.shaped = a.shaped != 0; p.replay = replay;
     for (int64_t i = 0; i < a.n; i++) {
         Game<C> g, term; unpack(g, a.state, i); term = g;
