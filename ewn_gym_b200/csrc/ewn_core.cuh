@@ -33,34 +33,34 @@ typedef uint32_t u32;
 typedef uint64_t u64;
 
 // ------------------------------------------------------------------------------------------------
-// bit intrinsics (device instructions when compiled for the GPU)
+// bit intrinsics (device instructions when compiled for the GPU); ctz_nz / msb_nz return -1 for x == 0 on both sides
 // ------------------------------------------------------------------------------------------------
 EWN_HD int ctz_nz(u32 x) {
 #if defined(__CUDA_ARCH__)
     return __ffs((int)x) - 1;
 #else
-    return __builtin_ctz(x);
+    return x ? __builtin_ctz(x) : -1;
 #endif
 }
 EWN_HD int ctz_nz(u64 x) {
 #if defined(__CUDA_ARCH__)
     return __ffsll((long long)x) - 1;
 #else
-    return __builtin_ctzll(x);
+    return x ? __builtin_ctzll(x) : -1;
 #endif
 }
 EWN_HD int msb_nz(u32 x) {
 #if defined(__CUDA_ARCH__)
     return 31 - __clz((int)x);
 #else
-    return 31 - __builtin_clz(x);
+    return x ? 31 - __builtin_clz(x) : -1;
 #endif
 }
 EWN_HD int msb_nz(u64 x) {
 #if defined(__CUDA_ARCH__)
     return 63 - __clzll((long long)x);
 #else
-    return 63 - __builtin_clzll(x);
+    return x ? 63 - __builtin_clzll(x) : -1;
 #endif
 }
 EWN_HD int popc(u32 x) {
@@ -278,16 +278,17 @@ template <class C> EWN_HD bool tl_won(const Game<C>& g, const Geo& geo) {
 // Shifts (bit offsets of the cube's field) of the cubes the side may move with the current die.
 // envs/ewn.py:144-176 find_near_cube, :202-215 find_cube_to_move.
 struct Movers { int d, hi, lo; };   // d >= 0: the dice cube itself is alive; else hi / lo = nearest larger / smaller (or -1)
-template <class C> EWN_HD Movers movers(typename C::W side, int dice) {
+template <class C> EWN_HD Movers movers(typename C::W side, int dice) {      // branch-free: lanes of a warp do not diverge here
     typedef typename C::W W;
     W alive = C::dead(side) ^ C::ONES;
     int sh = C::FB * (dice - 1);
-    Movers m; m.d = -1; m.hi = -1; m.lo = -1;
-    if ((alive >> sh) & 1) { m.d = sh; return m; }
+    bool has = (alive >> sh) & 1;
     W above = alive & (~(W)0 << (sh + 1));
     W below = alive & (((W)1 << sh) - 1);
-    if (above) m.hi = ctz_nz(above);
-    if (below) m.lo = msb_nz(below);
+    Movers m;
+    m.d = has ? sh : -1;
+    m.hi = has ? -1 : ctz_nz(above);
+    m.lo = has ? -1 : msb_nz(below);
     return m;
 }
 // envs/ewn.py:178-215: the flag is only consulted when the dice cube is gone, and falls back to the other side
@@ -305,11 +306,15 @@ template <class C> EWN_HD int cell_at(typename C::W side, int sh) { return (int)
 struct Legal { int first, second, first_flag, sh_first, sh_second; };
 template <class C, int BR> EWN_HD Legal legal(const Game<C>& g, const Geo& geo, const Movers& m) {
     typename C::W side = BR ? g.br : g.tl;
-    Legal l; l.first = 0; l.second = 0; l.first_flag = 0; l.sh_first = -1; l.sh_second = -1;
-    if (m.d >= 0) { l.first = C::template dirs<BR>(geo, cell_at<C>(side, m.d)); l.sh_first = m.d; return l; }
-    l.first_flag = 1;
-    if (m.hi >= 0) { l.first = C::template dirs<BR>(geo, cell_at<C>(side, m.hi)); l.sh_first = m.hi; }
-    if (m.lo >= 0) { l.second = C::template dirs<BR>(geo, cell_at<C>(side, m.lo)); l.sh_second = m.lo; }
+    Legal l;
+    const bool has = m.d >= 0;
+    l.first_flag = has ? 0 : 1;
+    l.sh_first = has ? m.d : m.hi;
+    l.sh_second = m.lo;                                       // -1 when the dice cube is alive (movers)
+    const int fa = C::template dirs<BR>(geo, cell_at<C>(side, l.sh_first & (int)(8 * sizeof(typename C::W) - 1)));
+    const int fb = C::template dirs<BR>(geo, cell_at<C>(side, l.sh_second & (int)(8 * sizeof(typename C::W) - 1)));
+    l.first = l.sh_first >= 0 ? fa : 0;
+    l.second = l.sh_second >= 0 ? fb : 0;
     return l;
 }
 // 6-bit mask, bit = larger*3 + dir (the action id convention of alpha_zero/ewn/EWNLogic.py:328)

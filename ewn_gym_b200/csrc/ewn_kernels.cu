@@ -261,6 +261,11 @@ k_step(const __grid_constant__ StepKArgs ka) {
     const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool mine = i < n;
+    __shared__ unsigned s_cnt[4];                   // per-block episode counters: one global atomic per block and counter
+    if (a.stats) {
+        if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+    }
 
     Game<C> g, term;
     g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
@@ -303,43 +308,48 @@ k_step(const __grid_constant__ StepKArgs ka) {
         }
     }
     const int64_t warp_env0 = i - lane;
-    if (warp_env0 >= n) return;
-    Geo geo = ka.p.geo;
-    if (NT) geo.N = NT;
-    const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
-    if (a.stats && done) {                          // one atomic per warp and counter, only when non-zero
-        const unsigned won = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_WON);
-        const unsigned lost = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_LOST);
-        if (lane == 0) {
-            if (won) atomicAdd(a.stats + 0, (unsigned long long)__popc(won));
-            if (lost) atomicAdd(a.stats + 1, (unsigned long long)__popc(lost));
-            if (done & ~(won | lost)) atomicAdd(a.stats + 2, (unsigned long long)__popc(done & ~(won | lost)));
-            atomicAdd(a.stats + 3, (unsigned long long)__popc(done));
+    if (warp_env0 < n) {
+        Geo geo = ka.p.geo;
+        if (NT) geo.N = NT;
+        const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
+        if (a.stats && done) {
+            const unsigned won = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_WON);
+            const unsigned lost = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_LOST);
+            if (lane == 0) {
+                if (won) atomicAdd(&s_cnt[0], (unsigned)__popc(won));
+                if (lost) atomicAdd(&s_cnt[1], (unsigned)__popc(lost));
+                if (done & ~(won | lost)) atomicAdd(&s_cnt[2], (unsigned)__popc(done & ~(won | lost)));
+                atomicAdd(&s_cnt[3], (unsigned)__popc(done));
+            }
+        }
+        const int NN = geo.N * geo.N;
+        int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
+        if (VEC || a.obs_board) {
+            stage_rows<C, NT>(g, mine, geo, sm, lane);
+            write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
+        }
+        if (done && (a.term_board || a.term_dice || a.term_count)) {
+            const bool compact = a.term_count != nullptr;
+            int64_t row0 = warp_env0;
+            if (compact) {
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(a.term_count, (unsigned)__popc(done));
+                row0 = (int64_t)__shfl_sync(0xffffffffu, base, 0);
+            }
+            if (mine && out.term) {
+                const int64_t row = compact ? row0 + __popc(done & ((1u << lane) - 1u)) : i;
+                if (a.term_dice) a.term_dice[row] = term.dice;
+                if (compact && a.term_index) a.term_index[row] = (int32_t)(a.term_index_base + i);
+            }
+            if (a.term_board) {
+                stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
+                write_rows_sparse<C, NT>(a.term_board, row0, compact, done, geo, sm, lane);
+            }
         }
     }
-    const int NN = geo.N * geo.N;
-    int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
-    if (VEC || a.obs_board) {
-        stage_rows<C, NT>(g, mine, geo, sm, lane);
-        write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
-    }
-    if (done && (a.term_board || a.term_dice || a.term_count)) {
-        const bool compact = a.term_count != nullptr;
-        int64_t row0 = warp_env0;
-        if (compact) {
-            unsigned base = 0;
-            if (lane == 0) base = atomicAdd(a.term_count, (unsigned)__popc(done));
-            row0 = (int64_t)__shfl_sync(0xffffffffu, base, 0);
-        }
-        if (mine && out.term) {
-            const int64_t row = compact ? row0 + __popc(done & ((1u << lane) - 1u)) : i;
-            if (a.term_dice) a.term_dice[row] = term.dice;
-            if (compact && a.term_index) a.term_index[row] = (int32_t)(a.term_index_base + i);
-        }
-        if (a.term_board) {
-            stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
-            write_rows_sparse<C, NT>(a.term_board, row0, compact, done, geo, sm, lane);
-        }
+    if (a.stats) {
+        __syncthreads();
+        if (threadIdx.x < 4 && s_cnt[threadIdx.x]) atomicAdd(a.stats + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
     }
 }
 
@@ -424,7 +434,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64*
 template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* pair_state, const u32* pair_root, const u32* pair_child,
                                                                      const u32* pair_slot, const int* n_pairs_dev, int64_t n_pairs_host,
                                                                      u32 first, u32 count, u32* wins, unsigned long long* plies,
-                                                                     Geo geo, u64 seed) {
+                                                                     Geo geo, const RoundKeys rk) {
     const int lane = threadIdx.x & 31;
     const int64_t warp_id = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
     const int64_t n_warps = ((int64_t)gridDim.x * TPB) >> 5;
@@ -471,7 +481,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
         }
         if (busy) {
             u32 blk[4];
-            playout_block(seed, rid, child, pidx, j++, blk);
+            playout_block_rk(rk, rid, child, pidx, j++, blk);
             g.dice = 1 + (int)bounded(blk[0], 6u);
             bool over = random_ply<C, SIDE_BR>(g, geo, blk[1], nullptr, nullptr);
             my_plies++;
@@ -792,8 +802,8 @@ int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = playout_grid(n * (int64_t)count);
-    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, seed);
-    else           k_playouts<P8><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, seed);
+    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
+    else           k_playouts<P8><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
     LAUNCHED("k_playouts");
     return EWN_OK;
 }
@@ -823,8 +833,8 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     LAUNCHED("k_mc_expand");
     if (count == 0) return EWN_OK;
     const int grid = playout_grid(n * 6 * (int64_t)count);
-    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, seed);
-    else           k_playouts<P8><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, seed);
+    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
+    else           k_playouts<P8><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
     LAUNCHED("k_playouts");
     return EWN_OK;
 }
