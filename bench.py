@@ -173,11 +173,17 @@ def run_ours(args, rank, world, local_rank):
     stats = torch.zeros(4, dtype=torch.int64, device=dev)
     want = tuple(shapes)
 
-    for s_i, S in enumerate(sets):          # pre-bound launches: one ctypes call per step in the timed loop
-        S["plan"] = e.step_plan(S["state"], S["act"], seed=SEED + s_i, step=0, env_id0=env_id0, autoreset=True, stats=stats, want=want, out=S["out"])
+    # pre-bound launches (one ctypes call per step in the timed loop).  Terminal observations are appended compacted;
+    # each set alternates two append counters, the launch that uses one clears the other (no memset launches).
+    for s_i, S in enumerate(sets):
+        S["cnt"] = torch.zeros(2, dtype=torch.int32, device=dev)
+        S["tidx"] = torch.empty(n, dtype=torch.int32, device=dev)
+        S["plans"] = [e.step_plan(S["state"], S["act"], seed=SEED + s_i, step=0, env_id0=env_id0, autoreset=True, stats=stats, want=want,
+                                  out=S["out"], term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b])) for b in (0, 1)]
 
     def one_step(t):
-        sets[t % N_SETS]["plan"].launch(t // N_SETS + 1)
+        k = t // N_SETS
+        sets[t % N_SETS]["plans"][k & 1].launch(k + 1)
 
     t = 0
     for _ in range(max(args.warmup, 3)):

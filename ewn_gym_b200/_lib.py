@@ -29,7 +29,7 @@ class StepArgs(C.Structure):
         ("action_i64", p_void), ("action_i32", p_void), ("action_u8", p_void),
         ("reward_f32", p_void), ("reward_f64", p_void), ("terminated", p_void), ("truncated", p_void), ("code", p_void),
         ("action_out", p_void), ("obs_board", p_void), ("obs_dice", p_void), ("term_board", p_void), ("term_dice", p_void),
-        ("term_count", p_void), ("term_index", p_void), ("term_index_base", i64), ("stats", p_void),
+        ("term_count", p_void), ("term_index", p_void), ("term_index_base", i64), ("term_count_clear", p_void), ("stats", p_void),
         ("tolerance", p_void), ("prev_score", p_void),
         ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
         ("reward", C.c_double), ("illegal_move_reward", C.c_double),

@@ -115,6 +115,38 @@ template <class C, int NT> __device__ __forceinline__ void write_rows_sparse(int
     __syncwarp();
 }
 
+// compacted terminal observations: the finished lanes of a warp own consecutive output rows row0 .. row0+cnt-1, so
+// they stage their boards back to back in shared memory and the warp writes one contiguous block
+template <class C, int NT> __device__ __forceinline__ void write_rows_compact(int16_t* out, int64_t row0, const Game<C>& g, bool fin,
+                                                                              unsigned done, const Geo& geo, int16_t* sm, int lane) {
+    const int NN = NT ? NT * NT : geo.N * geo.N;
+    const int cnt = __popc(done);
+    const int total = cnt * NN;                   // int16 elements
+    uint32_t* z = reinterpret_cast<uint32_t*>(sm);
+    for (int k = lane; k < (total + 1) / 2; k += 32) z[k] = 0u;
+    __syncwarp();
+    if (fin) {
+        int16_t* row = sm + __popc(done & ((1u << lane) - 1u)) * NN;
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            int c = (int)((g.tl >> (C::FB * k)) & C::FM);
+            if (c != (int)C::FM) row[lin_cell<C, NT>(geo, c)] = (int16_t)(k + 1);
+            int d = (int)((g.br >> (C::FB * k)) & C::FM);
+            if (d != (int)C::FM) row[lin_cell<C, NT>(geo, d)] = (int16_t)(-(k + 1));
+        }
+    }
+    __syncwarp();
+    int16_t* dst = out + row0 * NN;
+    if ((reinterpret_cast<uintptr_t>(dst) & 3) == 0) {          // 4-byte stores when the block starts on a word
+        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+        for (int k = lane; k < total / 2; k += 32) d4[k] = z[k];
+        if ((total & 1) && lane == 0) dst[total - 1] = sm[total - 1];
+    } else {
+        for (int k = lane; k < total; k += 32) dst[k] = sm[k];
+    }
+    __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------------
 // K0 codec
 // ------------------------------------------------------------------------------------------------
@@ -261,6 +293,7 @@ k_step(const __grid_constant__ StepKArgs ka) {
     const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool mine = i < n;
+    if (a.term_count_clear && i == 0) *a.term_count_clear = 0u;
     __shared__ unsigned s_cnt[4];                   // per-block episode counters: one global atomic per block and counter
     if (a.stats) {
         if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
@@ -342,8 +375,11 @@ k_step(const __grid_constant__ StepKArgs ka) {
                 if (compact && a.term_index) a.term_index[row] = (int32_t)(a.term_index_base + i);
             }
             if (a.term_board) {
-                stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
-                write_rows_sparse<C, NT>(a.term_board, row0, compact, done, geo, sm, lane);
+                if (compact) write_rows_compact<C, NT>(a.term_board, row0, term, mine && out.term, done, geo, sm, lane);
+                else {
+                    stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
+                    write_rows_sparse<C, NT>(a.term_board, row0, false, done, geo, sm, lane);
+                }
             }
         }
     }
@@ -970,7 +1006,8 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
         a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
         if (term_count) {               // compacted terminal observations, one list for all chunks
             a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr;
-            a.term_index = v->term_index; a.term_count = v->term_count; a.term_index_base = lo;
+            a.term_index = v->term_index; a.term_count = v->term_count + (v->step & 1); a.term_index_base = lo;
+            if (lo == 0) a.term_count_clear = v->term_count + ((v->step + 1) & 1);
         }
         if (c.shaped) { a.tolerance = v->tolerance + lo; a.prev_score = v->prev_score + lo; a.shaped = 1; }
         a.reward = c.reward; a.illegal_move_reward = c.illegal_move_reward;
@@ -988,7 +1025,7 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
     for (int i = 1; i < v->n_streams; i++) CU(cudaStreamSynchronize(v->streams[i]));
     cudaStream_t s0 = v->streams[0];
     if (term_count) {
-        CU(cudaMemcpyAsync(v->count_host, v->term_count, 4, cudaMemcpyDeviceToHost, s0));
+        CU(cudaMemcpyAsync(v->count_host, v->term_count + (v->step & 1), 4, cudaMemcpyDeviceToHost, s0));
         CU(cudaStreamSynchronize(s0));
         const uint32_t cnt = *v->count_host;
         *term_count = cnt;
@@ -997,7 +1034,6 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
             if (term_dice) CU(cudaMemcpyAsync(term_dice, v->term_dice, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s0));
             CU(cudaMemcpyAsync(term_index, v->term_index, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s0));
         }
-        CU(cudaMemsetAsync(v->term_count, 0, 4, s0));
     }
     CU(cudaStreamSynchronize(s0));
     v->step++;

@@ -168,12 +168,13 @@ class Engine:
 
     # ------------------------------------------------------------------ env step
     def step(self, state, action=None, *, seed=0, step=0, env_id0=0, reward=1.0, agent_random=False, autoreset=True,
-             shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None, stats=None,
+             shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None, stats=None, term_compact=None,
              want=("reward_f32", "terminated", "truncated"), out: Optional[dict] = None):
         """One env step for every game (envs/ewn.py:436-486), in place on `state`.
 
         action : int64[n,2] / int32[n,2] / uint8[n] tensor, or None with agent_random.
         inject : (dice_opp i32[n], opp_action i32[n,2], dice_next i32[n]) for replay mode.
+        term_compact : (count int32[1], index int32[n]) -> terminal observations are appended compacted (see ewn_b200.h).
         stats  : int64[4] accumulator {agent wins, agent losses, illegal-move endings, finished episodes}.
         want   : names of ewn_step_args outputs to allocate; `out` may carry pre-allocated ones.
         Returns the dict of output tensors.
@@ -208,6 +209,10 @@ class Engine:
                 setattr(a, name, xp.ptr(res[name]))
         if stats is not None:
             a.stats = xp.ptr(stats)
+        if term_compact is not None:               # (count int32[1] zeroed by the caller, index int32[n])
+            a.term_count, a.term_index = xp.ptr(term_compact[0]), xp.ptr(term_compact[1])
+            if len(term_compact) > 2:              # counter to clear for the next step
+                a.term_count_clear = xp.ptr(term_compact[2])
         if shaped:
             a.tolerance, a.prev_score = xp.ptr(tolerance), xp.ptr(prev_score)
         if inject is not None:

@@ -133,6 +133,8 @@ typedef struct ewn_step_args {
     uint32_t *term_count;         /* [1] device counter                                                         */
     int32_t *term_index;          /* [n] term_index[k] = term_index_base + position of the game in this call    */
     int64_t term_index_base;
+    uint32_t *term_count_clear;   /* [1] optional: set to 0 by this launch -- the counter the NEXT step will append to,   */
+                                  /*     so that a rollout loop alternates two counters and never launches a memset      */
     unsigned long long *stats;    /* [4] += {agent wins, agent losses, illegal-move endings, finished episodes}: the  */
                                   /*     counters that are all-reduced across GPUs (eval_random.py:101-108 win rate)   */
     /* MiniMaxHeuristicEnv state (required when shaped != 0), persists across resets: training_ewn.py:35-38     */

@@ -114,6 +114,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
     p.geo = geo; p.reward = a.reward; p.illegal_move_reward = a.illegal_move_reward;
     p.seed = a.seed; p.step = a.step; p.env_id0 = a.env_id0; p.rk = make_round_keys(a.seed);
     p.agent_random = a.agent_random != 0; p.autoreset = a.autoreset != 0; p.shaped = a.shaped != 0; p.replay = replay;
+    if (a.term_count_clear) *a.term_count_clear = 0u;
     for (int64_t i = 0; i < a.n; i++) {
         Game<C> g, term; unpack(g, a.state, i); term = g;
         int al = 0, ad = 0;
@@ -143,8 +144,10 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
             a.stats[3]++;
         }
         if (out.term) {
-            if (a.term_dice) a.term_dice[i] = term.dice;
-            if (a.term_board) decode_one<C>(term, geo, a.term_board + i * NN);
+            int64_t row = i;
+            if (a.term_count) { row = (*a.term_count)++; a.term_index[row] = (int32_t)(a.term_index_base + i); }
+            if (a.term_dice) a.term_dice[row] = term.dice;
+            if (a.term_board) decode_one<C>(term, geo, a.term_board + row * NN);
         }
     }
     return EWN_OK;

@@ -163,6 +163,7 @@ def test_step_philox_vs_oracle(backend, N, L, agent_random):
     stats = e.xp.zeros((4,), "i64")
     for t in range(1, 41):
         act = None if agent_random else np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+        prev_state = to_np(state).copy()
         out = e.step(state, None if act is None else e.xp.asarray(act, "i64"), seed=seed, step=t, env_id0=env_id0, agent_random=agent_random,
                      autoreset=True, stats=stats, want=("reward_f32", "reward_f64", "terminated", "truncated", "code", "action_out", "obs_board",
                                            "obs_dice", "term_board", "term_dice"))
@@ -179,6 +180,18 @@ def test_step_philox_vs_oracle(backend, N, L, agent_random):
             assert np.array_equal(np.stack([ao // 3, ao % 3], 1), ref["agent_action"])
         b2, d2 = e.decode(state)                                     # the stored state is what the observation shows
         assert np.array_equal(to_np(b2), ref["board"]) and np.array_equal(to_np(d2), ref["dice"])
+        if t % 4 == 0:                                               # compacted terminal observations: same rows, any order
+            s3 = e.xp.asarray(prev_state, "u64")
+            cnt, tidx = e.xp.zeros((1,), "i32"), e.xp.zeros((n,), "i32")
+            o3 = e.step(s3, None if act is None else e.xp.asarray(act, "i64"), seed=seed, step=t, env_id0=env_id0, agent_random=agent_random,
+                        autoreset=True, term_compact=(cnt, tidx), want=("term_board", "term_dice"))
+            k = int(to_np(cnt)[0])
+            assert k == int(done.sum())
+            order = np.argsort(to_np(tidx)[:k])
+            assert np.array_equal(to_np(tidx)[:k][order], np.flatnonzero(done))
+            assert np.array_equal(to_np(o3["term_board"])[:k][order], ref["term_board"][done])
+            assert np.array_equal(to_np(o3["term_dice"])[:k][order], ref["term_dice"][done])
+            assert np.array_equal(to_np(s3), to_np(state))
         ob, od = ref["board"], ref["dice"]
         wins += int((ref["code"] == O.CODE_AGENT_WON).sum()); losses += int((ref["code"] == O.CODE_AGENT_LOST).sum())
         illegal += int((ref["code"] == O.CODE_AGENT_ILLEGAL).sum())
