@@ -16,7 +16,7 @@ HEURISTICS = {"hybrid": 0, "min_dist": 1, "two_min_dist": 2, "attk": 3}
 TOP_LEFT, BOTTOM_RIGHT = 1, 2
 CODE_ONGOING, CODE_AGENT_ILLEGAL, CODE_AGENT_WON, CODE_OPP_ILLEGAL, CODE_AGENT_LOST, CODE_ILLEGAL_TOLERATED = range(6)
 MESSAGES = {  # info["message"] strings of envs/ewn.py:448,454,473,478
-    CODE_AGENT_ILLEGAL: "Illegal move!", CODE_AGENT_WON: "You won!", CODE_OPP_ILLEGAL: "Opponent illegal move!",
+    CODE_AGENT_ILLEGAL: "Invalid move for player! End the game.", CODE_AGENT_WON: "You won!", CODE_OPP_ILLEGAL: "Invalid move for opponent! End the game.",
     CODE_AGENT_LOST: "You lost!",
 }
 

@@ -48,9 +48,9 @@ extern "C" {
 
 /* step result codes (info["message"] of envs/ewn.py:448,454,473,478 and training_ewn.py:56) */
 #define EWN_CODE_ONGOING 0
-#define EWN_CODE_AGENT_ILLEGAL 1      /* "Illegal move!"            reward -R, terminated, truncated */
+#define EWN_CODE_AGENT_ILLEGAL 1      /* "Invalid move for player! End the game."    reward -R, terminated, truncated */
 #define EWN_CODE_AGENT_WON 2          /* "You won!"                 reward +R, terminated            */
-#define EWN_CODE_OPP_ILLEGAL 3        /* "Opponent illegal move!"   reward 0,  terminated, truncated */
+#define EWN_CODE_OPP_ILLEGAL 3        /* "Invalid move for opponent! End the game."  reward 0,  terminated, truncated */
 #define EWN_CODE_AGENT_LOST 4         /* "You lost!"                reward -R, terminated            */
 #define EWN_CODE_ILLEGAL_TOLERATED 5  /* training_ewn.py:48-56      reward illegal_move_reward, state unchanged */
 

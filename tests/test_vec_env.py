@@ -35,7 +35,7 @@ def test_vec_env_matches_oracle(N, L, shaped):
             assert np.array_equal(info["terminal_observation"]["board"], ref["term_board"][i])
             assert info["terminal_observation"]["dice_roll"] == ref["term_dice"][i]
             assert info["TimeLimit.truncated"] is False
-            want = {O.CODE_AGENT_ILLEGAL: "Illegal move!", O.CODE_AGENT_WON: "You won!", O.CODE_AGENT_LOST: "You lost!"}[int(ref["code"][i])]
+            want = {O.CODE_AGENT_ILLEGAL: "Invalid move for player! End the game.", O.CODE_AGENT_WON: "You won!", O.CODE_AGENT_LOST: "You lost!"}[int(ref["code"][i])]
             assert info["message"] == want
         for i in np.flatnonzero(~done)[:5]:
             assert infos[int(i)] == {}
