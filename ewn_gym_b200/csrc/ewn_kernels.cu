@@ -115,38 +115,6 @@ template <class C, int NT> __device__ __forceinline__ void write_rows_sparse(int
     __syncwarp();
 }
 
-// compacted terminal observations: the finished lanes of a warp own consecutive output rows row0 .. row0+cnt-1, so
-// they stage their boards back to back in shared memory and the warp writes one contiguous block
-template <class C, int NT> __device__ __forceinline__ void write_rows_compact(int16_t* out, int64_t row0, const Game<C>& g, bool fin,
-                                                                              unsigned done, const Geo& geo, int16_t* sm, int lane) {
-    const int NN = NT ? NT * NT : geo.N * geo.N;
-    const int cnt = __popc(done);
-    const int total = cnt * NN;                   // int16 elements
-    uint32_t* z = reinterpret_cast<uint32_t*>(sm);
-    for (int k = lane; k < (total + 1) / 2; k += 32) z[k] = 0u;
-    __syncwarp();
-    if (fin) {
-        int16_t* row = sm + __popc(done & ((1u << lane) - 1u)) * NN;
-#pragma unroll
-        for (int k = 0; k < 6; k++) {
-            int c = (int)((g.tl >> (C::FB * k)) & C::FM);
-            if (c != (int)C::FM) row[lin_cell<C, NT>(geo, c)] = (int16_t)(k + 1);
-            int d = (int)((g.br >> (C::FB * k)) & C::FM);
-            if (d != (int)C::FM) row[lin_cell<C, NT>(geo, d)] = (int16_t)(-(k + 1));
-        }
-    }
-    __syncwarp();
-    int16_t* dst = out + row0 * NN;
-    if ((reinterpret_cast<uintptr_t>(dst) & 3) == 0) {          // 4-byte stores when the block starts on a word
-        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
-        for (int k = lane; k < total / 2; k += 32) d4[k] = z[k];
-        if ((total & 1) && lane == 0) dst[total - 1] = sm[total - 1];
-    } else {
-        for (int k = lane; k < total; k += 32) dst[k] = sm[k];
-    }
-    __syncwarp();
-}
-
 // ------------------------------------------------------------------------------------------------
 // K0 codec
 // ------------------------------------------------------------------------------------------------
@@ -285,19 +253,30 @@ struct StepKArgs {
 
 // VEC = the VecEnv surface and nothing else (int64 actions in; f32 reward, terminated, truncated, int16 board and int64
 // dice out; Philox dice, random opponent): every optional-pointer test below folds away at compile time.
-template <class C, int NT, bool REPLAY, bool SHAPED, bool VEC> __global__ void __launch_bounds__(TPB)
+//
+// Finished games are handled at BLOCK level: warps append the packed terminal states of their finished lanes to a shared
+// list (one shared-memory atomic per warp, which also carries the won / lost tallies), the block reserves F consecutive
+// rows of the compacted terminal-observation arrays with ONE global atomic, and then all threads decode the F boards
+// together, one (game, cube) pair per thread -- no lane sits idle while a few lanes of its warp write boards.
+constexpr int STPB = 128;                // threads per block of k_step: small blocks keep the tail of the last wave short
+constexpr int SWARPS = STPB / 32;
+
+template <class C, int NT, bool REPLAY, bool SHAPED, bool VEC> __global__ void __launch_bounds__(STPB)
 k_step(const __grid_constant__ StepKArgs ka) {
     extern __shared__ uint4 smem_raw[];
+    __shared__ unsigned s_tot, s_row0;                          // s_tot = finished | won << 10 | lost << 20 of this block
+    __shared__ __align__(16) u64 s_term[STPB * C::WORDS];       // packed terminal states of the finished games
+    __shared__ unsigned char s_who[STPB];                       // ... and the thread that owns each of them
     const ewn_step_args& a = ka.a;
     const int64_t n = a.n;
-    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned tid = threadIdx.x;
+    const int64_t i = (int64_t)blockIdx.x * STPB + tid;
+    const int lane = tid & 31, warp = tid >> 5;
     const bool mine = i < n;
-    if (a.term_count_clear && i == 0) *a.term_count_clear = 0u;
-    __shared__ unsigned s_cnt[4];                   // per-block episode counters: one global atomic per block and counter
-    if (a.stats) {
-        if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
-        __syncthreads();
+    const bool compact = a.term_count != nullptr;
+    if (tid == 0) {
+        s_tot = 0;
+        if (a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
     }
 
     Game<C> g, term;
@@ -340,52 +319,95 @@ k_step(const __grid_constant__ StepKArgs ka) {
             if (a.obs_dice) a.obs_dice[i] = g.dice;
         }
     }
+    Geo geo = ka.p.geo;
+    if (NT) geo.N = NT;
+    const int NN = geo.N * geo.N;
+    int16_t* const smb = reinterpret_cast<int16_t*>(smem_raw);
     const int64_t warp_env0 = i - lane;
-    if (warp_env0 < n) {
-        Geo geo = ka.p.geo;
-        if (NT) geo.N = NT;
-        const unsigned done = __ballot_sync(0xffffffffu, mine && out.term);
-        if (a.stats && done) {
-            const unsigned won = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_WON);
-            const unsigned lost = __ballot_sync(0xffffffffu, mine && out.term && out.code == CODE_AGENT_LOST);
-            if (lane == 0) {
-                if (won) atomicAdd(&s_cnt[0], (unsigned)__popc(won));
-                if (lost) atomicAdd(&s_cnt[1], (unsigned)__popc(lost));
-                if (done & ~(won | lost)) atomicAdd(&s_cnt[2], (unsigned)__popc(done & ~(won | lost)));
-                atomicAdd(&s_cnt[3], (unsigned)__popc(done));
-            }
-        }
-        const int NN = geo.N * geo.N;
-        int16_t* sm = reinterpret_cast<int16_t*>(smem_raw) + warp * 32 * NN;
-        if (VEC || a.obs_board) {
-            stage_rows<C, NT>(g, mine, geo, sm, lane);
-            write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
-        }
-        if (done && (a.term_board || a.term_dice || a.term_count)) {
-            const bool compact = a.term_count != nullptr;
-            int64_t row0 = warp_env0;
-            if (compact) {
-                unsigned base = 0;
-                if (lane == 0) base = atomicAdd(a.term_count, (unsigned)__popc(done));
-                row0 = (int64_t)__shfl_sync(0xffffffffu, base, 0);
-            }
-            if (mine && out.term) {
-                const int64_t row = compact ? row0 + __popc(done & ((1u << lane) - 1u)) : i;
-                if (a.term_dice) a.term_dice[row] = term.dice;
-                if (compact && a.term_index) a.term_index[row] = (int32_t)(a.term_index_base + i);
-            }
+    const bool fin = mine && out.term;
+    if ((VEC || a.obs_board) && warp_env0 < n) {                 // observation after the step: warp-level staging
+        int16_t* sm = smb + warp * 32 * NN;
+        stage_rows<C, NT>(g, mine, geo, sm, lane);
+        write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
+    }
+    if (!compact && (a.term_board || a.term_dice)) {             // dense terminal rows (row = env index), warp-level
+        const unsigned done = __ballot_sync(0xffffffffu, fin);
+        if (done) {
+            if (fin && a.term_dice) a.term_dice[i] = term.dice;
             if (a.term_board) {
-                if (compact) write_rows_compact<C, NT>(a.term_board, row0, term, mine && out.term, done, geo, sm, lane);
-                else {
-                    stage_rows<C, NT>(term, mine && out.term, geo, sm, lane);
-                    write_rows_sparse<C, NT>(a.term_board, row0, false, done, geo, sm, lane);
+                int16_t* sm = smb + warp * 32 * NN;
+                stage_rows<C, NT>(term, fin, geo, sm, lane);
+                write_rows_sparse<C, NT>(a.term_board, warp_env0, false, done, geo, sm, lane);
+            }
+        }
+    }
+    if (!(a.stats || compact)) return;                            // uniform over the grid
+
+    __syncthreads();                                              // s_tot is zero; the staging area is free again
+    {
+        const unsigned done = __ballot_sync(0xffffffffu, fin);
+        if (done) {
+            const unsigned won = __ballot_sync(0xffffffffu, fin && out.code == CODE_AGENT_WON);
+            const unsigned lost = __ballot_sync(0xffffffffu, fin && out.code == CODE_AGENT_LOST);
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&s_tot, (unsigned)__popc(done) | ((unsigned)__popc(won) << 10) | ((unsigned)__popc(lost) << 20));
+            if (compact) {
+                base = __shfl_sync(0xffffffffu, base, 0) & 1023u;
+                if (fin) {
+                    const unsigned k = base + (unsigned)__popc(done & ((1u << lane) - 1u));
+                    pack(term, s_term, (long)k);
+                    s_who[k] = (unsigned char)tid;
                 }
             }
         }
     }
-    if (a.stats) {
-        __syncthreads();
-        if (threadIdx.x < 4 && s_cnt[threadIdx.x]) atomicAdd(a.stats + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+    __syncthreads();
+    const unsigned tot = s_tot;
+    const int F = (int)(tot & 1023u);
+    if (F == 0) return;                                           // uniform over the block
+    if (a.stats && tid < 4) {
+        const unsigned w = (tot >> 10) & 1023u, l = tot >> 20;
+        const unsigned v = tid == 0 ? w : tid == 1 ? l : tid == 2 ? (unsigned)F - w - l : (unsigned)F;
+        if (v) atomicAdd(a.stats + tid, (unsigned long long)v);
+    }
+    if (!compact) return;
+    if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+    const bool boards = a.term_board != nullptr;
+    if (boards) {                                                 // rows are staged at the 16-byte phase of their destination
+        uint4* v = reinterpret_cast<uint4*>(smb);
+        const int nvec = (F * NN + 14) >> 3;
+        for (int k = tid; k < nvec; k += STPB) v[k] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    const int64_t row0 = (int64_t)s_row0;
+    if ((int)tid < F) {
+        Game<C> t; unpack(t, s_term, (long)tid);
+        if (a.term_dice) __stcs(reinterpret_cast<long long*>(a.term_dice) + row0 + tid, (long long)t.dice);
+        __stcs(a.term_index + row0 + tid, (int32_t)(a.term_index_base + (int64_t)blockIdx.x * STPB + s_who[tid]));
+    }
+    if (!boards) return;
+    const int head = (int)(((unsigned)row0 * (unsigned)NN) & 7u);
+    for (int p = tid; p < F * 12; p += STPB) {                    // one (finished game, cube) pair per thread
+        const int r = (int)__umulhi((unsigned)p, 0x15555556u);    // p / 12
+        const int k = p - 12 * r;
+        const int br = k >= 6, kk = br ? k - 6 : k;
+        const typename C::W side = (typename C::W)(C::WORDS == 1 ? (br ? s_term[r] >> 32 : s_term[r]) : s_term[2 * r + br]);
+        const int c = (int)((side >> (C::FB * kk)) & C::FM);
+        if (c != (int)C::FM) smb[head + r * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(br ? -(kk + 1) : kk + 1);
+    }
+    __syncthreads();
+    int16_t* const dst = a.term_board + row0 * NN - head;         // element `e` of the staging area goes to dst[e]
+    const int lo = head, hi = head + F * NN;
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        const int v0 = (lo + 7) >> 3, v1 = hi >> 3;               // full 16-byte vectors [v0, v1)
+        const uint4* sv = reinterpret_cast<const uint4*>(smb);
+        uint4* dv = reinterpret_cast<uint4*>(dst);
+        for (int k = v0 + tid; k < v1; k += STPB) __stcs(dv + k, sv[k]);
+        const int h1 = min(v0 << 3, hi), t0 = max(v1 << 3, h1);
+        if ((int)tid < 8) { const int e = lo + tid; if (e < h1) dst[e] = smb[e]; }
+        else if (tid < 16) { const int e = t0 + (tid - 8); if (e < hi) dst[e] = smb[e]; }
+    } else {
+        for (int e = lo + tid; e < hi; e += STPB) dst[e] = smb[e];
     }
 }
 
@@ -586,6 +608,8 @@ int sm_count() {
 }
 
 template <class C> size_t obs_smem(const Geo& geo) { return (size_t)WARPS * 32 * geo.N * geo.N * sizeof(int16_t); }
+// k_step: one staging row per thread + slack for the 16-byte phase of the compacted terminal rows
+inline size_t step_smem(const Geo& geo) { return (size_t)STPB * geo.N * geo.N * sizeof(int16_t) + 32; }
 
 #define DISPATCH(N, expr_p5, expr_p8) \
     do { if (use_p5(N)) { typedef P5 C; expr_p5; } else { typedef P8 C; expr_p8; } } while (0)
@@ -735,17 +759,17 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     ka.p.seed = a->seed; ka.p.step = a->step; ka.p.env_id0 = a->env_id0; ka.p.rk = make_round_keys(a->seed);
     ka.p.agent_random = a->agent_random != 0; ka.p.autoreset = a->autoreset != 0;
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned grid = blocks_for(a->n);
+    const unsigned grid = (unsigned)((a->n + STPB - 1) / STPB);
     const bool need_smem = a->obs_board || a->term_board;
     if (a->term_count && !a->term_index) return EWN_EARG;
     const bool vec = a->action_i64 && a->reward_f32 && a->terminated && a->truncated && a->obs_board && a->obs_dice && !a->reward_f64 &&
                      !a->code && !a->action_out && !a->agent_random && !replay && !a->shaped;
 #define LAUNCH_STEP(C, NT)                                                                           \
     do {                                                                                             \
-        size_t sm = need_smem ? obs_smem<C>(ka.p.geo) : 0;                                           \
-        if (vec) k_step<C, NT, false, false, true><<<grid, TPB, sm, st>>>(ka);                       \
-        else if (replay) { if (a->shaped) k_step<C, NT, true, true, false><<<grid, TPB, sm, st>>>(ka); else k_step<C, NT, true, false, false><<<grid, TPB, sm, st>>>(ka); } \
-        else        { if (a->shaped) k_step<C, NT, false, true, false><<<grid, TPB, sm, st>>>(ka); else k_step<C, NT, false, false, false><<<grid, TPB, sm, st>>>(ka); } \
+        size_t sm = need_smem ? step_smem(ka.p.geo) : 0;                                             \
+        if (vec) k_step<C, NT, false, false, true><<<grid, STPB, sm, st>>>(ka);                       \
+        else if (replay) { if (a->shaped) k_step<C, NT, true, true, false><<<grid, STPB, sm, st>>>(ka); else k_step<C, NT, true, false, false><<<grid, STPB, sm, st>>>(ka); } \
+        else        { if (a->shaped) k_step<C, NT, false, true, false><<<grid, STPB, sm, st>>>(ka); else k_step<C, NT, false, false, false><<<grid, STPB, sm, st>>>(ka); } \
     } while (0)
     const int N = a->board_size;
     if (N == 5) LAUNCH_STEP(P5, 5); else if (use_p5(N)) LAUNCH_STEP(P5, 0); else if (N == 7) LAUNCH_STEP(P8, 7); else LAUNCH_STEP(P8, 0);
