@@ -34,7 +34,7 @@ class StepArgs(C.Structure):
         ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
         ("reward", C.c_double), ("illegal_move_reward", C.c_double),
         ("seed", u64), ("step", u64), ("env_id0", u64),
-        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("reserved", i32),
+        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("flags", i32),
     ]
 
 

@@ -170,13 +170,13 @@ template <class C> struct Game {
     int player;    // SIDE_TL / SIDE_BR: side to move
 };
 
-EWN_HD void unpack(Game<P5>& g, const u64* p, long i) {
-    u64 v = p[i];
+EWN_HD void unpack_regs(Game<P5>& g, u64 v, u64) {     // from words already in registers (prefetching kernels)
     u32 lo = (u32)v, hi = (u32)(v >> 32);
     g.tl = lo & P5::ALL; g.br = hi & P5::ALL;
     g.dice = 1 + (int)((lo >> 30) | ((hi >> 28) & 4u));
     g.player = (int)(hi >> 31);
 }
+EWN_HD void unpack(Game<P5>& g, const u64* p, long i) { unpack_regs(g, p[i], 0); }
 EWN_HD u64 pack_word(const Game<P5>& g) {
     u32 d = (u32)(g.dice - 1);
     u32 lo = g.tl | ((d & 3u) << 30);
@@ -194,6 +194,7 @@ EWN_HD void pack_words(const Game<P8>& g, u64& w0, u64& w1) {
     w0 = g.tl | ((u64)(g.dice - 1) << 48);
     w1 = g.br | ((u64)g.player << 48);
 }
+EWN_HD void unpack_regs(Game<P8>& g, u64 w0, u64 w1) { unpack_words(g, w0, w1); }
 EWN_HD void unpack(Game<P8>& g, const u64* p, long i) {
 #if defined(__CUDA_ARCH__)
     ulonglong2 v = reinterpret_cast<const ulonglong2*>(p)[i];
@@ -358,7 +359,10 @@ template <class C, int BR> EWN_HD bool ply_action(Game<C>& g, const Geo& geo, in
     Movers m = movers<C>(side, g.dice);
     int sh = cube_to_move(m, larger == 1);
     sh_out = sh;
-    if (sh < 0 || dir < 0 || dir > 2) return false;
+    if (sh < 0) return false;
+    // envs/ewn.py:229-247: a direction outside {0,1,2} matches no branch, (x, y) stays put, the bounds test passes and the
+    // cube is put back where it stood -- a VALID no-op move (the action space never produces it; parity keeps it)
+    if ((unsigned)dir > 2u) { t_out = cell_at<C>(side, sh); return true; }
     int ok = C::template dirs<BR>(geo, cell_at<C>(side, sh));
     if (!((ok >> dir) & 1)) return false;
     t_out = apply_move<C, BR>(g, sh, dir);
@@ -528,15 +532,17 @@ struct StepOut {
 
 // g: in = state at the agent's turn; out = next state (after auto-reset when the episode ended).
 // term_state: the terminal state (valid when out.term).
-template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const StepParams& p, long i, int a_larger, int a_dir,
-                                        const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
-    const Geo& geo = p.geo;
+// `geo` and the three mode flags are passed beside `p` so that a kernel can specialise them at compile time while `p`
+// itself stays a read-only kernel parameter (constant bank): nothing of it is copied into registers or local memory.
+template <class C> EWN_HD void step_one_cfg(Game<C>& g, Game<C>& term_state, const StepParams& p, const Geo& geo, const int replay,
+                                            const int shaped, const int agent_random, long i, int a_larger, int a_dir,
+                                            const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
     u32 blk[4] = {0, 0, 0, 0};
-    if (!p.replay || p.agent_random) env_block_rk(p.rk, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
+    if (!replay || agent_random) env_block_rk(p.rk, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
     bool pre = full_win<C>(g, geo);        // stepping an already finished game keeps reporting a win (check_win is sticky)
     out.reward = 0.0; out.term = 0; out.trunc = 0; out.code = CODE_ONGOING;
     bool valid; int t = 0, sh = -1;
-    if (p.agent_random) {
+    if (agent_random) {
         Movers m = movers<C>(g.tl, g.dice);
         Legal l = legal<C, SIDE_TL>(g, geo, m);
         int cnt = legal_count(l);
@@ -550,7 +556,7 @@ template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const S
     }
     out.a_larger = a_larger; out.a_dir = a_dir;
     if (!valid) {
-        if (p.shaped) {                                                   // training_ewn.py:48-56
+        if (shaped) {                                                   // training_ewn.py:48-56
             int tol = *tolerance - 1; *tolerance = tol;
             if (tol <= 0) { out.reward = -p.reward; out.term = 1; out.trunc = 1; out.code = CODE_AGENT_ILLEGAL; }
             else { out.reward = p.illegal_move_reward; out.code = CODE_ILLEGAL_TOLERATED; }
@@ -559,9 +565,9 @@ template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const S
         out.reward = p.reward; out.term = 1; out.code = CODE_AGENT_WON;
     } else {
         g.player = SIDE_BR;                                               // :457-458
-        g.dice = p.replay ? inj.dice_opp : 1 + (int)bounded(blk[0], (u32)geo.cube_num);
+        g.dice = replay ? inj.dice_opp : 1 + (int)bounded(blk[0], (u32)geo.cube_num);
         bool ovalid; int ot = 0, osh;
-        if (p.replay) ovalid = ply_action<C, SIDE_BR>(g, geo, inj.o_larger, inj.o_dir, ot, osh);   // :461-467
+        if (replay) ovalid = ply_action<C, SIDE_BR>(g, geo, inj.o_larger, inj.o_dir, ot, osh);   // :461-467
         else {
             Movers m = movers<C>(g.br, g.dice);
             Legal l = legal<C, SIDE_BR>(g, geo, m);
@@ -577,8 +583,8 @@ template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const S
         else if (win_after<C, SIDE_BR>(g, geo, ot)) { out.reward = -p.reward; out.term = 1; out.code = CODE_AGENT_LOST; }   // :475-478
         else {
             g.player = SIDE_TL;                                           // :481-483
-            g.dice = p.replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num);
-            if (p.shaped) {                                               // training_ewn.py:94-96
+            g.dice = replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num);
+            if (shaped) {                                               // training_ewn.py:94-96
                 double s = evaluate<C>(g, geo, H_HYBRID);
                 out.reward = f64_sub(s, *prev_score); *prev_score = s;
             }
@@ -586,8 +592,13 @@ template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const S
     }
     if (out.term) {
         term_state = g;
-        if (p.autoreset) setup<C>(g, geo, p.replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num));
+        if (p.autoreset) setup<C>(g, geo, replay ? inj.dice_next : 1 + (int)bounded(blk[2], (u32)geo.cube_num));
     }
+}
+
+template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const StepParams& p, long i, int a_larger, int a_dir,
+                                        const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
+    step_one_cfg<C>(g, term_state, p, p.geo, p.replay, p.shaped, p.agent_random, i, a_larger, a_dir, inj, tolerance, prev_score, out);
 }
 
 // ------------------------------------------------------------------------------------------------

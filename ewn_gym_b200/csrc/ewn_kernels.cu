@@ -412,6 +412,198 @@ k_step(const __grid_constant__ StepKArgs ka) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// K1v  persistent VecEnv step.  Same arithmetic as k_step<.., VEC = true>, different schedule:
+//   * the grid is sized to the machine (sm_count x VMINB resident blocks); a block walks units of VTPB games with a
+//     grid stride and loads the NEXT unit's state and action before it computes the current one, so DRAM latency and
+//     the block-launch ramp are paid once per block instead of once per game;
+//   * observation rows are staged per warp (__syncwarp only) -- there is no block barrier inside the loop;
+//   * finished games are only APPENDED (packed state + env index) to a block-local shared list inside the loop, one
+//     shared atomic per warp; after the loop the block reserves its rows of the compacted terminal-observation arrays
+//     with ONE global atomic and all threads decode the boards together, one (game, cube) pair per thread.
+// ------------------------------------------------------------------------------------------------
+#ifndef EWN_VTPB
+#define EWN_VTPB 128
+#endif
+#ifndef EWN_VMINB
+#define EWN_VMINB 12
+#endif
+#ifndef EWN_VITER_MAX
+#define EWN_VITER_MAX 8
+#endif
+constexpr int VTPB = EWN_VTPB, VMINB = EWN_VMINB, VITER_MAX = EWN_VITER_MAX;
+
+// lane-private scatter of the twelve cubes into the lane's row of a zeroed [32][NN] int16 tile
+template <class C, int NT> __device__ __forceinline__ void scatter_row(const Game<C>& g, const Geo& geo, int16_t* sm, int lane) {
+    const int NN = NT ? NT * NT : geo.N * geo.N;
+    char* row = reinterpret_cast<char*>(sm) + lane * (2 * NN);
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        if (C::S == (NT ? NT : -1)) {                 // packed cell == row-major index (5x5): byte offset straight from the field
+            const u32 a = (u32)(k == 0 ? (g.tl << 1) : (g.tl >> (C::FB * k - 1))) & (2u * (u32)C::FM);
+            const u32 b = (u32)(k == 0 ? (g.br << 1) : (g.br >> (C::FB * k - 1))) & (2u * (u32)C::FM);
+            if (a != 2u * (u32)C::FM) *reinterpret_cast<int16_t*>(row + a) = (int16_t)(k + 1);
+            if (b != 2u * (u32)C::FM) *reinterpret_cast<int16_t*>(row + b) = (int16_t)(-(k + 1));
+        } else {
+            const int c = (int)((g.tl >> (C::FB * k)) & C::FM), d = (int)((g.br >> (C::FB * k)) & C::FM);
+            if (c != (int)C::FM) *reinterpret_cast<int16_t*>(row + 2 * lin_cell<C, NT>(geo, c)) = (int16_t)(k + 1);
+            if (d != (int)C::FM) *reinterpret_cast<int16_t*>(row + 2 * lin_cell<C, NT>(geo, d)) = (int16_t)(-(k + 1));
+        }
+    }
+}
+
+// asynchronous copy of one game's packed state and int64 action pair into the thread's 32-byte shared slot
+template <class C> __device__ __forceinline__ void prefetch_game(unsigned slot, const u64* state, const int64_t* action, int i) {
+    if (C::WORDS == 1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(slot), "l"(state + i) : "memory");
+    else               asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot), "l"(state + 2 * (size_t)i) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + 16u), "l"(action + 2 * (size_t)i) : "memory");
+}
+
+template <class C, int NT> __global__ void __launch_bounds__(VTPB, VMINB)
+k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
+    extern __shared__ uint4 smem_raw[];
+    __shared__ unsigned s_cnt, s_won, s_lost, s_row0;
+    __shared__ ulonglong2 s_pf[2 * VTPB];
+    const ewn_step_args& a = ka.a;
+    const int n = (int)a.n;                                        // the host keeps n below 2^31 on this path: 32-bit indices
+    const unsigned tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    const bool compact = a.term_count != nullptr;
+    const bool tally = compact || a.stats != nullptr;
+    Geo geo = ka.p.geo;
+    if (NT) { geo.N = NT; geo.corner = C::cell(NT - 1, NT - 1); }
+    const int NN = geo.N * geo.N;
+    int16_t* const smb = reinterpret_cast<int16_t*>(smem_raw);                       // [VTPB][NN] staging (+ 32 B slack)
+    u64* const s_term = reinterpret_cast<u64*>(reinterpret_cast<char*>(smem_raw) + (((size_t)VTPB * NN * 2 + 32 + 15) & ~(size_t)15));
+    u32* const s_who = reinterpret_cast<u32*>(s_term + (size_t)cap * C::WORDS);
+    if (tid == 0) {
+        s_cnt = 0; s_won = 0; s_lost = 0;
+        if (a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
+    }
+    __syncthreads();
+
+    const int n_units = (n + VTPB - 1) / VTPB;
+    int u = blockIdx.x;
+    int i = u * VTPB + tid;
+    bool mine = i < n;
+    // prefetch slot of this thread: state (8 / 16 B) + action (16 B), filled by cp.async while the previous unit is computed
+    const unsigned pf = (unsigned)__cvta_generic_to_shared(s_pf) + tid * 32u;
+    if (mine) prefetch_game<C>(pf, a.state, a.action_i64, i);
+    unsigned tally_c = 0;                                          // wins | losses << 16 of this thread
+    int16_t* const sm = smb + warp * 32 * NN;
+    while (u < n_units) {                                          // block-uniform
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        const ulonglong2 sw = s_pf[2 * tid];                        // own slot: no cross-thread hazard
+        const longlong2 act = reinterpret_cast<const longlong2*>(s_pf)[2 * tid + 1];
+        const int un = u + (int)gridDim.x, in = un * VTPB + (int)tid;
+        const bool mine_n = in < n;
+        if (mine_n) prefetch_game<C>(pf, a.state, a.action_i64, in);
+        Game<C> g, term;
+        g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
+        StepOut out; out.term = 0; out.code = CODE_ONGOING;
+        if (mine) {
+            unpack_regs(g, sw.x, sw.y);
+            const int al = (int)act.x, ad = (act.y < 0 || act.y > 2) ? 3 : (int)act.y;
+            StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
+            int tol = 0; double prev = 0.0;
+            step_one_cfg<C>(g, term, ka.p, geo, 0, 0, 0, i, al, ad, inj, &tol, &prev, out);
+            pack(g, a.state, i);
+            __stcs(a.reward_f32 + i, (float)out.reward);
+            __stcs(a.terminated + i, (uint8_t)out.term);
+            __stcs(a.truncated + i, (uint8_t)out.trunc);
+            __stcs(reinterpret_cast<long long*>(a.obs_dice) + i, (long long)g.dice);
+        }
+        if (tally) {                                               // finished games: append to the block's list
+            const bool fin = mine && out.term;
+            const unsigned done = __ballot_sync(0xffffffffu, fin);
+            if (done) {
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(&s_cnt, (unsigned)__popc(done));
+                if (compact) {
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (fin) {
+                        const unsigned k = base + (unsigned)__popc(done & ((1u << lane) - 1u));
+                        pack(term, s_term, (long)k);
+                        s_who[k] = (u32)i;
+                    }
+                }
+                if (fin) tally_c += (out.code == CODE_AGENT_WON ? 1u : 0u) + (out.code == CODE_AGENT_LOST ? 0x10000u : 0u);
+            }
+        }
+        const int warp_env0 = i - lane;
+        if (warp_env0 < n) {                                       // warp-uniform: observation rows of this warp's 32 games
+            uint4* v = reinterpret_cast<uint4*>(sm);
+            const int nvec = 4 * NN;
+            if (NT) {
+#pragma unroll
+                for (int k = 0; k < (4 * NT * NT + 31) / 32; k++) if (lane + 32 * k < nvec) v[lane + 32 * k] = make_uint4(0, 0, 0, 0);
+            } else {
+                for (int k = lane; k < nvec; k += 32) v[k] = make_uint4(0, 0, 0, 0);
+            }
+            __syncwarp();
+            if (mine) scatter_row<C, NT>(g, geo, sm, lane);
+            __syncwarp();
+            write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
+        }
+        u = un; i = in; mine = mine_n;
+    }
+    if (!tally) return;
+    if (a.stats) {
+        const unsigned wl = __reduce_add_sync(0xffffffffu, tally_c);          // <= 32 * VITER_MAX per half: no carry
+        if (lane == 0 && wl) { atomicAdd(&s_won, wl & 0xffffu); atomicAdd(&s_lost, wl >> 16); }
+    }
+    __syncthreads();
+    const int F = (int)s_cnt;
+    if (F == 0) return;                                            // uniform over the block
+    if (a.stats && tid < 4) {
+        const unsigned w = s_won, l = s_lost;
+        const unsigned v = tid == 0 ? w : tid == 1 ? l : tid == 2 ? (unsigned)F - w - l : (unsigned)F;
+        if (v) atomicAdd(a.stats + tid, (unsigned long long)v);
+    }
+    if (!compact) return;
+    if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+    __syncthreads();
+    const int64_t row0 = (int64_t)s_row0;
+    for (int r = tid; r < F; r += VTPB) {
+        Game<C> t; unpack(t, s_term, (long)r);
+        if (a.term_dice) __stcs(reinterpret_cast<long long*>(a.term_dice) + row0 + r, (long long)t.dice);
+        __stcs(a.term_index + row0 + r, (int32_t)(a.term_index_base + (int64_t)s_who[r]));
+    }
+    if (!a.term_board) return;
+    for (int r0 = 0; r0 < F; r0 += VTPB) {                         // VTPB rows per pass through the staging tile
+        const int Fc = min(VTPB, F - r0);
+        const int64_t rowc = row0 + r0;
+        const int head = (int)(((unsigned)rowc * (unsigned)NN) & 7u);   // 16-byte phase of the destination
+        uint4* v = reinterpret_cast<uint4*>(smb);
+        const int nvec = (head + Fc * NN + 7) >> 3;
+        for (int k = tid; k < nvec; k += VTPB) v[k] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        for (int q = tid; q < Fc * 12; q += VTPB) {                // one (finished game, cube) pair per thread
+            const int r = (int)__umulhi((unsigned)q, 0x15555556u);  // q / 12
+            const int k = q - 12 * r;
+            const int br = k >= 6, kk = br ? k - 6 : k;
+            const u64 wsel = C::WORDS == 1 ? (br ? s_term[r0 + r] >> 32 : s_term[r0 + r]) : s_term[2 * (r0 + r) + br];
+            const int c = (int)(((typename C::W)wsel >> (C::FB * kk)) & C::FM);
+            if (c != (int)C::FM) smb[head + r * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(br ? -(kk + 1) : kk + 1);
+        }
+        __syncthreads();
+        int16_t* const dst = a.term_board + rowc * NN - head;      // element e of the staging tile goes to dst[e]
+        const int lo = head, hi = head + Fc * NN;
+        if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+            const int v0 = (lo + 7) >> 3, v1 = hi >> 3;            // full 16-byte vectors [v0, v1)
+            const uint4* sv = reinterpret_cast<const uint4*>(smb);
+            uint4* dv = reinterpret_cast<uint4*>(dst);
+            for (int k = v0 + tid; k < v1; k += VTPB) __stcs(dv + k, sv[k]);
+            const int h1 = min(v0 << 3, hi), t0 = max(v1 << 3, h1);
+            if ((int)tid < 8) { const int e = lo + tid; if (e < h1) dst[e] = smb[e]; }
+            else if (tid < 16) { const int e = t0 + (tid - 8); if (e < hi) dst[e] = smb[e]; }
+        } else {
+            for (int e = lo + tid; e < hi; e += VTPB) dst[e] = smb[e];
+        }
+        if (r0 + VTPB < F) __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // evaluate
 // ------------------------------------------------------------------------------------------------
 template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* state, double* value, int64_t n, Geo geo, int heuristic) {
@@ -772,6 +964,23 @@ int ewn_step(const ewn_step_args* a, void* stream) {
         else        { if (a->shaped) k_step<C, NT, false, true, false><<<grid, STPB, sm, st>>>(ka); else k_step<C, NT, false, false, false><<<grid, STPB, sm, st>>>(ka); } \
     } while (0)
     const int N = a->board_size;
+    // the VecEnv surface with compacted (or no) terminal observations runs on the persistent kernel
+    if (vec && !(a->flags & EWN_STEP_BLOCK_KERNEL) && (a->term_count || (!a->term_board && !a->term_dice)) && a->n < ((int64_t)1 << 30)) {
+        const int64_t n_units = (a->n + VTPB - 1) / VTPB;
+        int64_t blocks = (int64_t)sm_count() * VMINB;
+        if (blocks > n_units) blocks = n_units;
+        if (blocks * VITER_MAX < n_units) blocks = (n_units + VITER_MAX - 1) / VITER_MAX;
+        const int iters = (int)((n_units + blocks - 1) / blocks);
+        const int cap = a->term_count ? iters * VTPB : 0;
+        const int words = use_p5(N) ? 1 : 2;
+        const size_t sm = (((size_t)VTPB * N * N * 2 + 32 + 15) & ~(size_t)15) + (size_t)cap * (8 * words + 4);
+        if (N == 5) k_vstep<P5, 5><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
+        else if (use_p5(N)) k_vstep<P5, 0><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
+        else if (N == 7) k_vstep<P8, 7><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
+        else k_vstep<P8, 0><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
+        LAUNCHED("k_vstep");
+        return EWN_OK;
+    }
     if (N == 5) LAUNCH_STEP(P5, 5); else if (use_p5(N)) LAUNCH_STEP(P5, 0); else if (N == 7) LAUNCH_STEP(P8, 7); else LAUNCH_STEP(P8, 0);
 #undef LAUNCH_STEP
     LAUNCHED("k_step");

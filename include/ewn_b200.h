@@ -150,8 +150,11 @@ typedef struct ewn_step_args {
     int32_t agent_random;         /* TOP_LEFT plays uniformly over its legal list inside the kernel             */
     int32_t autoreset;            /* SB3 VecEnv contract                                                        */
     int32_t shaped;               /* MiniMaxHeuristicEnv.step                                                   */
-    int32_t reserved;
+    int32_t flags;                /* EWN_STEP_* bits, 0 = defaults                                              */
 } ewn_step_args;
+
+/* flags: run the VecEnv surface on the one-block-per-128-games kernel instead of the persistent one (A/B measurements) */
+#define EWN_STEP_BLOCK_KERNEL 1
 
 EWN_API int ewn_step(const ewn_step_args *args, void *stream);
 

@@ -228,10 +228,16 @@ def test_action_dtypes_and_out_of_range(backend):
         out = e.step(st, e.xp.asarray(arr, dt), seed=4, step=1, want=("code",))
         res.append((to_np(st).copy(), to_np(out["code"]).copy()))
     assert all(np.array_equal(res[0][0], r[0]) and np.array_equal(res[0][1], r[1]) for r in res[1:])
-    st = e.reset(4, seed=4)
-    out = e.step(st, e.xp.asarray(np.array([[0, 3], [1, -1], [0, 7], [5, 1]], np.int64), "i64"), seed=4, step=1, want=("code",))
-    assert to_np(out["code"])[:3].tolist() == [O.CODE_AGENT_ILLEGAL] * 3      # outside MultiDiscrete([2,3]) => illegal move
-    assert to_np(out["code"])[3] != O.CODE_AGENT_ILLEGAL                      # larger flag: only `== 1` means larger (ewn.py:439)
+    # outside MultiDiscrete([2,3]): the reference's execute_move matches no direction branch, leaves the cube in place and
+    # reports a VALID move (envs/ewn.py:229-247); only `action[0] == 1` means larger (:439).  Same here, bit for bit.
+    odd = np.array([[0, 3], [1, -1], [0, 7], [5, 1], [1, 2], [0, -9]], np.int64)
+    st = e.reset(len(odd), seed=4)
+    b0, d0 = (to_np(x) for x in e.decode(st))
+    out = e.step(st, e.xp.asarray(odd, "i64"), seed=4, step=1, want=("code", "obs_board", "obs_dice"))
+    ref = O.step_philox(b0, d0, odd, 4, 1)
+    assert np.array_equal(to_np(out["code"]), ref["code"]) and np.array_equal(to_np(out["obs_board"]), ref["board"])
+    assert np.array_equal(to_np(out["obs_dice"]), ref["dice"])
+    assert O.CODE_AGENT_ILLEGAL not in to_np(out["code"])[[0, 1, 2, 5]].tolist()
 
 
 # --------------------------------------------------------------------------------------------------- config 5: shaped env

@@ -110,7 +110,10 @@ def test_helper_methods(backend):
     assert np.array_equal(env.board, before)
     # off-board move: state untouched, False (:262-263)
     env.reset(seed=1)
-    assert not env.execute_move(-1, 5) and env.update_position(4, 4, 2, -1) == (3, 3) and not env.is_within_board(5, 0)
+    b1 = env.board.copy()
+    assert env.update_position(4, 4, 2, -1) == (3, 3) and not env.is_within_board(5, 0)
+    # a direction outside {0,1,2} matches no branch of :229-247: the cube stays, the move counts as valid
+    assert env.execute_move(-1, 5) and np.array_equal(env.board, b1)
     # evaluate: fresh MiniMaxHeuristicEnv value of SURVEY 8c, terminal +-10
     assert env.evaluate() == -0.49999999999999994 and env.evaluate("attk") == -12.0
     w = env.simulate()
@@ -122,8 +125,16 @@ def test_step_illegal_and_opponents(backend):
     eng = make_engine(backend, 5, 3)
     env = EinsteinWuerfeltNichtEnv(engine=eng, reward=2.0)
     obs, _ = env.reset(seed=3)
-    obs, r, term, trunc, info = env.step(np.array([0, 7]))                   # direction out of range
-    assert (r, term, trunc) == (-2.0, True, True) and info["message"] == "Invalid move for player! End the game."
+    b0 = obs["board"].copy()
+    obs, r, term, trunc, info = env.step(np.array([0, 7]))                   # direction out of range: a valid no-op in the reference
+    assert (r, term, trunc) == (0, False, False) and (obs["board"] > 0).sum() == 6 and np.array_equal(obs["board"] * (obs["board"] > 0), b0 * (b0 > 0))
+    for _ in range(40):                                                        # walk right until a cube leaves the board (:445-448)
+        obs, r, term, trunc, info = env.step(np.array([0, 0]))
+        if term:
+            break
+    assert term and r in (2.0, -2.0)
+    if trunc:
+        assert r == -2.0 and info["message"] == "Invalid move for player! End the game."
     # minimax and Monte-Carlo opponents plug in through the same ctor keywords as the reference (envs/ewn.py:265-283)
     for pol, kw in ((ClassicalPolicy.minimax, dict(max_depth=2)), ("mcts", dict(num_simulations=4, num_env_copies=2))):
         env = EinsteinWuerfeltNichtEnv(engine=eng, opponent_policy=pol, **kw)

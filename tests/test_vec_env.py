@@ -58,3 +58,41 @@ def test_vec_env_surface():
     assert obs["board"].shape == (64, 5, 5) and rew.shape == (64,) and done.shape == (64,)
     assert env.env_is_wrapped(object) == [False] * 64 and env.get_attr("board_size") == [5] * 64
     env.close()
+
+
+@pytest.mark.parametrize("N,L,n", [(5, 3, 300_000 + 77), (7, 3, 260_000 + 5), (5, 3, 100), (4, 2, 4096)])
+def test_persistent_step_kernel_vs_block_kernel_and_oracle(N, L, n):
+    """k_vstep (persistent, prefetching, deferred terminal compaction) against k_step (one block per 128 games) on the
+    VecEnv surface, every output incl. the compacted terminal observations, several units per block; a slice against the oracle."""
+    import torch
+    from ewn_gym_b200.engine import Engine
+    e = Engine(N, L)
+    seed, env_id0 = 99, 1000
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    want = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice", "term_board", "term_dice")
+    sa, sb = e.reset(n, seed=seed, env_id0=env_id0), e.reset(n, seed=seed, env_id0=env_id0)
+    board0, dice0 = (x.cpu().numpy() for x in e.decode(sa))
+    m = min(n, 3000)
+    ob, od = board0[:m].copy(), dice0[:m].copy()
+    stats_a, stats_b = torch.zeros(4, dtype=torch.int64, device="cuda"), torch.zeros(4, dtype=torch.int64, device="cuda")
+    for t in range(1, 13):
+        act = torch.stack([torch.randint(0, 2, (n,), generator=g, device="cuda"), torch.randint(-1, 4, (n,), generator=g, device="cuda")], 1).contiguous()
+        ca, cb = torch.zeros(1, dtype=torch.int32, device="cuda"), torch.zeros(1, dtype=torch.int32, device="cuda")
+        ia, ib = torch.empty(n, dtype=torch.int32, device="cuda"), torch.empty(n, dtype=torch.int32, device="cuda")
+        ra = e.step(sa, act, seed=seed, step=t, env_id0=env_id0, stats=stats_a, term_compact=(ca, ia), want=want)
+        rb = e.step(sb, act, seed=seed, step=t, env_id0=env_id0, stats=stats_b, term_compact=(cb, ib), want=want, block_kernel=True)
+        assert torch.equal(sa, sb), t
+        for k in ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice"):
+            assert torch.equal(ra[k], rb[k]), (t, k)
+        F = int(ca.item())
+        assert F == int(cb.item()) == int(ra["terminated"].sum().item())
+        pa, pb = torch.argsort(ia[:F]), torch.argsort(ib[:F])           # row order is arbitrary: compare by env index
+        assert torch.equal(ia[:F][pa], ib[:F][pb])
+        assert torch.equal(ia[:F][pa].long(), torch.nonzero(ra["terminated"]).flatten())
+        assert torch.equal(ra["term_board"][:F][pa], rb["term_board"][:F][pb]) and torch.equal(ra["term_dice"][:F][pa], rb["term_dice"][:F][pb])
+        ref = O.step_philox(ob, od, act[:m].cpu().numpy(), seed, t, env_id0, N, L, reward=1.0, autoreset=True, threads=4)
+        assert np.array_equal(ra["obs_board"][:m].cpu().numpy(), ref["board"]) and np.array_equal(ra["obs_dice"][:m].cpu().numpy(), ref["dice"])
+        sel = ia[:F][pa] < m
+        assert np.array_equal(ra["term_board"][:F][pa][sel].cpu().numpy(), ref["term_board"][ref["terminated"] == 1])
+        ob, od = ref["board"], ref["dice"]
+    assert torch.equal(stats_a, stats_b) and int(stats_a[3].item()) > 0

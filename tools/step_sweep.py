@@ -2,6 +2,9 @@
 import sys, os, itertools
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+from ewn_gym_b200 import _lib
+if os.environ.get("EWN_LIB_VARIANT"):          # experiment builds (build/variants/*.so); the product always loads csrc/libewn_b200.so
+    _lib.LIB_PATH = os.path.abspath(os.environ["EWN_LIB_VARIANT"])
 from ewn_gym_b200.engine import Engine
 
 dev = torch.device("cuda", 0)
@@ -13,7 +16,11 @@ shapes = {"reward_f32": ((n,), "f32"), "terminated": ((n,), "u8"), "truncated": 
           "obs_dice": ((n,), "i64"), "term_board": ((n, 5, 5), "i16"), "term_dice": ((n,), "i64")}
 
 
-def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=False, compact=False):
+full = list(shapes)
+vec = ["reward_f32", "terminated", "truncated", "obs_board", "obs_dice"]
+
+
+def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=False, compact=False, block_kernel=False):
     sets = []
     st = torch.zeros(4, dtype=torch.int64, device=dev) if stats else None
     for s in range(nsets):
@@ -22,7 +29,7 @@ def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=Fal
         S["out"] = {k: e.xp.empty(*shapes[k]) for k in want}
         S["cnt"] = torch.zeros(2, dtype=torch.int32, device=dev); S["tidx"] = torch.empty(n, dtype=torch.int32, device=dev)
         S["plans"] = [e.step_plan(S["state"], None if agent_random else S["act"], seed=SEED + s, autoreset=True, stats=st, want=tuple(want), out=S["out"],
-                                  agent_random=agent_random,
+                                  agent_random=agent_random, block_kernel=block_kernel,
                                   term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b]) if compact else None) for b in (0, 1)]
         sets.append(S)
     fl = torch.empty(256 << 20, dtype=torch.int8, device=dev) if flush else None
@@ -47,9 +54,14 @@ def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=Fal
     print(f"{label:60s} sets={nsets} {us:8.2f} us/launch  {n / us * 1e6:.3e} steps/s", flush=True)
 
 
-full = list(shapes)
-vec = ["reward_f32", "terminated", "truncated", "obs_board", "obs_dice"]
+if os.environ.get("EWN_SWEEP_SHORT"):
+    run("vec + compact term obs, PERSISTENT kernel", 4, full, compact=True)
+    run("vec + compact term obs, block kernel", 4, full, compact=True, block_kernel=True)
+    run("vec surface, no term obs, PERSISTENT", 4, vec)
+    run("vec surface, no term obs, no stats, PERSISTENT", 4, vec, stats=False)
+    sys.exit(0)
 run("vec surface + DENSE term obs", 4, full)
+run("vec + compact term obs, block kernel", 4, full, compact=True, block_kernel=True)
 run("vec surface + COMPACT term obs (bench)", 4, full, compact=True)
 run("vec surface + COMPACT term obs, 1 set (L2 resident)", 1, full, compact=True)
 run("vec surface, no term obs", 4, vec)
