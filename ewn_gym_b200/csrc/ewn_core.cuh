@@ -334,11 +334,13 @@ EWN_HD void legal_pick(const Legal& l, int idx, int& larger, int& dir, int& sh) 
 }
 
 // envs/ewn.py:217-263 execute_move for a move already known to stay on the board. Returns the target cell.
+// dir 3 is the reference's "no branch matches" case (:229-247): (x, y) stays put, the cube is lifted and put back.
 template <class C, int BR> EWN_HD int apply_move(Game<C>& g, int sh, int dir) {
     typedef typename C::W W;
     W own = BR ? g.br : g.tl;
     int c = (int)((own >> sh) & C::FM);
     int delta = (dir != 1) + C::S * (dir != 0);            // envs/ewn.py:301-319 update_position
+    delta = dir > 2 ? 0 : delta;
     int t = BR ? c - delta : c + delta;
     W rep = (W)t * C::ONES;
     g.tl = capture<C>(g.tl, rep);
@@ -354,18 +356,18 @@ template <class C, int BR> EWN_HD bool win_after(const Game<C>& g, const Geo& ge
 
 // One ply with an externally chosen action (find_cube_to_move + execute_move, envs/ewn.py:439-442).
 // Returns false (state untouched, :262-263) when the move leaves the board or the side has no cube.
+// A direction outside {0,1,2} matches no branch of :229-247: (x, y) stays put, the bounds test passes and the cube is
+// put back where it stood -- a VALID no-op move (the action space never produces it; parity keeps it).  It is folded
+// into the data path as pseudo-direction 3 (always "on the board", displacement 0) so that the ply stays branch-free.
 template <class C, int BR> EWN_HD bool ply_action(Game<C>& g, const Geo& geo, int larger, int dir, int& t_out, int& sh_out) {
     typename C::W side = BR ? g.br : g.tl;
     Movers m = movers<C>(side, g.dice);
     int sh = cube_to_move(m, larger == 1);
     sh_out = sh;
-    if (sh < 0) return false;
-    // envs/ewn.py:229-247: a direction outside {0,1,2} matches no branch, (x, y) stays put, the bounds test passes and the
-    // cube is put back where it stood -- a VALID no-op move (the action space never produces it; parity keeps it)
-    if ((unsigned)dir > 2u) { t_out = cell_at<C>(side, sh); return true; }
-    int ok = C::template dirs<BR>(geo, cell_at<C>(side, sh));
-    if (!((ok >> dir) & 1)) return false;
-    t_out = apply_move<C, BR>(g, sh, dir);
+    const int d = (unsigned)dir > 2u ? 3 : dir;
+    const int ok = C::template dirs<BR>(geo, cell_at<C>(side, sh & (int)(8 * sizeof(typename C::W) - 1))) | 8;
+    if (sh < 0 || !((ok >> d) & 1)) return false;
+    t_out = apply_move<C, BR>(g, sh, d);
     return true;
 }
 

@@ -461,7 +461,7 @@ template <class C> __device__ __forceinline__ void prefetch_game(unsigned slot, 
 template <class C, int NT> __global__ void __launch_bounds__(VTPB, VMINB)
 k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     extern __shared__ uint4 smem_raw[];
-    __shared__ unsigned s_cnt, s_won, s_lost, s_row0;
+    __shared__ unsigned s_won, s_lost, s_row0, s_wcnt[VTPB / 32];
     __shared__ ulonglong2 s_pf[2 * VTPB];
     const ewn_step_args& a = ka.a;
     const int n = (int)a.n;                                        // the host keeps n below 2^31 on this path: 32-bit indices
@@ -475,10 +475,13 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     int16_t* const smb = reinterpret_cast<int16_t*>(smem_raw);                       // [VTPB][NN] staging (+ 32 B slack)
     u64* const s_term = reinterpret_cast<u64*>(reinterpret_cast<char*>(smem_raw) + (((size_t)VTPB * NN * 2 + 32 + 15) & ~(size_t)15));
     u32* const s_who = reinterpret_cast<u32*>(s_term + (size_t)cap * C::WORDS);
-    if (tid == 0) {
-        s_cnt = 0; s_won = 0; s_lost = 0;
-        if (a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
-    }
+    // Programmatic dependent launch: let the NEXT kernel of the stream become resident while this grid drains (its blocks
+    // take the SM slots our blocks free and park at their own griddepcontrol.wait), and do not touch global memory
+    // before the PREVIOUS grid has completed and flushed.  Both are no-ops for launches without the PDL attribute.
+    asm volatile("griddepcontrol.launch_dependents;");
+    if (tid == 0) { s_won = 0; s_lost = 0; }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (tid == 0 && a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
     __syncthreads();
 
     const int n_units = (n + VTPB - 1) / VTPB;
@@ -488,7 +491,10 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     // prefetch slot of this thread: state (8 / 16 B) + action (16 B), filled by cp.async while the previous unit is computed
     const unsigned pf = (unsigned)__cvta_generic_to_shared(s_pf) + tid * 32u;
     if (mine) prefetch_game<C>(pf, a.state, a.action_i64, i);
+    const bool obs_vec = (reinterpret_cast<uintptr_t>(a.obs_board) & 15) == 0;
     unsigned tally_c = 0;                                          // wins | losses << 16 of this thread
+    unsigned wcnt = 0;                                             // finished games of this warp so far (warp-uniform)
+    const unsigned seg = (unsigned)cap / (VTPB / 32);              // list entries per warp: one per game the warp can meet
     int16_t* const sm = smb + warp * 32 * NN;
     while (u < n_units) {                                          // block-uniform
         asm volatile("cp.async.wait_all;" ::: "memory");
@@ -505,27 +511,30 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             const int al = (int)act.x, ad = (act.y < 0 || act.y > 2) ? 3 : (int)act.y;
             StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
             int tol = 0; double prev = 0.0;
+#if defined(EWN_EXP_NOSTEP)      /* experiment build: the I/O skeleton without the rules (tools/step_sweep.py) */
+            out.reward = 0.0; out.trunc = 0; g.dice = 1 + ((g.dice + al + ad) % 6);
+#elif defined(EWN_EXP_PHILOX)    /* experiment build: I/O skeleton + the Philox block only */
+            { u32 blk[4]; env_block_rk(ka.p.rk, ka.p.env_id0 + (u64)i, ka.p.step, TAG_STEP, blk);
+              out.reward = 0.0; out.trunc = 0; g.dice = 1 + (int)bounded(blk[0] ^ blk[1] ^ blk[2] ^ blk[3] ^ (u32)(al + ad), 6u); }
+#else
             step_one_cfg<C>(g, term, ka.p, geo, 0, 0, 0, i, al, ad, inj, &tol, &prev, out);
+#endif
             pack(g, a.state, i);
             __stcs(a.reward_f32 + i, (float)out.reward);
             __stcs(a.terminated + i, (uint8_t)out.term);
             __stcs(a.truncated + i, (uint8_t)out.trunc);
             __stcs(reinterpret_cast<long long*>(a.obs_dice) + i, (long long)g.dice);
         }
-        if (tally) {                                               // finished games: append to the block's list
+        if (tally) {                                               // finished games: append to this WARP's segment of the list
             const bool fin = mine && out.term;
             const unsigned done = __ballot_sync(0xffffffffu, fin);
-            if (done) {
-                unsigned base = 0;
-                if (lane == 0) base = atomicAdd(&s_cnt, (unsigned)__popc(done));
-                if (compact) {
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (fin) {
-                        const unsigned k = base + (unsigned)__popc(done & ((1u << lane) - 1u));
-                        pack(term, s_term, (long)k);
-                        s_who[k] = (u32)i;
-                    }
+            if (done) {                                            // warp-uniform; no atomics, the counter lives in a register
+                if (compact && fin) {
+                    const unsigned k = (unsigned)warp * seg + wcnt + (unsigned)__popc(done & ((1u << lane) - 1u));
+                    pack(term, s_term, (long)k);
+                    s_who[k] = (u32)i;
                 }
+                wcnt += (unsigned)__popc(done);
                 if (fin) tally_c += (out.code == CODE_AGENT_WON ? 1u : 0u) + (out.code == CODE_AGENT_LOST ? 0x10000u : 0u);
             }
         }
@@ -542,17 +551,32 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             __syncwarp();
             if (mine) scatter_row<C, NT>(g, geo, sm, lane);
             __syncwarp();
-            write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
+            if (obs_vec && warp_env0 + 32 <= n) {                  // 32 full rows, 16-byte aligned: the warp's tile as vectors
+                uint4* d = reinterpret_cast<uint4*>(a.obs_board) + (size_t)(warp_env0 >> 5) * nvec;
+                if (NT) {
+#pragma unroll
+                    for (int k = 0; k < (4 * NT * NT + 31) / 32; k++) if (lane + 32 * k < nvec) __stcs(d + lane + 32 * k, v[lane + 32 * k]);
+                } else {
+                    for (int k = lane; k < nvec; k += 32) __stcs(d + k, v[k]);
+                }
+                __syncwarp();
+            } else {
+                write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
+            }
         }
         u = un; i = in; mine = mine_n;
     }
     if (!tally) return;
-    if (a.stats) {
+    {
         const unsigned wl = __reduce_add_sync(0xffffffffu, tally_c);          // <= 32 * VITER_MAX per half: no carry
-        if (lane == 0 && wl) { atomicAdd(&s_won, wl & 0xffffu); atomicAdd(&s_lost, wl >> 16); }
+        if (lane == 0) { s_wcnt[warp] = wcnt; if (wl) { atomicAdd(&s_won, wl & 0xffffu); atomicAdd(&s_lost, wl >> 16); } }
     }
     __syncthreads();
-    const int F = (int)s_cnt;
+    unsigned pre[VTPB / 32 + 1];                                   // exclusive prefix of the warps' counts
+    pre[0] = 0;
+#pragma unroll
+    for (int w = 0; w < VTPB / 32; w++) pre[w + 1] = pre[w] + s_wcnt[w];
+    const int F = (int)pre[VTPB / 32];
     if (F == 0) return;                                            // uniform over the block
     if (a.stats && tid < 4) {
         const unsigned w = s_won, l = s_lost;
@@ -561,12 +585,23 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     }
     if (!compact) return;
     if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+    // row r of this block's output <-> entry src(r) of the segmented list
+    auto src = [&](int r) -> int {
+        int w = 0;
+#pragma unroll
+        for (int k = 1; k < VTPB / 32; k++) w += (unsigned)r >= pre[k];
+        unsigned base = 0;
+#pragma unroll
+        for (int k = 1; k < VTPB / 32; k++) base = w == k ? pre[k] : base;
+        return w * (int)seg + (r - (int)base);
+    };
     __syncthreads();
     const int64_t row0 = (int64_t)s_row0;
     for (int r = tid; r < F; r += VTPB) {
-        Game<C> t; unpack(t, s_term, (long)r);
+        const int e = src(r);
+        Game<C> t; unpack(t, s_term, (long)e);
         if (a.term_dice) __stcs(reinterpret_cast<long long*>(a.term_dice) + row0 + r, (long long)t.dice);
-        __stcs(a.term_index + row0 + r, (int32_t)(a.term_index_base + (int64_t)s_who[r]));
+        __stcs(a.term_index + row0 + r, (int32_t)(a.term_index_base + (int64_t)s_who[e]));
     }
     if (!a.term_board) return;
     for (int r0 = 0; r0 < F; r0 += VTPB) {                         // VTPB rows per pass through the staging tile
@@ -581,7 +616,8 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             const int r = (int)__umulhi((unsigned)q, 0x15555556u);  // q / 12
             const int k = q - 12 * r;
             const int br = k >= 6, kk = br ? k - 6 : k;
-            const u64 wsel = C::WORDS == 1 ? (br ? s_term[r0 + r] >> 32 : s_term[r0 + r]) : s_term[2 * (r0 + r) + br];
+            const int e = src(r0 + r);
+            const u64 wsel = C::WORDS == 1 ? (br ? s_term[e] >> 32 : s_term[e]) : s_term[2 * e + br];
             const int c = (int)(((typename C::W)wsel >> (C::FB * kk)) & C::FM);
             if (c != (int)C::FM) smb[head + r * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(br ? -(kk + 1) : kk + 1);
         }
@@ -974,10 +1010,19 @@ int ewn_step(const ewn_step_args* a, void* stream) {
         const int cap = a->term_count ? iters * VTPB : 0;
         const int words = use_p5(N) ? 1 : 2;
         const size_t sm = (((size_t)VTPB * N * N * 2 + 32 + 15) & ~(size_t)15) + (size_t)cap * (8 * words + 4);
-        if (N == 5) k_vstep<P5, 5><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
-        else if (use_p5(N)) k_vstep<P5, 0><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
-        else if (N == 7) k_vstep<P8, 7><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
-        else k_vstep<P8, 0><<<(unsigned)blocks, VTPB, sm, st>>>(ka, cap);
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3(VTPB); cfg.dynamicSmemBytes = sm; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = (a->flags & EWN_STEP_NO_PDL) ? 0 : 1;
+        cudaError_t le;
+        if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5>, ka, cap);
+        else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0>, ka, cap);
+        else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7>, ka, cap);
+        else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0>, ka, cap);
+        if (le != cudaSuccess) return cuda_fail(le, "k_vstep");
         LAUNCHED("k_vstep");
         return EWN_OK;
     }

@@ -155,6 +155,8 @@ typedef struct ewn_step_args {
 
 /* flags: run the VecEnv surface on the one-block-per-128-games kernel instead of the persistent one (A/B measurements) */
 #define EWN_STEP_BLOCK_KERNEL 1
+/* flags: launch the persistent kernel without the programmatic-dependent-launch attribute (A/B measurements) */
+#define EWN_STEP_NO_PDL 2
 
 EWN_API int ewn_step(const ewn_step_args *args, void *stream);
 

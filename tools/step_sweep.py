@@ -20,7 +20,7 @@ full = list(shapes)
 vec = ["reward_f32", "terminated", "truncated", "obs_board", "obs_dice"]
 
 
-def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=False, compact=False, block_kernel=False):
+def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=False, compact=False, block_kernel=False, no_pdl=False):
     sets = []
     st = torch.zeros(4, dtype=torch.int64, device=dev) if stats else None
     for s in range(nsets):
@@ -29,7 +29,7 @@ def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=Fal
         S["out"] = {k: e.xp.empty(*shapes[k]) for k in want}
         S["cnt"] = torch.zeros(2, dtype=torch.int32, device=dev); S["tidx"] = torch.empty(n, dtype=torch.int32, device=dev)
         S["plans"] = [e.step_plan(S["state"], None if agent_random else S["act"], seed=SEED + s, autoreset=True, stats=st, want=tuple(want), out=S["out"],
-                                  agent_random=agent_random, block_kernel=block_kernel,
+                                  agent_random=agent_random, block_kernel=block_kernel, no_pdl=no_pdl,
                                   term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b]) if compact else None) for b in (0, 1)]
         sets.append(S)
     fl = torch.empty(256 << 20, dtype=torch.int8, device=dev) if flush else None
@@ -56,6 +56,8 @@ def run(label, nsets, want, iters=200, agent_random=False, stats=True, flush=Fal
 
 if os.environ.get("EWN_SWEEP_SHORT"):
     run("vec + compact term obs, PERSISTENT kernel", 4, full, compact=True)
+    run("vec + compact term obs, PERSISTENT, no PDL", 4, full, compact=True, no_pdl=True)
+    run("vec + compact term obs, PERSISTENT, 1 set (true dependency)", 1, full, compact=True)
     run("vec + compact term obs, block kernel", 4, full, compact=True, block_kernel=True)
     run("vec surface, no term obs, PERSISTENT", 4, vec)
     run("vec surface, no term obs, no stats, PERSISTENT", 4, vec, stats=False)
