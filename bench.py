@@ -292,7 +292,7 @@ def run_ours(args, rank, world, local_rank):
 
     hbm, peak_src = peaks()
     achieved = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_step<P5,false,false>", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+    roofline = {"bound": "hbm", "kernel": "k_vstep<P5,5>", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                 "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": BYTES_PER_STEP * n}
     prof = os.path.join(ROOT, "profiles", "k_step_traffic.json")
     if os.path.exists(prof):

@@ -422,10 +422,10 @@ k_step(const __grid_constant__ StepKArgs ka) {
 //     with ONE global atomic and all threads decode the boards together, one (game, cube) pair per thread.
 // ------------------------------------------------------------------------------------------------
 #ifndef EWN_VTPB
-#define EWN_VTPB 128
+#define EWN_VTPB 32
 #endif
 #ifndef EWN_VMINB
-#define EWN_VMINB 12
+#define EWN_VMINB 32
 #endif
 #ifndef EWN_VITER_MAX
 #define EWN_VITER_MAX 8
