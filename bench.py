@@ -252,13 +252,69 @@ def run_ours(args, rank, world, local_rank):
         roots = e.reset(roots_n, seed=SEED + 2)
         for s in range(1, 5):
             e.step(roots, None, seed=SEED + 2, step=s, agent_random=True, autoreset=True, want=())
-        e.expectiminimax(roots[:1024], 4)
+        e.expectiminimax(roots, 4)                  # warm-up at full size: the library's scratch allocation happens here
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize(); a0.record()
         v, a = e.expectiminimax(roots, 4)
         a1.record(); torch.cuda.synchronize()
         ems = a0.elapsed_time(a1)
         emm = {"value": roots_n / (ems / 1e3), "unit": "roots/s (depth 4, hybrid, pruned semantics)", "ms": ems, "roots": roots_n, "per_gpu": True}
+
+    # ---- secondary: configs[4], 7x7 MiniMaxHeuristicEnv rollout collection, 4096 envs x 128 steps over all ranks, counters all-reduced
+    rollout = None
+    if not args.skip_rollout:
+        e7 = Engine(7, 3, device=dev)
+        n7, T = 4096 // world, 128
+        st7 = e7.reset(n7, seed=SEED + 3, env_id0=rank * n7)
+        tol = torch.full((n7,), 10, dtype=torch.int32, device=dev)
+        prev = e7.evaluate(st7, "hybrid")
+        pool = [torch.stack([torch.randint(0, 2, (n7,), generator=g, device=dev), torch.randint(0, 3, (n7,), generator=g, device=dev)], 1).contiguous()
+                for _ in range(8)]                 # policy stub (SB3 is not installed): uniform MultiDiscrete([2,3]) samples
+        want7 = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice")
+        out7 = {k: None for k in want7}
+        st_roll = torch.zeros(4, dtype=torch.int64, device=dev)
+        ctr = torch.zeros(1, dtype=torch.int64, device=dev)
+        first = e7.step(st7, pool[0], seed=SEED + 3, step=1, env_id0=rank * n7, shaped=True, illegal_move_reward=-1.0, tolerance=tol,
+                        prev_score=prev, stats=st_roll, want=want7, step_dev=ctr)
+        side = torch.cuda.Stream(device=dev)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):              # plans bind the stream that is current when they are built
+            plans = [e7.step_plan(st7, pool[t % 8], seed=SEED + 3, step=t + 1, env_id0=rank * n7, shaped=True, illegal_move_reward=-1.0,
+                                  tolerance=tol, prev_score=prev, stats=st_roll, want=want7, out=first, step_dev=ctr) for t in range(T)]
+
+            def rollout_stream():
+                for t in range(T):
+                    plans[t].launch(t + 1)
+                e7.counter_add(ctr, T)
+
+            rollout_stream(); torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                rollout_stream()                    # 128 step kernels + the counter bump: the next replay draws fresh Philox counters
+            graph.replay(); torch.cuda.synchronize()
+        res = {}
+        for name, fn in (("stream", rollout_stream), ("graph", graph.replay)):
+            reps = 10
+            st_roll.zero_()
+            torch.cuda.synchronize()
+            if dist: dist.barrier()
+            a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            with torch.cuda.stream(side):
+                a0.record()
+                for _ in range(reps):
+                    fn()
+                a1.record()
+                tot = st_roll.clone()
+                if dist: dist.all_reduce(tot)       # wins / losses / illegal endings / episodes of the whole job
+                a2.record()
+            torch.cuda.synchronize()
+            ms, ar = a0.elapsed_time(a1) / reps, a0.elapsed_time(a2) - a0.elapsed_time(a1)
+            if dist:
+                tt = torch.tensor([ms, ar], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms, ar = tt.tolist()
+            res[name] = {"ms_per_rollout": ms, "env_steps_per_s": n7 * world * T / (ms / 1e3), "allreduce_us": 1e3 * ar,
+                         "episodes": int(tot[3].item()) // reps}
+        rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
+                               "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
 
     if rank != 0:
         if dist: dist.destroy_process_group()
@@ -310,7 +366,7 @@ def run_ours(args, rank, world, local_rank):
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env steps/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm,
+            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
             "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3]},
             "wall_s_timed_region": wall}
     print(json.dumps(line), flush=True)
@@ -328,6 +384,7 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-playouts", action="store_true")
     ap.add_argument("--skip-search", action="store_true")
+    ap.add_argument("--skip-rollout", action="store_true")
     ap.add_argument("--skip-clocks", action="store_true", help="no extended load phase for the clock sampler (profiling runs)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))

@@ -34,7 +34,7 @@ class StepArgs(C.Structure):
         ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
         ("reward", C.c_double), ("illegal_move_reward", C.c_double),
         ("seed", u64), ("step", u64), ("env_id0", u64),
-        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("flags", i32),
+        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("flags", i32), ("step_dev", p_void),
     ]
 
 
@@ -64,6 +64,7 @@ PROTOTYPES = {
     "ewn_set_dice": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_random_action": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
     "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),
+    "ewn_counter_add": (C.c_int, [p_void, u64, p_void]),
     "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
     "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
     "ewn_expectiminimax": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void, p_void, C.c_size_t, p_void]),

@@ -537,10 +537,10 @@ struct StepOut {
 // `geo` and the three mode flags are passed beside `p` so that a kernel can specialise them at compile time while `p`
 // itself stays a read-only kernel parameter (constant bank): nothing of it is copied into registers or local memory.
 template <class C> EWN_HD void step_one_cfg(Game<C>& g, Game<C>& term_state, const StepParams& p, const Geo& geo, const int replay,
-                                            const int shaped, const int agent_random, long i, int a_larger, int a_dir,
+                                            const int shaped, const int agent_random, const u64 step, long i, int a_larger, int a_dir,
                                             const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
     u32 blk[4] = {0, 0, 0, 0};
-    if (!replay || agent_random) env_block_rk(p.rk, p.env_id0 + (u64)i, p.step, TAG_STEP, blk);
+    if (!replay || agent_random) env_block_rk(p.rk, p.env_id0 + (u64)i, step, TAG_STEP, blk);
     bool pre = full_win<C>(g, geo);        // stepping an already finished game keeps reporting a win (check_win is sticky)
     out.reward = 0.0; out.term = 0; out.trunc = 0; out.code = CODE_ONGOING;
     bool valid; int t = 0, sh = -1;
@@ -600,7 +600,7 @@ template <class C> EWN_HD void step_one_cfg(Game<C>& g, Game<C>& term_state, con
 
 template <class C> EWN_HD void step_one(Game<C>& g, Game<C>& term_state, const StepParams& p, long i, int a_larger, int a_dir,
                                         const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
-    step_one_cfg<C>(g, term_state, p, p.geo, p.replay, p.shaped, p.agent_random, i, a_larger, a_dir, inj, tolerance, prev_score, out);
+    step_one_cfg<C>(g, term_state, p, p.geo, p.replay, p.shaped, p.agent_random, p.step, i, a_larger, a_dir, inj, tolerance, prev_score, out);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -301,6 +301,7 @@ k_step(const __grid_constant__ StepKArgs ka) {
         }
         int tol = 0; double prev = 0.0;
         if (SHAPED) { tol = a.tolerance[i]; prev = a.prev_score[i]; }
+        if (a.step_dev) p.step += __ldg(a.step_dev);
         step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
         if (SHAPED) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
         pack(g, a.state, i);
@@ -484,6 +485,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     if (tid == 0 && a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
     __syncthreads();
 
+    const u64 step = ka.p.step + (a.step_dev ? __ldg(a.step_dev) : 0ull);   // device-resident step counter: CUDA-graph replays
     const int n_units = (n + VTPB - 1) / VTPB;
     int u = blockIdx.x;
     int i = u * VTPB + tid;
@@ -514,10 +516,10 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
 #if defined(EWN_EXP_NOSTEP)      /* experiment build: the I/O skeleton without the rules (tools/step_sweep.py) */
             out.reward = 0.0; out.trunc = 0; g.dice = 1 + ((g.dice + al + ad) % 6);
 #elif defined(EWN_EXP_PHILOX)    /* experiment build: I/O skeleton + the Philox block only */
-            { u32 blk[4]; env_block_rk(ka.p.rk, ka.p.env_id0 + (u64)i, ka.p.step, TAG_STEP, blk);
+            { u32 blk[4]; env_block_rk(ka.p.rk, ka.p.env_id0 + (u64)i, step, TAG_STEP, blk);
               out.reward = 0.0; out.trunc = 0; g.dice = 1 + (int)bounded(blk[0] ^ blk[1] ^ blk[2] ^ blk[3] ^ (u32)(al + ad), 6u); }
 #else
-            step_one_cfg<C>(g, term, ka.p, geo, 0, 0, 0, i, al, ad, inj, &tol, &prev, out);
+            step_one_cfg<C>(g, term, ka.p, geo, 0, 0, 0, step, i, al, ad, inj, &tol, &prev, out);
 #endif
             pack(g, a.state, i);
             __stcs(a.reward_f32 + i, (float)out.reward);
@@ -839,6 +841,19 @@ template <class C> size_t obs_smem(const Geo& geo) { return (size_t)WARPS * 32 *
 // k_step: one staging row per thread + slack for the 16-byte phase of the compacted terminal rows
 inline size_t step_smem(const Geo& geo) { return (size_t)STPB * geo.N * geo.N * sizeof(int16_t) + 32; }
 
+// grid of k_playouts: 8 blocks of 256 threads per SM.  Only 6 are resident at once (36 registers), so the last third of
+// the blocks runs as a short second wave at low occupancy; measured on B200 this is FASTER than exactly one resident wave
+// (1.66 ms vs 1.82 ms for 14.5 M playouts): the kernel is bound by the alu pipe, and the second wave's warps run with less
+// contention while the equal-share ranges stay shorter (profiles/r1_k_playouts_grid_experiment.txt).
+template <class C> int playout_grid(int64_t total_games) {
+    int64_t warps_needed = (total_games + 31) / 32;
+    int64_t blocks = (warps_needed + WARPS - 1) / WARPS;
+    int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
 #define DISPATCH(N, expr_p5, expr_p8) \
     do { if (use_p5(N)) { typedef P5 C; expr_p5; } else { typedef P8 C; expr_p8; } } while (0)
 
@@ -1032,6 +1047,15 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     return EWN_OK;
 }
 
+__global__ void k_counter_add(unsigned long long* c, unsigned long long k) { if (threadIdx.x == 0 && blockIdx.x == 0) *c += k; }
+
+int ewn_counter_add(uint64_t* counter, uint64_t k, void* stream) {
+    if (!counter) return EWN_EARG;
+    k_counter_add<<<1, 32, 0, (cudaStream_t)stream>>>(reinterpret_cast<unsigned long long*>(counter), (unsigned long long)k);
+    LAUNCHED("k_counter_add");
+    return EWN_OK;
+}
+
 int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void* stream) {
     if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
     if (n == 0) return EWN_OK;
@@ -1099,15 +1123,6 @@ size_t ewn_mc_workspace(int64_t n) {
     return 256 + (size_t)n * 6 * (16 + 4 + 4 + 4);
 }
 
-static int playout_grid(int64_t total_games) {
-    int64_t warps_needed = (total_games + 31) / 32;
-    int64_t blocks = (warps_needed + WARPS - 1) / WARPS;
-    int64_t cap = (int64_t)sm_count() * 8;       // 8 resident blocks of 256 threads per SM
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return (int)blocks;
-}
-
 int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
                  uint32_t* wins, unsigned long long* plies, void* stream) {
     if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
@@ -1115,7 +1130,7 @@ int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int
     if (n == 0 || count == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    const int grid = playout_grid(n * (int64_t)count);
+    const int grid = use_p5(N) ? playout_grid<P5>(n * (int64_t)count) : playout_grid<P8>(n * (int64_t)count);
     if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
     else           k_playouts<P8><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
     LAUNCHED("k_playouts");
@@ -1146,7 +1161,7 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     else           k_mc_expand<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children);
     LAUNCHED("k_mc_expand");
     if (count == 0) return EWN_OK;
-    const int grid = playout_grid(n * 6 * (int64_t)count);
+    const int grid = use_p5(N) ? playout_grid<P5>(n * 6 * (int64_t)count) : playout_grid<P8>(n * 6 * (int64_t)count);
     if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
     else           k_playouts<P8><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
     LAUNCHED("k_playouts");

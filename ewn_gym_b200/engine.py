@@ -169,7 +169,7 @@ class Engine:
     # ------------------------------------------------------------------ env step
     def step(self, state, action=None, *, seed=0, step=0, env_id0=0, reward=1.0, agent_random=False, autoreset=True,
              shaped=False, illegal_move_reward=-1.0, tolerance=None, prev_score=None, inject=None, stats=None, term_compact=None,
-             want=("reward_f32", "terminated", "truncated"), out: Optional[dict] = None, block_kernel=False, no_pdl=False):
+             want=("reward_f32", "terminated", "truncated"), out: Optional[dict] = None, block_kernel=False, no_pdl=False, step_dev=None):
         """One env step for every game (envs/ewn.py:436-486), in place on `state`.
 
         action : int64[n,2] / int32[n,2] / uint8[n] tensor, or None with agent_random.
@@ -224,8 +224,14 @@ class Engine:
         a.seed, a.step, a.env_id0 = seed, step, env_id0
         a.agent_random, a.autoreset, a.shaped = int(agent_random), int(autoreset), int(shaped)
         a.flags = (1 if block_kernel else 0) | (2 if no_pdl else 0)
+        if step_dev is not None:                   # int64[1] device counter added to `step` at run time (CUDA-graph replays)
+            a.step_dev = xp.ptr(step_dev)
         self._chk(self.lib.ewn_step(C.byref(a), xp.stream()), "ewn_step")
         return res
+
+    def counter_add(self, counter, k: int):
+        """*counter += k on the current stream (see ewn_step_args.step_dev)"""
+        self._chk(self.lib.ewn_counter_add(self.xp.ptr(counter), int(k), self.xp.stream()), "ewn_counter_add")
 
     def step_plan(self, state, action=None, **kw):
         """Pre-bind a step (pointers, sizes, flags) so that a rollout loop pays one ctypes call per launch:

@@ -151,6 +151,9 @@ typedef struct ewn_step_args {
     int32_t autoreset;            /* SB3 VecEnv contract                                                        */
     int32_t shaped;               /* MiniMaxHeuristicEnv.step                                                   */
     int32_t flags;                /* EWN_STEP_* bits, 0 = defaults                                              */
+    const uint64_t *step_dev;     /* optional device counter added to `step` when the kernel runs: a CUDA graph of K   */
+                                  /* captured steps (step = 1..K baked in) is replayed with fresh Philox counters by   */
+                                  /* ewn_counter_add(step_dev, K) at the end of the graph                              */
 } ewn_step_args;
 
 /* flags: run the VecEnv surface on the one-block-per-128-games kernel instead of the persistent one (A/B measurements) */
@@ -159,6 +162,8 @@ typedef struct ewn_step_args {
 #define EWN_STEP_NO_PDL 2
 
 EWN_API int ewn_step(const ewn_step_args *args, void *stream);
+/* *counter += k on `stream` (one tiny kernel; capturable).  See ewn_step_args.step_dev. */
+EWN_API int ewn_counter_add(uint64_t *counter, uint64_t k, void *stream);
 
 /* ---- search ---------------------------------------------------------------------------------------------- */
 

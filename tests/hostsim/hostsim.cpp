@@ -112,7 +112,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
     const bool replay = a.inject_dice_opp != nullptr;
     StepParams p; memset(&p, 0, sizeof(p));
     p.geo = geo; p.reward = a.reward; p.illegal_move_reward = a.illegal_move_reward;
-    p.seed = a.seed; p.step = a.step; p.env_id0 = a.env_id0; p.rk = make_round_keys(a.seed);
+    p.seed = a.seed; p.step = a.step + (a.step_dev ? *a.step_dev : 0); p.env_id0 = a.env_id0; p.rk = make_round_keys(a.seed);
     p.agent_random = a.agent_random != 0; p.autoreset = a.autoreset != 0; p.shaped = a.shaped != 0; p.replay = replay;
     if (a.term_count_clear) *a.term_count_clear = 0u;
     for (int64_t i = 0; i < a.n; i++) {
@@ -319,6 +319,7 @@ int ewn_step(const ewn_step_args* a, void*) {
     Geo geo = make_geo(a->board_size, a->cube_layer);
     return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
 }
+int ewn_counter_add(uint64_t* counter, uint64_t k, void*) { if (!counter) return EWN_EARG; *counter += k; return EWN_OK; }
 int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void*) {
     if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
     Geo geo = make_geo(N, L);

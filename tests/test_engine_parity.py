@@ -329,3 +329,22 @@ def test_playout_win_rates_vs_reference(backend, N):
     pool = (w + ref_w) / (count + ref_n)
     se = np.sqrt(np.maximum(pool * (1 - pool), 1e-9) * (1 / count + 1 / ref_n))
     assert (np.abs(p - q) <= 4.5 * se + 1e-12).all(), np.c_[p, q, se][np.abs(p - q) > 4.5 * se]
+
+
+def test_device_step_counter(backend):
+    """ewn_step_args.step_dev: step = baked step + *step_dev, so a captured graph can be replayed with fresh Philox counters."""
+    e = make_engine(backend, 5, 3)
+    n = 2048
+    rng = np.random.default_rng(11)
+    act = np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+    sa, sb = e.reset(n, seed=8), e.reset(n, seed=8)
+    ctr = e.xp.asarray(np.zeros(1, np.int64), "i64")
+    want = ("reward_f32", "terminated", "obs_board", "obs_dice")
+    for t in range(1, 7):
+        ra = e.step(sa, e.xp.asarray(act, "i64"), seed=8, step=t, want=want)
+        rb = e.step(sb, e.xp.asarray(act, "i64"), seed=8, step=1 + (t - 1) % 3, step_dev=ctr, want=want)   # "graph" of 3 baked steps
+        if t % 3 == 0:
+            e.counter_add(ctr, 3)
+        for k in want:
+            assert np.array_equal(to_np(ra[k]), to_np(rb[k])), (t, k)
+    assert int(to_np(ctr)[0]) == 6
