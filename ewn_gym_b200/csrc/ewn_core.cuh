@@ -371,6 +371,24 @@ template <class C, int BR> EWN_HD bool ply_action(Game<C>& g, const Geo& geo, in
     return true;
 }
 
+// The board as the other side sees it: np.rot90(-board, 2) (envs/ewn.py:289-296 opponent_action).  Cube k of one side at
+// (x, y) becomes cube k of the other side at (N-1-x, N-1-y); the die is kept, the side to move is mirrored.
+template <class C> EWN_HD typename C::W flip_side(typename C::W side, const Geo& geo) {
+    typedef typename C::W W;
+    W out = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        int c = (int)((side >> (C::FB * k)) & C::FM);
+        int f = c == (int)C::FM ? (int)C::FM : geo.corner - c;      // both codecs: cell(N-1-x, N-1-y) = corner - cell(x, y)
+        out |= (W)f << (C::FB * k);
+    }
+    return out;
+}
+template <class C> EWN_HD void flip_game(Game<C>& g, const Geo& geo) {
+    typename C::W tl = flip_side<C>(g.br, geo), br = flip_side<C>(g.tl, geo);
+    g.tl = tl; g.br = br; g.player ^= 1;
+}
+
 // ------------------------------------------------------------------------------------------------
 // leaf evaluation, envs/minimax_ewn.py:29-213 (agent is always TOP_LEFT: minimax_ewn.py:17-19)
 // ------------------------------------------------------------------------------------------------

@@ -230,6 +230,14 @@ template <class C> __global__ void __launch_bounds__(TPB) k_set_dice(u64* state,
     pack(g, state, i);
 }
 
+template <class C> __global__ void __launch_bounds__(TPB) k_flip(const u64* in, u64* out, int64_t n, Geo geo) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, in, i);
+    flip_game<C>(g, geo);
+    pack(g, out, i);
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_random_action(const u64* state, int64_t* action, int64_t n, Geo geo,
                                                                           u64 seed, u64 step, u64 env_id0) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
@@ -972,6 +980,17 @@ int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, in
     if (use_p5(N)) k_set_dice<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
     else           k_set_dice<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
     LAUNCHED("k_set_dice");
+    return EWN_OK;
+}
+
+int ewn_flip(const uint64_t* state, uint64_t* out, int64_t n, int N, int L, void* stream) {
+    if (!state || !out || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_flip<P5><<<blocks_for(n), TPB, 0, st>>>(state, out, n, geo);
+    else           k_flip<P8><<<blocks_for(n), TPB, 0, st>>>(state, out, n, geo);
+    LAUNCHED("k_flip");
     return EWN_OK;
 }
 

@@ -159,6 +159,13 @@ class Engine:
                   "ewn_set_dice")
         return state
 
+    def flip(self, state, out=None):
+        """the position as the other side sees it: np.rot90(-board, 2), side to move mirrored (envs/ewn.py:289-296)"""
+        n = self._n(state)
+        o = self.new_state(n) if out is None else out
+        self._chk(self.lib.ewn_flip(self.xp.ptr(state), self.xp.ptr(o), n, self.N, self.L, self.xp.stream()), "ewn_flip")
+        return o
+
     def random_action(self, state, seed: int, step: int, env_id0: int = 0, out=None):
         n = self._n(state)
         a = self.xp.empty((n, 2), "i64") if out is None else out

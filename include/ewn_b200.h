@@ -101,6 +101,10 @@ EWN_API int ewn_ply(uint64_t *state, int player, const int32_t *action, uint8_t 
 /* MinimaxEnv.set_dice_roll (envs/minimax_ewn.py:26-27): overwrite the die (int32[n]) and optionally the side to move. */
 EWN_API int ewn_set_dice(uint64_t *state, const int32_t *dice, const int32_t *player, int64_t n, int board_size, int cube_layer,
                  void *stream);
+/* envs/ewn.py:289-296 opponent_action: the position as the other side sees it, np.rot90(-board, 2) -- cube k at (x, y) becomes
+ * the other colour's cube k at (N-1-x, N-1-y); die kept, side to move mirrored.  `out` may alias `state`.  Policies reason as
+ * TOP_LEFT (minimax.py:92, mcts.py:49), so a BOTTOM_RIGHT player is served by flip -> policy -> play the same [larger, dir]. */
+EWN_API int ewn_flip(const uint64_t *state, uint64_t *out, int64_t n, int board_size, int cube_layer, void *stream);
 /* classical_policies/random_policy.py:11-15 RandomAgent.predict for the TOP_LEFT side of every game:
  * action int64[n][2] = uniform over the ordered legal list, index = bounded(Philox(seed; env_id0+i, step, STEP)[3]). */
 EWN_API int ewn_random_action(const uint64_t *state, int64_t *action, int64_t n, int board_size, int cube_layer, uint64_t seed,

@@ -344,6 +344,39 @@ def gen_stats(name):
     print(f"{name}: {out} {time.time() - t:.1f}s")
 
 
+def count_policy_games(args):
+    """eval_minimax.py / eval_random.py evaluation(): agent policy (TOP_LEFT) vs the env's opponent policy, reward of the last step"""
+    N, L, seeds, agent_kind, agent_kw, opp_kind, opp_kw = args
+    env = R.EinsteinWuerfeltNichtEnv(board_size=N, cube_layer=L, opponent_policy=getattr(R.ClassicalPolicy, opp_kind), **opp_kw)
+    agent = R.RandomAgent(env) if agent_kind == "random" else R.ExpectiMinimaxAgent(cube_layer=L, board_size=N, **agent_kw)
+    wins = 0
+    for seed in seeds:
+        obs, _ = env.reset(seed=seed)
+        done = False
+        while not done:
+            a, _ = agent.predict(obs)
+            obs, r, done, _, _ = env.step(a)
+        wins += r > 0
+    return wins
+
+
+def gen_pair_stats(name):
+    """agent-vs-opponent win counts of the unmodified reference for the tournament driver's statistical parity test"""
+    t = time.time()
+    out = {}
+    cases = [("minimax_d1_vs_random", "minimax", dict(max_depth=1), "random", {}, 1600),
+             ("minimax_d2_vs_random", "minimax", dict(max_depth=2), "random", {}, 1200),
+             ("minimax_d3_vs_random", "minimax", dict(max_depth=3), "random", {}, 800),
+             ("random_vs_minimax_d1", "random", {}, "minimax", dict(max_depth=1), 1600),
+             ("random_vs_minimax_d2", "random", {}, "minimax", dict(max_depth=2), 1200)]
+    for key, ak, akw, ok, okw, n in cases:
+        res = pmap(count_policy_games, [(5, 3, s, ak, akw, ok, okw) for s in split(range(200000, 200000 + n), NPROC * 4)])
+        out[key] = dict(games=n, first_seed=200000, agent_wins=int(sum(res)))
+        print(key, out[key], f"{time.time() - t:.1f}s", flush=True)
+    with open(os.path.join(HERE, name), "w") as f:
+        json.dump(out, f, indent=1)
+
+
 TARGETS = {
     "games5": lambda: gen_games("random_games_5x5.npz", 5, 3, 10000),
     "games7": lambda: gen_games("random_games_7x7.npz", 7, 3, 1000),
@@ -357,6 +390,7 @@ TARGETS = {
     "mc5": lambda: gen_mc("mc_sim_5x5.npz", 5, 3, 48, 4000),
     "mc7": lambda: gen_mc("mc_sim_7x7.npz", 7, 3, 16, 2000),
     "stats": lambda: gen_stats("random_vs_random_stats.json"),
+    "pairs": lambda: gen_pair_stats("policy_pairs_stats.json"),
 }
 
 if __name__ == "__main__":

@@ -239,6 +239,10 @@ template <class C> int t_mc_best(const uint64_t* state, const uint32_t* wins, in
 }
 }  // namespace
 
+template <class C> static int t_flip(const uint64_t* in, uint64_t* out, int64_t n, const Geo& geo) {
+    for (int64_t i = 0; i < n; i++) { Game<C> g; unpack(g, in, i); flip_game<C>(g, geo); pack(g, out, i); }
+    return EWN_OK;
+}
 #define BY_CODEC(N, call_p5, call_p8) (use_p5(N) ? (call_p5) : (call_p8))
 
 extern "C" {
@@ -318,6 +322,11 @@ int ewn_step(const ewn_step_args* a, void*) {
     if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
     Geo geo = make_geo(a->board_size, a->cube_layer);
     return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
+}
+int ewn_flip(const uint64_t* state, uint64_t* out, int64_t n, int N, int L, void*) {
+    if (!state || !out || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_flip<P5>(state, out, n, geo), t_flip<P8>(state, out, n, geo));
 }
 int ewn_counter_add(uint64_t* counter, uint64_t k, void*) { if (!counter) return EWN_EARG; *counter += k; return EWN_OK; }
 int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void*) {
