@@ -736,44 +736,45 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
     const int64_t n_warps = ((int64_t)gridDim.x * TPB) >> 5;
     const int64_t n_pairs = n_pairs_dev ? (int64_t)*n_pairs_dev : n_pairs_host;
     const int64_t total = n_pairs * (int64_t)count;
-    int64_t chunk = (total + n_warps - 1) / n_warps;
-    chunk = (chunk + 31) & ~(int64_t)31;
-    int64_t next = warp_id * chunk;
-    int64_t hi = next + chunk; if (hi > total) hi = total;
-    if (next >= hi) return;
+    // Games are dealt to warps in chunks of CH consecutive games, round-robin (chunk c belongs to warp c % n_warps): playout
+    // length depends on the root position, so a warp that owned ONE contiguous range of ~1,500 games of one or two roots
+    // would finish much earlier or later than its neighbours; many small chunks average over the roots.
+    constexpr int CH = 128;
+    const int64_t n_chunks = (total + CH - 1) / CH;
+    const int64_t my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
+    int64_t tnext = 0;                                         // warp-uniform cursor over the warp's local game indices
+    const int64_t tend = my_chunks * CH;
+    if (tend == 0) return;
 
     Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
     bool busy = false;
     u32 rid = 0, child = 0, slot = 0, pidx = 0, j = 0;
     unsigned long long my_plies = 0;
     const unsigned lt = (1u << lane) - 1u;
-    int64_t base_pair = next / count;                          // warp-uniform cursor: game `next` = (base_pair, base_off)
-    u32 base_off = (u32)(next - base_pair * count);
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !busy);
         if (need) {
             const u32 rank = (u32)__popc(need & lt), taken = (u32)__popc(need);
-            const int64_t mine = next + rank;
-            if (!busy && mine < hi) {
-                u32 off = base_off + rank;                     // < count + 32
-                const u32 q = off / count;
-                off -= q * count;
-                const int64_t pair = base_pair + q;
-                pidx = first + off;
-                unpack(g, pair_state, pair);
-                rid = pair_root ? pair_root[pair] : (u32)pair;
-                child = pair_child ? pair_child[pair] : 7u;
-                slot = pair_slot ? pair_slot[pair] : (u32)pair;
-                j = 0;
-                busy = true;
-                if (full_win<C>(g, geo)) {                       // mcts.py:28: the loop body never runs
-                    if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
-                    busy = false;
+            const int64_t t = tnext + rank;
+            if (!busy && t < tend) {
+                const int64_t gi = ((t / CH) * n_warps + warp_id) * CH + (t % CH);      // global game index
+                if (gi < total) {
+                    const int64_t pair = gi / count;
+                    pidx = first + (u32)(gi - pair * count);
+                    unpack(g, pair_state, pair);
+                    rid = pair_root ? pair_root[pair] : (u32)pair;
+                    child = pair_child ? pair_child[pair] : 7u;
+                    slot = pair_slot ? pair_slot[pair] : (u32)pair;
+                    j = 0;
+                    busy = true;
+                    if (full_win<C>(g, geo)) {                   // mcts.py:28: the loop body never runs
+                        if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
+                        busy = false;
+                    }
                 }
             }
-            next += taken;
-            { u32 off = base_off + taken; const u32 q = off / count; base_off = off - q * count; base_pair += q; }
-            if (!__ballot_sync(0xffffffffu, busy) && next >= hi) break;
+            tnext += taken;
+            if (!__ballot_sync(0xffffffffu, busy) && tnext >= tend) break;
         }
         if (busy) {
             u32 blk[4];

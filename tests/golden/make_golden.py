@@ -368,7 +368,12 @@ def gen_pair_stats(name):
              ("minimax_d2_vs_random", "minimax", dict(max_depth=2), "random", {}, 1200),
              ("minimax_d3_vs_random", "minimax", dict(max_depth=3), "random", {}, 800),
              ("random_vs_minimax_d1", "random", {}, "minimax", dict(max_depth=1), 1600),
-             ("random_vs_minimax_d2", "random", {}, "minimax", dict(max_depth=2), 1200)]
+             ("random_vs_minimax_d2", "random", {}, "minimax", dict(max_depth=2), 1200),
+             ("minimax_d4_vs_random", "minimax", dict(max_depth=4), "random", {}, 800),
+             ("minimax_d5_vs_random", "minimax", dict(max_depth=5), "random", {}, 480),
+             ("random_vs_minimax_d3", "random", {}, "minimax", dict(max_depth=3), 800),
+             ("minimax_d2_vs_minimax_d1", "minimax", dict(max_depth=2), "minimax", dict(max_depth=1), 800),
+             ("minimax_d3_min_dist_vs_random", "minimax", dict(max_depth=3, heuristic="min_dist"), "random", {}, 800)]
     for key, ak, akw, ok, okw, n in cases:
         res = pmap(count_policy_games, [(5, 3, s, ak, akw, ok, okw) for s in split(range(200000, 200000 + n), NPROC * 4)])
         out[key] = dict(games=n, first_seed=200000, agent_wins=int(sum(res)))

@@ -51,3 +51,38 @@ def test_minimax_and_monte_carlo_beat_random_from_both_seats(backend):
     assert r["agent_wins"] / n > 0.70 and r["unfinished"] == 0
     lo, hi = A.wilson(r["agent_wins"], n)
     assert lo < r["agent_wins"] / n < hi
+
+
+PAIR_CASES = {   # key in tests/golden/policy_pairs_stats.json -> (agent, opponent) of the driver
+    "minimax_d1_vs_random": (lambda: A.MinimaxPolicy(1), lambda: A.RandomPolicy(seed=21)),
+    "minimax_d2_vs_random": (lambda: A.MinimaxPolicy(2), lambda: A.RandomPolicy(seed=22)),
+    "minimax_d3_vs_random": (lambda: A.MinimaxPolicy(3), lambda: A.RandomPolicy(seed=23)),
+    "minimax_d4_vs_random": (lambda: A.MinimaxPolicy(4), lambda: A.RandomPolicy(seed=24)),
+    "minimax_d5_vs_random": (lambda: A.MinimaxPolicy(5), lambda: A.RandomPolicy(seed=25)),
+    "random_vs_minimax_d1": (lambda: A.RandomPolicy(seed=26), lambda: A.MinimaxPolicy(1)),
+    "random_vs_minimax_d2": (lambda: A.RandomPolicy(seed=27), lambda: A.MinimaxPolicy(2)),
+    "random_vs_minimax_d3": (lambda: A.RandomPolicy(seed=28), lambda: A.MinimaxPolicy(3)),
+    "minimax_d2_vs_minimax_d1": (lambda: A.MinimaxPolicy(2), lambda: A.MinimaxPolicy(1)),
+    "minimax_d3_min_dist_vs_random": (lambda: A.MinimaxPolicy(3, "min_dist"), lambda: A.RandomPolicy(seed=29)),
+}
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("case", sorted(PAIR_CASES))
+def test_pair_win_rates_match_the_reference(backend, case):
+    """The unmodified reference played these pairs (eval_minimax.py / eval_random.py loop, make_golden.py `pairs`): agent =
+    ExpectiMinimaxAgent or RandomAgent as TOP_LEFT against the env's opponent policy on the flipped board.  The driver's win
+    rate must agree with the recorded one: two-sample z-test at the 99.9 % level (|z| < 3.29)."""
+    ref = json.load(open(os.path.join(GOLD, "policy_pairs_stats.json")))[case]
+    deep = any(d in case for d in ("d4", "d5", "d3"))
+    if backend != "cuda" and deep:
+        pytest.skip("depth >= 3 pairs run on the GPU tier (the host simulator is a single-thread debug build)")
+    e = make_engine(backend, 5, 3)
+    n = 8192 if backend == "cuda" else 1500
+    ag, op = PAIR_CASES[case]
+    r = A.play_matches(e, ag(), op(), n, seed=77)
+    assert r["unfinished"] == 0
+    p1, p2 = r["agent_wins"] / n, ref["agent_wins"] / ref["games"]
+    p = (r["agent_wins"] + ref["agent_wins"]) / (n + ref["games"])
+    z = (p1 - p2) / (p * (1 - p) * (1 / n + 1 / ref["games"])) ** 0.5
+    assert abs(z) < 3.29, (case, p1, p2, z)
