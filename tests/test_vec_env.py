@@ -96,3 +96,53 @@ def test_persistent_step_kernel_vs_block_kernel_and_oracle(N, L, n):
         assert np.array_equal(ra["term_board"][:F][pa][sel].cpu().numpy(), ref["term_board"][ref["terminated"] == 1])
         ob, od = ref["board"], ref["dice"]
     assert torch.equal(stats_a, stats_b) and int(stats_a[3].item()) > 0
+
+
+def test_full_size_properties_1mi_games():
+    """BASELINE.json configs[1] at full size (1,048,576 games): properties that do not need the oracle -- every board holds each
+    cube number at most once and only in range, finished games were reset to the initial layout, the compacted terminal list has
+    exactly one row per finished game, the stats counters add up, and a second run from the same seed gives the same checksums;
+    a 4,096-game slice is replayed on the oracle."""
+    import torch
+    from ewn_gym_b200.engine import Engine
+    N, L, n, seed = 5, 3, 1 << 20, 9487
+    e = Engine(N, L)
+    g = torch.Generator(device="cuda")
+    want = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice", "term_board", "term_dice")
+    sums = []
+    for rep in range(2):
+        g.manual_seed(1)
+        st = e.reset(n, seed=seed)
+        stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+        b0, d0 = e.decode(st)
+        ob, od = b0[:4096].cpu().numpy(), d0[:4096].cpu().numpy()
+        acc = torch.zeros((), dtype=torch.int64, device="cuda")
+        fin_total = 0
+        for t in range(1, 21):
+            act = torch.stack([torch.randint(0, 2, (n,), generator=g, device="cuda"), torch.randint(0, 3, (n,), generator=g, device="cuda")], 1).contiguous()
+            cnt, idx = torch.zeros(1, dtype=torch.int32, device="cuda"), torch.empty(n, dtype=torch.int32, device="cuda")
+            r = e.step(st, act, seed=seed, step=t, stats=stats, term_compact=(cnt, idx), want=want)
+            F = int(cnt.item())
+            fin = r["terminated"].bool()
+            assert F == int(fin.sum().item())
+            assert torch.equal(torch.sort(idx[:F].long()).values, torch.nonzero(fin).flatten())
+            fin_total += F
+            board = r["obs_board"].reshape(n, N * N).long()
+            assert int(board.abs().max().item()) <= 6
+            for k in (1, 3, 6):                                    # a cube number appears at most once per colour
+                assert int((board == k).sum(1).max().item()) <= 1 and int((board == -k).sum(1).max().item()) <= 1
+            assert torch.equal(r["obs_board"][fin], b0[:1].expand(F, N, N))                    # auto-reset: initial layout
+            assert int((r["obs_dice"] < 1).sum().item()) == 0 and int((r["obs_dice"] > 6).sum().item()) == 0
+            assert torch.equal(r["truncated"].bool() & ~fin, torch.zeros_like(fin))           # truncated implies terminated
+            if F:
+                tb = r["term_board"][:F].reshape(F, N * N).long()
+                assert int((tb != 0).sum(1).min().item()) >= 1                                   # a terminal board is never empty
+            acc = acc * 1000003 + (board * torch.arange(1, 26, device="cuda")).sum() + r["obs_dice"].sum() * 31 + (r["reward_f32"].double().sum() * 7).long()
+            if rep == 0:
+                ref = O.step_philox(ob, od, act[:4096].cpu().numpy(), seed, t, 0, N, L, reward=1.0, autoreset=True, threads=4)
+                assert np.array_equal(r["obs_board"][:4096].cpu().numpy(), ref["board"]) and np.array_equal(r["reward_f32"][:4096].cpu().numpy(), ref["reward"].astype(np.float32))
+                ob, od = ref["board"], ref["dice"]
+        s = stats.cpu().tolist()
+        assert s[3] == fin_total and s[0] + s[1] + s[2] == s[3] and s[0] > 0 and s[1] > 0
+        sums.append((int(acc.item()), tuple(s), int(st.sum().item())))
+    assert sums[0] == sums[1]
