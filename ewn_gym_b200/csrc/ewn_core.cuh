@@ -124,6 +124,10 @@ struct Geo {
     u64 tl0, br0;                            // side words of the initial layout (envs/ewn.py:94-107)
 };
 
+// Geo plus the shared-memory address of a per-block table  dirs[side][cell]  (k_vstep, k_playouts): the legal-direction set of
+// a cube becomes one LDS instead of ~9 integer instructions.  Functions below are generic in the geometry type G.
+struct GeoLut : Geo { u32 lut; };
+
 enum { SIDE_TL = 0, SIDE_BR = 1 };
 enum { H_HYBRID = 0, H_MIN_DIST = 1, H_TWO_MIN_DIST = 2, H_ATTK = 3 };
 enum { CODE_ONGOING = 0, CODE_AGENT_ILLEGAL = 1, CODE_AGENT_WON = 2, CODE_OPP_ILLEGAL = 3, CODE_AGENT_LOST = 4,
@@ -146,6 +150,14 @@ struct P5 {
         u32 ok0 = ~(e0 >> c) & 1u, ok1 = ~(e1 >> c) & 1u;
         return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
     }
+    static constexpr int LUT = 32;                                   // table entries per side (every 5-bit field value)
+    template <int BR> static EWN_HD int dirs(const GeoLut& g, int c) {
+#if defined(__CUDA_ARCH__)
+        u32 v; asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(g.lut + (u32)(BR * LUT) + (u32)c)); return (int)v;
+#else
+        return dirs<BR>(static_cast<const Geo&>(g), c);
+#endif
+    }
 };
 
 struct P8 {
@@ -161,6 +173,14 @@ struct P8 {
         int x = c >> 4, y = c & 15;
         u32 ok0 = BR ? (y > 0) : (y < g.N - 1), ok1 = BR ? (x > 0) : (x < g.N - 1);
         return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
+    }
+    static constexpr int LUT = 256;
+    template <int BR> static EWN_HD int dirs(const GeoLut& g, int c) {
+#if defined(__CUDA_ARCH__)
+        u32 v; asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(g.lut + (u32)(BR * LUT) + (u32)c)); return (int)v;
+#else
+        return dirs<BR>(static_cast<const Geo&>(g), c);
+#endif
     }
 };
 
@@ -305,7 +325,7 @@ template <class C> EWN_HD int cell_at(typename C::W side, int sh) { return (int)
 //   dice cube alive : first = dirs(dice cube) with flag 0, second = empty
 //   otherwise       : first = dirs(larger neighbour) with flag 1, second = dirs(smaller neighbour) with flag 0
 struct Legal { int first, second, first_flag, sh_first, sh_second; };
-template <class C, int BR> EWN_HD Legal legal(const Game<C>& g, const Geo& geo, const Movers& m) {
+template <class C, int BR, class G> EWN_HD Legal legal(const Game<C>& g, const G& geo, const Movers& m) {
     typename C::W side = BR ? g.br : g.tl;
     Legal l;
     const bool has = m.d >= 0;
@@ -359,7 +379,7 @@ template <class C, int BR> EWN_HD bool win_after(const Game<C>& g, const Geo& ge
 // A direction outside {0,1,2} matches no branch of :229-247: (x, y) stays put, the bounds test passes and the cube is
 // put back where it stood -- a VALID no-op move (the action space never produces it; parity keeps it).  It is folded
 // into the data path as pseudo-direction 3 (always "on the board", displacement 0) so that the ply stays branch-free.
-template <class C, int BR> EWN_HD bool ply_action(Game<C>& g, const Geo& geo, int larger, int dir, int& t_out, int& sh_out) {
+template <class C, int BR, class G> EWN_HD bool ply_action(Game<C>& g, const G& geo, int larger, int dir, int& t_out, int& sh_out) {
     typename C::W side = BR ? g.br : g.tl;
     Movers m = movers<C>(side, g.dice);
     int sh = cube_to_move(m, larger == 1);
@@ -498,7 +518,7 @@ EWN_HD void playout_block(u64 seed, u32 root_id, u32 child, u32 playout, u32 j, 
 // ------------------------------------------------------------------------------------------------
 // one uniformly random ply (random_policy.py:11-15 / mcts.py:29-35). Returns true if the mover has won.
 // ------------------------------------------------------------------------------------------------
-template <class C, int BR> EWN_HD bool random_ply(Game<C>& g, const Geo& geo, u32 r_index, int* larger_out, int* dir_out) {
+template <class C, int BR, class G> EWN_HD bool random_ply(Game<C>& g, const G& geo, u32 r_index, int* larger_out, int* dir_out) {
     Movers m = movers<C>(BR ? g.br : g.tl, g.dice);
     Legal l = legal<C, BR>(g, geo, m);
     int idx = (int)bounded(r_index, (u32)legal_count(l));
@@ -554,7 +574,7 @@ struct StepOut {
 // term_state: the terminal state (valid when out.term).
 // `geo` and the three mode flags are passed beside `p` so that a kernel can specialise them at compile time while `p`
 // itself stays a read-only kernel parameter (constant bank): nothing of it is copied into registers or local memory.
-template <class C> EWN_HD void step_one_cfg(Game<C>& g, Game<C>& term_state, const StepParams& p, const Geo& geo, const int replay,
+template <class C, class G> EWN_HD void step_one_cfg(Game<C>& g, Game<C>& term_state, const StepParams& p, const G& geo, const int replay,
                                             const int shaped, const int agent_random, const u64 step, long i, int a_larger, int a_dir,
                                             const StepInject& inj, int* tolerance, double* prev_score, StepOut& out) {
     u32 blk[4] = {0, 0, 0, 0};
@@ -655,7 +675,7 @@ EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
 //                     game is not over: minimax.py:22-23 + :64-73 over six identical depth-0 leaves)
 //   earlier levels  : EMM_INTERIOR, or evaluate() if the game ended there (minimax.py:22-23)
 //   a >= #legal     : EMM_ABSENT
-template <class C> EWN_HD void emm_expand_slot(Game<C> g, const Geo& geo, int depth, int heuristic, u32 t, double* v) {
+template <class C, class G> EWN_HD void emm_expand_slot(Game<C> g, const G& geo, int depth, int heuristic, u32 t, double* v) {
     const int m = emm_levels(depth);
     u32 pow36 = (u32)emm_level_size(m) / 6;        // 36^(m-k) at level k; t % pow36 == 0 <=> this slot owns its level-k node
     long off = 0, lvl = 6;

@@ -441,6 +441,18 @@ k_step(const __grid_constant__ StepKArgs ka) {
 #endif
 constexpr int VTPB = EWN_VTPB, VMINB = EWN_VMINB, VITER_MAX = EWN_VITER_MAX;
 
+// fills the per-block table dirs[side][cell] and returns the geometry that reads it (call by all threads, then __syncthreads)
+template <class C, int NTHREADS> __device__ __forceinline__ GeoLut make_geo_lut(const Geo& geo, unsigned char* tab) {
+    for (int c = threadIdx.x; c < C::LUT; c += NTHREADS) {
+        tab[c] = (unsigned char)C::template dirs<SIDE_TL>(geo, c);
+        tab[C::LUT + c] = (unsigned char)C::template dirs<SIDE_BR>(geo, c);
+    }
+    GeoLut gl;
+    static_cast<Geo&>(gl) = geo;
+    gl.lut = (u32)__cvta_generic_to_shared(tab);
+    return gl;
+}
+
 // lane-private scatter of the twelve cubes into the lane's row of a zeroed [32][NN] int16 tile
 template <class C, int NT> __device__ __forceinline__ void scatter_row(const Game<C>& g, const Geo& geo, int16_t* sm, int lane) {
     const int NN = NT ? NT * NT : geo.N * geo.N;
@@ -472,6 +484,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     extern __shared__ uint4 smem_raw[];
     __shared__ unsigned s_won, s_lost, s_row0, s_wcnt[VTPB / 32];
     __shared__ ulonglong2 s_pf[2 * VTPB];
+    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];     // legal-direction set per (side, cell): one LDS per cube
     const ewn_step_args& a = ka.a;
     const int n = (int)a.n;                                        // the host keeps n below 2^31 on this path: 32-bit indices
     const unsigned tid = threadIdx.x;
@@ -489,6 +502,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     // before the PREVIOUS grid has completed and flushed.  Both are no-ops for launches without the PDL attribute.
     asm volatile("griddepcontrol.launch_dependents;");
     if (tid == 0) { s_won = 0; s_lost = 0; }
+    const GeoLut geol = make_geo_lut<C, VTPB>(geo, s_dirs);
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (tid == 0 && a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
     __syncthreads();
@@ -527,7 +541,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             { u32 blk[4]; env_block_rk(ka.p.rk, ka.p.env_id0 + (u64)i, step, TAG_STEP, blk);
               out.reward = 0.0; out.trunc = 0; g.dice = 1 + (int)bounded(blk[0] ^ blk[1] ^ blk[2] ^ blk[3] ^ (u32)(al + ad), 6u); }
 #else
-            step_one_cfg<C>(g, term, ka.p, geo, 0, 0, 0, step, i, al, ad, inj, &tol, &prev, out);
+            step_one_cfg<C>(g, term, ka.p, geol, 0, 0, 0, step, i, al, ad, inj, &tol, &prev, out);
 #endif
             pack(g, a.state, i);
             __stcs(a.reward_f32 + i, (float)out.reward);
@@ -667,6 +681,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* 
 // ------------------------------------------------------------------------------------------------
 template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, double* vals, int64_t n_roots, Geo geo,
                                                                        int depth, int heuristic) {
+    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];
+    const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
+    __syncthreads();
     const int m = emm_levels(depth);
     const u32 slots = (u32)emm_level_size(m);
     const u32 gid = blockIdx.x * (u32)TPB + threadIdx.x;          // host keeps n_roots * slots below 2^31
@@ -675,7 +692,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64
     Game<C> g; unpack(g, state, (long)root);
     g.player = SIDE_TL;
     if (full_win<C>(g, geo)) return;               // finished root: phase 2 evaluates it directly
-    emm_expand_slot<C>(g, geo, depth, heuristic, t, vals + (int64_t)root * emm_level_offset(m + 1));
+    emm_expand_slot<C>(g, geol, depth, heuristic, t, vals + (int64_t)root * emm_level_offset(m + 1));
 }
 
 template <class C, int M> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const double* vals, int64_t n_roots,
@@ -731,6 +748,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
                                                                      const u32* pair_slot, const int* n_pairs_dev, int64_t n_pairs_host,
                                                                      u32 first, u32 count, u32* wins, unsigned long long* plies,
                                                                      Geo geo, const RoundKeys rk) {
+    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];
+    const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);       // legal directions of a cube: one LDS (two cubes per ply)
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int64_t warp_id = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
     const int64_t n_warps = ((int64_t)gridDim.x * TPB) >> 5;
@@ -780,11 +800,11 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
             u32 blk[4];
             playout_block_rk(rk, rid, child, pidx, j++, blk);
             g.dice = 1 + (int)bounded(blk[0], 6u);
-            bool over = random_ply<C, SIDE_BR>(g, geo, blk[1], nullptr, nullptr);
+            bool over = random_ply<C, SIDE_BR>(g, geol, blk[1], nullptr, nullptr);
             my_plies++;
             if (!over) {
                 g.dice = 1 + (int)bounded(blk[2], 6u);
-                over = random_ply<C, SIDE_TL>(g, geo, blk[3], nullptr, nullptr);
+                over = random_ply<C, SIDE_TL>(g, geol, blk[3], nullptr, nullptr);
                 my_plies++;
             }
             if (over) {
