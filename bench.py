@@ -324,7 +324,7 @@ def run_ours(args, rank, world, local_rank):
     from ewn_gym_b200.vec_env import EWNVecEnv
     e2e = None
     if not args.skip_e2e:
-        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank)
+        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank, staged=args.e2e_staged, chunks=args.e2e_chunks)
         env.reset()
         rng = np.random.default_rng(7)
         pool = [np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64) for _ in range(2)]
@@ -343,7 +343,9 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n,
                "d2h_bytes_per_step": (2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8 + 4) * (term_rows // ksteps) + 4, "ms_per_step": 1e3 * tot / ksteps,
                "steps": ksteps, "n_gpus": 1, "terminal_observations_per_step": term_rows // ksteps,
-               "note": "one GPU, host wall clock around EWNVecEnv.step (pinned host buffers, 8 chunks on 3 streams); PCIe-bound"}
+               "note": "one GPU, host wall clock around EWNVecEnv.step: H2D copy of the int64 actions from page-locked memory, k_vstep in 8 chunks on 3 streams, "
+                       + ("results staged in HBM and copied back (D2H)" if args.e2e_staged else "results stored by the kernel straight into the page-locked host buffers over PCIe")
+                       + "; PCIe-bound"}
         env.close()
 
     hbm, peak_src = peaks()
@@ -385,6 +387,8 @@ def main():
     ap.add_argument("--skip-playouts", action="store_true")
     ap.add_argument("--skip-search", action="store_true")
     ap.add_argument("--skip-rollout", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=0, help="pipeline depth of EWNVecEnv.step (0 = library default)")
+    ap.add_argument("--e2e-staged", action="store_true", help="e2e through device staging arrays + D2H copies instead of direct host stores")
     ap.add_argument("--skip-clocks", action="store_true", help="no extended load phase for the clock sampler (profiling runs)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))

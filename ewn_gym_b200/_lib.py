@@ -42,7 +42,7 @@ class VecConfig(C.Structure):
     """struct ewn_vec_config"""
     _fields_ = [
         ("n", i64), ("board_size", i32), ("cube_layer", i32), ("reward", C.c_double), ("illegal_move_reward", C.c_double),
-        ("seed", u64), ("env_id0", u64), ("shaped", i32), ("illegal_move_tolerance", i32), ("chunks", i32), ("device", i32),
+        ("seed", u64), ("env_id0", u64), ("shaped", i32), ("illegal_move_tolerance", i32), ("chunks", i32), ("device", i32), ("flags", i32), ("reserved", i32),
     ]
 
 

@@ -1227,6 +1227,8 @@ struct ewn_vec {
     int words;
     int n_streams;
     cudaStream_t streams[4];
+    cudaStream_t h2d;              // action uploads run ahead of the compute / download streams (PCIe is full duplex)
+    cudaEvent_t ev[64];            // ev[k]: chunk k's actions are on the device
     uint64_t step;
     uint64_t* state;
     int64_t* action;
@@ -1240,6 +1242,8 @@ static void vec_free(ewn_vec* v) {
     if (!v) return;
     cudaSetDevice(v->cfg.device);
     for (int i = 0; i < v->n_streams; i++) if (v->streams[i]) cudaStreamDestroy(v->streams[i]);
+    if (v->h2d) cudaStreamDestroy(v->h2d);
+    for (int i = 0; i < 64; i++) if (v->ev[i]) cudaEventDestroy(v->ev[i]);
     cudaFree(v->state); cudaFree(v->action); cudaFree(v->obs_board); cudaFree(v->obs_dice); cudaFree(v->reward);
     cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->term_index); cudaFree(v->term_count);
     if (v->count_host) cudaFreeHost(v->count_host);
@@ -1263,6 +1267,8 @@ int ewn_vec_create(const ewn_vec_config* cfg, ewn_vec** out) {
     if (e != cudaSuccess) { delete v; return cuda_fail(e, "cudaSetDevice"); }
 #define VEC_TRY(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { int rc = cuda_fail(e__, #call); vec_free(v); return rc; } } while (0)
     for (int i = 0; i < v->n_streams; i++) VEC_TRY(cudaStreamCreateWithFlags(&v->streams[i], cudaStreamNonBlocking));
+    VEC_TRY(cudaStreamCreateWithFlags(&v->h2d, cudaStreamNonBlocking));
+    for (int i = 0; i < v->cfg.chunks; i++) VEC_TRY(cudaEventCreateWithFlags(&v->ev[i], cudaEventDisableTiming));
     VEC_TRY(cudaMalloc(&v->state, (size_t)n * v->words * 8));
     VEC_TRY(cudaMalloc(&v->action, (size_t)n * 16));
     VEC_TRY(cudaMalloc(&v->obs_board, (size_t)n * NN * 2));
@@ -1316,6 +1322,15 @@ int ewn_vec_reset(ewn_vec* v, int16_t* obs_board, int64_t* obs_dice) {
     return EWN_OK;
 }
 
+// device-visible alias of a page-locked host buffer (unified addressing maps every cudaHostAlloc / cudaHostRegister
+// allocation into the device address space), or nullptr if `p` is pageable
+static void* pinned_alias(const void* p) {
+    if (!p) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
+}
+
 int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t* obs_dice, float* reward, uint8_t* done, uint8_t* truncated,
                  int16_t* term_board, int64_t* term_dice, int32_t* term_index, uint32_t* term_count) {
     if (!v || !action) return EWN_EARG;
@@ -1323,38 +1338,60 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
     CU(cudaSetDevice(v->cfg.device));
     const ewn_vec_config& c = v->cfg;
     const int NN = c.board_size * c.board_size;
+    // DIRECT mode: when every output buffer the caller handed in is page-locked, the kernel stores its results straight into
+    // host memory over PCIe (coalesced 16-byte vectors) -- no device staging copy, no D2H memcpy, no pipeline ramp: the step is
+    // one pass that runs at the PCIe write rate.  Pageable buffers take the staged path (device arrays + cudaMemcpyAsync).
+    int16_t* d_board = (int16_t*)pinned_alias(obs_board); int64_t* d_dice = (int64_t*)pinned_alias(obs_dice);
+    float* d_rew = (float*)pinned_alias(reward); uint8_t* d_done = (uint8_t*)pinned_alias(done); uint8_t* d_trunc = (uint8_t*)pinned_alias(truncated);
+    int16_t* d_tb = (int16_t*)pinned_alias(term_board); int64_t* d_td = (int64_t*)pinned_alias(term_dice); int32_t* d_ti = (int32_t*)pinned_alias(term_index);
+    const bool direct = !c.shaped && !(c.flags & EWN_VEC_STAGED) && d_board && d_dice && d_rew && d_done && d_trunc &&
+                        (!term_count || ((!term_board || d_tb) && (!term_dice || d_td) && d_ti));
     // chunk boundaries are multiples of 1024 games so that every chunk starts 16-byte aligned in every array
     int64_t per = (c.n + c.chunks - 1) / c.chunks;
     per = (per + 1023) & ~(int64_t)1023;
     int k = 0;
+    for (int64_t lo = 0; lo < c.n; lo += per, k++) {       // all uploads first, on their own stream: they never queue behind a download
+        const int64_t m = (c.n - lo < per) ? (c.n - lo) : per;
+        CU(cudaMemcpyAsync(v->action + 2 * lo, action + 2 * lo, (size_t)m * 16, cudaMemcpyHostToDevice, v->h2d));
+        CU(cudaEventRecord(v->ev[k], v->h2d));
+    }
+    k = 0;
     for (int64_t lo = 0; lo < c.n; lo += per, k++) {
         const int64_t m = (c.n - lo < per) ? (c.n - lo) : per;
         cudaStream_t st = v->streams[k % v->n_streams];
-        CU(cudaMemcpyAsync(v->action + 2 * lo, action + 2 * lo, (size_t)m * 16, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamWaitEvent(st, v->ev[k], 0));
         ewn_step_args a;
         memset(&a, 0, sizeof(a));
         a.state = v->state + lo * v->words; a.n = m; a.board_size = c.board_size; a.cube_layer = c.cube_layer;
         a.action_i64 = v->action + 2 * lo;
-        a.reward_f32 = v->reward + lo; a.terminated = v->done + lo; a.truncated = v->trunc + lo;
-        a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
+        if (direct) {
+            a.reward_f32 = d_rew + lo; a.terminated = d_done + lo; a.truncated = d_trunc + lo;
+            a.obs_board = d_board + lo * NN; a.obs_dice = d_dice + lo;
+        } else {
+            a.reward_f32 = v->reward + lo; a.terminated = v->done + lo; a.truncated = v->trunc + lo;
+            a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
+        }
         if (term_count) {               // compacted terminal observations, one list for all chunks
-            a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr;
-            a.term_index = v->term_index; a.term_count = v->term_count + (v->step & 1); a.term_index_base = lo;
+            if (direct) { a.term_board = d_tb; a.term_dice = d_td; a.term_index = d_ti; }
+            else { a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr; a.term_index = v->term_index; }
+            a.term_count = v->term_count + (v->step & 1); a.term_index_base = lo;
             if (lo == 0) a.term_count_clear = v->term_count + ((v->step + 1) & 1);
         }
         if (c.shaped) { a.tolerance = v->tolerance + lo; a.prev_score = v->prev_score + lo; a.shaped = 1; }
         a.reward = c.reward; a.illegal_move_reward = c.illegal_move_reward;
         a.seed = c.seed; a.step = v->step; a.env_id0 = c.env_id0 + (uint64_t)lo;
         a.autoreset = 1;
+        a.flags = EWN_STEP_NO_PDL;      // chunks run on different streams: nothing to chain
         int rc = ewn_step(&a, st);
         if (rc) return rc;
+        if (direct) continue;
         if (obs_board) CU(cudaMemcpyAsync(obs_board + lo * NN, v->obs_board + lo * NN, (size_t)m * NN * 2, cudaMemcpyDeviceToHost, st));
         if (obs_dice) CU(cudaMemcpyAsync(obs_dice + lo, v->obs_dice + lo, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
         if (reward) CU(cudaMemcpyAsync(reward + lo, v->reward + lo, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
         if (done) CU(cudaMemcpyAsync(done + lo, v->done + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
         if (truncated) CU(cudaMemcpyAsync(truncated + lo, v->trunc + lo, (size_t)m, cudaMemcpyDeviceToHost, st));
     }
-    // every kernel has run once the first two streams drain their kernels; the count is final after all streams sync
+    // every kernel has run once the streams drain; the append counter is final after all of them
     for (int i = 1; i < v->n_streams; i++) CU(cudaStreamSynchronize(v->streams[i]));
     cudaStream_t s0 = v->streams[0];
     if (term_count) {
@@ -1362,7 +1399,7 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
         CU(cudaStreamSynchronize(s0));
         const uint32_t cnt = *v->count_host;
         *term_count = cnt;
-        if (cnt) {
+        if (cnt && !direct) {
             if (term_board) CU(cudaMemcpyAsync(term_board, v->term_board, (size_t)cnt * NN * 2, cudaMemcpyDeviceToHost, s0));
             if (term_dice) CU(cudaMemcpyAsync(term_dice, v->term_dice, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s0));
             CU(cudaMemcpyAsync(term_index, v->term_index, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s0));

@@ -91,7 +91,7 @@ class EWNVecEnv:
 
     def __init__(self, num_envs: int, board_size: int = 5, cube_layer: int = 3, seed: int = 9487, reward: float = 1.0,
                  shaped: bool = False, illegal_move_reward: float = -1.0, illegal_move_tolerance: int = 10, device: int = 0,
-                 env_id0: int = 0, terminal_observation: bool = True, chunks: int = 0, **_ignored):
+                 env_id0: int = 0, terminal_observation: bool = True, chunks: int = 0, staged: bool = False, **_ignored):
         assert cube_layer < board_size - 1
         self.lib = _lib.lib()
         self.num_envs, self.board_size, self.cube_layer = int(num_envs), int(board_size), int(cube_layer)
@@ -106,7 +106,7 @@ class EWNVecEnv:
             "dice_roll": Discrete(self.cube_num + 1, start=1),
         })
         cfg = _lib.VecConfig(self.num_envs, board_size, cube_layer, self.reward, float(illegal_move_reward), int(seed), int(env_id0),
-                             int(self.shaped), int(illegal_move_tolerance), int(chunks), int(device))
+                             int(self.shaped), int(illegal_move_tolerance), int(chunks), int(device), 1 if staged else 0, 0)
         h = C.c_void_p()
         _lib.check(self.lib.ewn_vec_create(C.byref(cfg), C.byref(h)), "ewn_vec_create", self.lib)
         self._h = h

@@ -212,7 +212,12 @@ typedef struct ewn_vec_config {
     int32_t shaped, illegal_move_tolerance;
     int32_t chunks;               /* pipeline depth (0 = default)                                               */
     int32_t device;               /* CUDA device ordinal                                                        */
+    int32_t flags;                /* EWN_VEC_* bits, 0 = defaults                                               */
+    int32_t reserved;
 } ewn_vec_config;
+/* flags: always stage outputs in device memory and copy them back (default: page-locked output buffers are written by the
+ * kernel directly over PCIe) */
+#define EWN_VEC_STAGED 1
 
 EWN_API int ewn_vec_create(const ewn_vec_config *cfg, ewn_vec **out);
 EWN_API void ewn_vec_destroy(ewn_vec *v);

@@ -7,11 +7,14 @@ from oracle import oracle as O
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("N,L,shaped", [(5, 3, False), (7, 3, True), (5, 3, True), (4, 2, False)])
-def test_vec_env_matches_oracle(N, L, shaped):
+@pytest.mark.parametrize("N,L,shaped,staged", [(5, 3, False, False), (5, 3, False, True), (7, 3, False, False), (7, 3, True, False),
+                                               (5, 3, True, False), (4, 2, False, False)])
+def test_vec_env_matches_oracle(N, L, shaped, staged):
+    """staged = outputs through device staging arrays + D2H copies; default = the kernel writes the page-locked host buffers directly"""
     from ewn_gym_b200.vec_env import EWNVecEnv
     n, seed, env_id0 = 10000 + 123, 321, 7
-    env = EWNVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_reward=-1.0, illegal_move_tolerance=3, env_id0=env_id0, chunks=5)
+    env = EWNVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_reward=-1.0, illegal_move_tolerance=3, env_id0=env_id0, chunks=5,
+                    staged=staged)
     obs = env.reset()
     ob, od = O.reset_philox(n, seed, 0, env_id0, N, L)
     assert obs["board"].dtype == np.int16 and obs["dice_roll"].dtype == np.int64
