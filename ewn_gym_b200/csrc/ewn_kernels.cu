@@ -230,6 +230,41 @@ template <class C> __global__ void __launch_bounds__(TPB) k_set_dice(u64* state,
     pack(g, state, i);
 }
 
+// NN-facing observation (classical_policies/alpha_zero/alpha_zero.py:39-58 ewn_obs_one_hot): board[x][y][k] = +1 where TOP_LEFT's
+// cube k+1 stands, -1 for BOTTOM_RIGHT's, dice one-hot.  One warp per 32 games: the block's tile is zero-filled and written with
+// coalesced float4 stores, then every lane drops its <= 12 non-zeros (and the die) into its own game's row.
+template <class C> __global__ void __launch_bounds__(TPB) k_decode_onehot(const u64* state, float* board, float* dice, int64_t n, Geo geo) {
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    const int cn = geo.cube_num, NN = geo.N * geo.N, row = NN * cn;
+    const int64_t blk0 = (int64_t)blockIdx.x * TPB;
+    const int64_t rows = (n - blk0 < TPB) ? (n - blk0) : TPB;
+    if (rows <= 0) return;
+    {   // zero fill of this block's contiguous slab
+        float* b0 = board + blk0 * row;
+        const int64_t tot = rows * row;
+        if ((reinterpret_cast<uintptr_t>(b0) & 15) == 0) {
+            float4* v = reinterpret_cast<float4*>(b0);
+            for (int64_t k = threadIdx.x; k < (tot >> 2); k += TPB) v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int64_t k = (tot & ~(int64_t)3) + threadIdx.x; k < tot; k += TPB) b0[k] = 0.f;
+        } else {
+            for (int64_t k = threadIdx.x; k < tot; k += TPB) b0[k] = 0.f;
+        }
+        if (dice) { float* d0 = dice + blk0 * cn; for (int64_t k = threadIdx.x; k < rows * cn; k += TPB) d0[k] = 0.f; }
+    }
+    __syncthreads();
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    float* b = board + i * row;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        if (k >= cn) break;
+        const int c = (int)((g.tl >> (C::FB * k)) & C::FM), d = (int)((g.br >> (C::FB * k)) & C::FM);
+        if (c != (int)C::FM) b[(C::x_of(c) * geo.N + C::y_of(c)) * cn + k] = 1.f;
+        if (d != (int)C::FM) b[(C::x_of(d) * geo.N + C::y_of(d)) * cn + k] = -1.f;
+    }
+    if (dice && g.dice >= 1 && g.dice <= cn) dice[i * cn + g.dice - 1] = 1.f;
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_flip(const u64* in, u64* out, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
@@ -1001,6 +1036,17 @@ int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, in
     if (use_p5(N)) k_set_dice<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
     else           k_set_dice<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
     LAUNCHED("k_set_dice");
+    return EWN_OK;
+}
+
+int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t n, int N, int L, void* stream) {
+    if (!state || !board || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_decode_onehot<P5><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
+    else           k_decode_onehot<P8><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
+    LAUNCHED("k_decode_onehot");
     return EWN_OK;
 }
 

@@ -128,6 +128,16 @@ class Engine:
                                       self.xp.stream()), "ewn_decode")
         return (board, dice, player) if want_player else (board, dice)
 
+    def decode_onehot(self, state, want_dice=True):
+        """-> (board f32[n,N,N,cube_num] with +1 / -1, dice f32[n,cube_num] one-hot): the NN-facing observation of
+        alpha_zero.py:39-58 ewn_obs_one_hot"""
+        n = self._n(state)
+        board = self.xp.empty((n, self.N, self.N, self.cube_num), "f32")
+        dice = self.xp.empty((n, self.cube_num), "f32") if want_dice else None
+        self._chk(self.lib.ewn_decode_onehot(self.xp.ptr(state), self.xp.ptr(board), self.xp.ptr(dice), n, self.N, self.L, self.xp.stream()),
+                  "ewn_decode_onehot")
+        return board, dice
+
     # ------------------------------------------------------------------ rules
     def legal(self, state, player: int = 0, want_list=True):
         n = self._n(state)

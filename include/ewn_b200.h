@@ -85,6 +85,11 @@ EWN_API int ewn_encode(const int16_t *board, const int32_t *dice, const int32_t 
 EWN_API int ewn_decode(const uint64_t *state, int16_t *board, int64_t *dice, int32_t *player, int64_t n, int board_size, int cube_layer,
                void *stream);
 
+/* packed state -> the NN-facing observation of classical_policies/alpha_zero/alpha_zero.py:39-58 (ewn_obs_one_hot, also
+ * minimax.py:118-139): board f32[n][N][N][cube_num] with +1 where TOP_LEFT's cube k+1 stands and -1 for BOTTOM_RIGHT's,
+ * dice f32[n][cube_num] one-hot (or NULL).  Combine with ewn_flip for the canonical form of EWNGame.py:85-92. */
+EWN_API int ewn_decode_onehot(const uint64_t *state, float *board, float *dice, int64_t n, int board_size, int cube_layer, void *stream);
+
 /* ---- rules ----------------------------------------------------------------------------------------------- */
 
 /* envs/ewn.py:338-375 get_legal_actions(player).  player: 0 = the state's side to move, 1 / 2 = forced.

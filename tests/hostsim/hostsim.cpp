@@ -323,6 +323,25 @@ int ewn_step(const ewn_step_args* a, void*) {
     Geo geo = make_geo(a->board_size, a->cube_layer);
     return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
 }
+int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t n, int N, int L, void*) {
+    if (!state || !board || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    const int cn = geo.cube_num, row = N * N * cn;
+    for (int64_t i = 0; i < n; i++) {
+        float* b = board + i * row;
+        for (int k = 0; k < row; k++) b[k] = 0.f;
+        int64_t tl, br; int dice_v;
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); dice_v = g.dice;
+            for (int k = 0; k < cn; k++) { int c = (g.tl >> (5 * k)) & 31, d = (g.br >> (5 * k)) & 31;
+                if (c != 31) b[(P5::x_of(c) * N + P5::y_of(c)) * cn + k] = 1.f; if (d != 31) b[(P5::x_of(d) * N + P5::y_of(d)) * cn + k] = -1.f; } }
+        else { Game<P8> g; unpack(g, state, i); dice_v = g.dice;
+            for (int k = 0; k < cn; k++) { int c = (int)((g.tl >> (8 * k)) & 255), d = (int)((g.br >> (8 * k)) & 255);
+                if (c != 255) b[(P8::x_of(c) * N + P8::y_of(c)) * cn + k] = 1.f; if (d != 255) b[(P8::x_of(d) * N + P8::y_of(d)) * cn + k] = -1.f; } }
+        (void)tl; (void)br;
+        if (dice) { for (int k = 0; k < cn; k++) dice[i * cn + k] = 0.f; if (dice_v >= 1 && dice_v <= cn) dice[i * cn + dice_v - 1] = 1.f; }
+    }
+    return EWN_OK;
+}
 int ewn_flip(const uint64_t* state, uint64_t* out, int64_t n, int N, int L, void*) {
     if (!state || !out || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);

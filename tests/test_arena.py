@@ -86,3 +86,24 @@ def test_pair_win_rates_match_the_reference(backend, case):
     p = (r["agent_wins"] + ref["agent_wins"]) / (n + ref["games"])
     z = (p1 - p2) / (p * (1 - p) * (1 / n + 1 / ref["games"])) ** 0.5
     assert abs(z) < 3.29, (case, p1, p2, z)
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("N,L", [(5, 3), (7, 3), (4, 2)])
+def test_onehot_observation_matches_reference_encoding(backend, N, L):
+    """alpha_zero.py:39-58 ewn_obs_one_hot restated on the decoded int16 board (board[i, j, |v|-1] = sign(v), dice one-hot)"""
+    e = make_engine(backend, N, L)
+    n = 777
+    st = e.reset(n, seed=6)
+    for t in range(1, 7):
+        e.step(st, None, seed=6, step=t, agent_random=True, want=())
+    b, d = (to_np(x) for x in e.decode(st))
+    ob, od = (to_np(x) for x in e.decode_onehot(st))
+    cn = L * (L + 1) // 2
+    ref = np.zeros((n, N, N, cn), np.float32)
+    g, i, j = np.nonzero(b)
+    v = b[g, i, j]
+    ref[g, i, j, np.abs(v) - 1] = np.sign(v)
+    rd = np.zeros((n, cn), np.float32)
+    rd[np.arange(n), d - 1] = 1
+    assert ob.dtype == np.float32 and np.array_equal(ob, ref) and np.array_equal(od, rd)
