@@ -348,3 +348,37 @@ def test_device_step_counter(backend):
         for k in want:
             assert np.array_equal(to_np(ra[k]), to_np(rb[k])), (t, k)
     assert int(to_np(ctr)[0]) == 6
+
+
+@pytest.mark.parametrize("N,L", [(3, 1), (4, 1), (4, 2), (5, 1), (5, 2), (6, 3), (8, 3), (9, 3), (9, 1), (6, 2)])
+def test_every_supported_board_size(backend, N, L):
+    """3 <= board_size <= 9 with every cube_layer < board_size - 1 (envs/ewn.py:47): both codecs (one word up to 5x5, two words above),
+    the run-time-N kernel instantiations, VecEnv surface + generic surface, legal lists, and search / playouts where the reference
+    allows them (six-face die: cube_layer 3)."""
+    e = make_engine(backend, N, L)
+    n, seed = 1500, 17
+    st = e.reset(n, seed=seed)
+    ob, od = O.reset_philox(n, seed, 0, 0, N, L)
+    assert np.array_equal(to_np(e.decode(st)[0]), ob)
+    rng = np.random.default_rng(N * 10 + L)
+    for t in range(1, 13):
+        act = np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+        want = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice") + (("code",) if t % 2 else ())
+        out = e.step(st, e.xp.asarray(act, "i64"), seed=seed, step=t, want=want)
+        ref = O.step_philox(ob, od, act, seed, t, 0, N, L)
+        assert np.array_equal(to_np(out["obs_board"]), ref["board"]) and np.array_equal(to_np(out["obs_dice"]), ref["dice"]), t
+        assert np.array_equal(to_np(out["terminated"]), ref["terminated"]) and np.array_equal(to_np(out["truncated"]), ref["truncated"])
+        assert np.array_equal(to_np(out["reward_f32"]), ref["reward"].astype(np.float32))
+        ob, od = ref["board"], ref["dice"]
+        for player in (1, 2):
+            mask, lst, cnt = (to_np(x) for x in e.legal(st, player))
+            rm, rl, rc = O.legal(ob, od, player, N, L)
+            assert np.array_equal(cnt, rc) and np.array_equal(lst, rl) and np.array_equal(mask, rm)
+    if L == 3:
+        m = 200
+        v, a = e.expectiminimax(e.encode(ob[:m], od[:m]), 3)
+        ov, oa, _ = O.expectiminimax(ob[:m], od[:m], 3, N=N, L=L)
+        assert np.array_equal(to_np(v).view(np.uint64), ov.view(np.uint64)) and np.array_equal(to_np(a), oa)
+        w, nch = e.mc_root_wins(e.encode(ob[:m], od[:m]), seed=3, first=0, count=16)
+        ow, onch, _ = O.mc_root_wins(ob[:m], od[:m], np.arange(m, dtype=np.uint32), 3, 0, 16, N=N, L=L)
+        assert np.array_equal(to_np(w).astype(np.uint32), ow) and np.array_equal(to_np(nch), onch)
