@@ -126,7 +126,10 @@ struct Geo {
 
 // Geo plus the shared-memory address of a per-block table  dirs[side][cell]  (k_vstep, k_playouts): the legal-direction set of
 // a cube becomes one LDS instead of ~9 integer instructions.  Functions below are generic in the geometry type G.
-struct GeoLut : Geo { u32 lut; };
+struct GeoLut : Geo {
+    u32 lut;              // shared address of dirs[2][C::LUT]; the table min(x, y)[C::LUT] (dead cube: -1) follows it
+    const double* vt;     // optional global table of 'hybrid' leaf values (k_emm_table), nullptr = compute
+};
 
 enum { SIDE_TL = 0, SIDE_BR = 1 };
 enum { H_HYBRID = 0, H_MIN_DIST = 1, H_TWO_MIN_DIST = 2, H_ATTK = 3 };
@@ -462,6 +465,49 @@ EWN_HD double six_fold(double v) {
     return e;
 }
 
+// 'hybrid' leaf values as a table: the heuristic depends on (1 + max min(x,y), #cubes) of either side only (minimax_ewn.py:79-86),
+// i.e. on at most N*6*N*6 combinations.  vt[fold][pb][pc-1][nb][nc-1], fold = the value after minimax.py:65-73 over six identical
+// leaves.  The entries are produced on the device by the very same f64_mul / f64_sub / six_fold calls, so they are bit-identical.
+EWN_HD long emm_table_index(int N, int fold, int pb, int pc, int nb, int nc) {
+    return ((((long)fold * N + pb) * 6 + (pc - 1)) * N + nb) * 6 + (nc - 1);
+}
+EWN_HD long emm_table_size(int N) { return 2L * N * 6 * N * 6; }
+EWN_HD double emm_table_entry(int N, long idx) {
+    int nc = 1 + (int)(idx % 6); idx /= 6;
+    int nb = (int)(idx % N); idx /= N;
+    int pc = 1 + (int)(idx % 6); idx /= 6;
+    int pb = (int)(idx % N); idx /= N;
+    double a = f64_mul((double)(1 + pb), inv_count(pc)), b = f64_mul((double)(1 + nb), inv_count(nc));
+    double v = f64_sub(a, b);
+    return idx ? six_fold(v) : v;
+}
+// value stored for a position reached by a move of side `mover_br` (over = that move won), six-folded when `fold`
+template <class C> EWN_HD double leaf_value(const Game<C>& g, const Geo& geo, int heuristic, bool over, int mover_br, bool fold) {
+    (void)over; (void)mover_br;
+    double e = evaluate<C>(g, geo, heuristic);
+    return fold ? six_fold(e) : e;
+}
+template <class C> EWN_HD double leaf_value(const Game<C>& g, const GeoLut& geo, int heuristic, bool over, int mover_br, bool fold) {
+#if defined(__CUDA_ARCH__)
+    if (heuristic == H_HYBRID && geo.vt) {
+        // a move that does not win from a live position leaves a live position: evaluate()'s terminal tests are `over`
+        if (over) return mover_br ? -10.0 : 10.0;                          // minimax_ewn.py:42-47 (never six-folded: fold implies !over)
+        int pb = -1, nb = -1;
+        const u32 mn = geo.lut + 2u * (u32)C::LUT;
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            int a, b;
+            asm("ld.shared.s8 %0, [%1];" : "=r"(a) : "r"(mn + (u32)((g.tl >> (C::FB * k)) & C::FM)));
+            asm("ld.shared.s8 %0, [%1];" : "=r"(b) : "r"(mn + (u32)((g.br >> (C::FB * k)) & C::FM)));
+            pb = a > pb ? a : pb; nb = b > nb ? b : nb;
+        }
+        const int pc = popc(C::dead(g.tl) ^ C::ONES), nc = popc(C::dead(g.br) ^ C::ONES);
+        return __ldg(geo.vt + emm_table_index(geo.N, fold ? 1 : 0, pb, pc, nb, nc));
+    }
+#endif
+    return leaf_value<C>(g, static_cast<const Geo&>(geo), heuristic, over, mover_br, fold);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Philox4x32-10 (Salmon et al., SC'11) and the draw schedule (DESIGN.md "RNG schedule")
 // ------------------------------------------------------------------------------------------------
@@ -696,12 +742,10 @@ template <class C, class G> EWN_HD void emm_expand_slot(Game<C> g, const G& geo,
         }
         if (a >= cnt) { if (owner) v[off + idx] = bits_to_f64(EMM_ABSENT); return; }
         if (k == m) {
-            double e = evaluate<C>(g, geo, heuristic);
-            if (!(depth & 1) && !over) e = six_fold(e);
-            v[off + idx] = e;
+            v[off + idx] = leaf_value<C>(g, geo, heuristic, over, (k & 1) ? 0 : 1, !(depth & 1) && !over);
             return;
         }
-        if (over) { if (owner) v[off + idx] = evaluate<C>(g, geo, heuristic); return; }
+        if (over) { if (owner) v[off + idx] = leaf_value<C>(g, geo, heuristic, true, (k & 1) ? 0 : 1, false); return; }
         if (owner) v[off + idx] = bits_to_f64(EMM_INTERIOR);
         off += lvl; lvl *= 36; pow36 /= 36;
     }

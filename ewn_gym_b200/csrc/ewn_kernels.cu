@@ -481,10 +481,13 @@ template <class C, int NTHREADS> __device__ __forceinline__ GeoLut make_geo_lut(
     for (int c = threadIdx.x; c < C::LUT; c += NTHREADS) {
         tab[c] = (unsigned char)C::template dirs<SIDE_TL>(geo, c);
         tab[C::LUT + c] = (unsigned char)C::template dirs<SIDE_BR>(geo, c);
+        const int x = C::x_of(c), y = C::y_of(c);
+        tab[2 * C::LUT + c] = (unsigned char)(signed char)(c == (int)C::FM ? -1 : (x < y ? x : y));   // min(x, y), dead cube: -1
     }
     GeoLut gl;
     static_cast<Geo&>(gl) = geo;
     gl.lut = (u32)__cvta_generic_to_shared(tab);
+    gl.vt = nullptr;
     return gl;
 }
 
@@ -519,7 +522,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     extern __shared__ uint4 smem_raw[];
     __shared__ unsigned s_won, s_lost, s_row0, s_wcnt[VTPB / 32];
     __shared__ ulonglong2 s_pf[2 * VTPB];
-    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];     // legal-direction set per (side, cell): one LDS per cube
+    __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];     // legal-direction set per (side, cell): one LDS per cube
     const ewn_step_args& a = ka.a;
     const int n = (int)a.n;                                        // the host keeps n below 2^31 on this path: 32-bit indices
     const unsigned tid = threadIdx.x;
@@ -714,10 +717,16 @@ template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* 
 // no inter-thread communication.  Phase 2 (k_emm_replay): one thread per root replays minimax.py:19-73 over the
 // stored values, so the reference's window hand-through at chance nodes is reproduced bit for bit.
 // ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPB) k_emm_table(double* vt, int N) {
+    const long i = (long)blockIdx.x * TPB + threadIdx.x;
+    if (i < emm_table_size(N)) vt[i] = emm_table_entry(N, i);
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, double* vals, int64_t n_roots, Geo geo,
-                                                                       int depth, int heuristic) {
-    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];
-    const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
+                                                                       int depth, int heuristic, const double* vt) {
+    __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
+    GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
+    geol.vt = vt;
     __syncthreads();
     const int m = emm_levels(depth);
     const u32 slots = (u32)emm_level_size(m);
@@ -783,7 +792,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
                                                                      const u32* pair_slot, const int* n_pairs_dev, int64_t n_pairs_host,
                                                                      u32 first, u32 count, u32* wins, unsigned long long* plies,
                                                                      Geo geo, const RoundKeys rk) {
-    __shared__ __align__(16) unsigned char s_dirs[2 * C::LUT];
+    __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
     const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);       // legal directions of a cube: one LDS (two cubes per ply)
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -1158,6 +1167,23 @@ size_t ewn_expectiminimax_workspace(int64_t n, int depth) {
     return (size_t)n * (size_t)emm_level_offset(emm_levels(depth) + 1) * sizeof(double);
 }
 
+// 'hybrid' leaf-value table of one board size, built once per device on first use (k_emm_table) and kept for the process
+static const double* emm_value_table(int N, cudaStream_t st) {
+    static double* tab[64][EWN_MAX_BOARD + 1] = {{nullptr}};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!tab[dev][N]) {
+        double* p = nullptr;
+        const long cnt = emm_table_size(N);
+        if (cudaMalloc(&p, (size_t)cnt * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        k_emm_table<<<(unsigned)((cnt + TPB - 1) / TPB), TPB, 0, st>>>(p, N);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        if (cudaStreamSynchronize(st) != cudaSuccess) { cudaGetLastError(); cudaFree(p); return nullptr; }
+        tab[dev][N] = p;
+    }
+    return tab[dev][N];
+}
+
 int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth, int heuristic, int pruned, double* value, int8_t* action,
                        void* workspace, size_t workspace_bytes, void* stream) {
     if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
@@ -1167,6 +1193,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
     const int m = emm_levels(depth);
+    const double* vt = heuristic == H_HYBRID ? emm_value_table(N, st) : nullptr;      // nullptr: leaves are computed in place
     const size_t per_root = (size_t)emm_level_offset(m + 1) * sizeof(double);
     if (!workspace || workspace_bytes == 0) {
         size_t want = per_root * (size_t)n;
@@ -1188,7 +1215,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
         double* vals = (double*)workspace;
 #define LAUNCH_EMM(C)                                                                                              \
     do {                                                                                                           \
-        k_emm_expand<C><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic);                               \
+        k_emm_expand<C><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic, vt);                               \
         LAUNCHED("k_emm_expand");                                                                                  \
         switch (m) {                                                                                               \
             case 1: k_emm_replay<C, 1><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
