@@ -316,37 +316,40 @@ def run_ours(args, rank, world, local_rank):
         rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
                                "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
 
-    if rank != 0:
-        if dist: dist.destroy_process_group()
-        return
-
-    # ---- e2e through the public host-buffer API (EWNVecEnv.step: pinned host actions in, host observations out)
+    # ---- e2e through the public host-buffer API (EWNVecEnv.step: pinned host actions in, host observations out), every rank at once
     from ewn_gym_b200.vec_env import EWNVecEnv
     e2e = None
     if not args.skip_e2e:
-        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank, staged=args.e2e_staged, chunks=args.e2e_chunks)
+        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank, env_id0=env_id0, staged=args.e2e_staged, chunks=args.e2e_chunks)
         env.reset()
-        rng = np.random.default_rng(7)
+        rng = np.random.default_rng(7 + rank)
         pool = [np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64) for _ in range(2)]
         abuf = env.action_buffer
         for k in range(3):
             abuf[...] = pool[k % 2]; env.step(abuf)
         ksteps = max(3, min(args.steps, 20))
         tot, term_rows = 0.0, 0
+        if dist: dist.barrier()
         for k in range(ksteps):
             abuf[...] = pool[k % 2]                  # the policy's output lands in page-locked memory (untimed)
             t0 = time.perf_counter()
             obs, rew, done, infos = env.step(abuf)   # H2D actions + kernel + D2H obs/reward/done/terminal obs, synchronous
             tot += time.perf_counter() - t0
             term_rows += int(env._b["tcount"].array[0])
+        if dist:                                     # whole job: all ranks step their own games over their own PCIe link; slowest rank counts
+            tt = torch.tensor([tot], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); tot = float(tt.item())
         nn = N_BOARD * N_BOARD
-        e2e = {"value": n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n,
-               "d2h_bytes_per_step": (2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8 + 4) * (term_rows // ksteps) + 4, "ms_per_step": 1e3 * tot / ksteps,
-               "steps": ksteps, "n_gpus": 1, "terminal_observations_per_step": term_rows // ksteps,
-               "note": "one GPU, host wall clock around EWNVecEnv.step: H2D copy of the int64 actions from page-locked memory, k_vstep in 8 chunks on 3 streams, "
+        e2e = {"value": world * n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n * world,
+               "d2h_bytes_per_step": ((2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8 + 4) * (term_rows // ksteps) + 4) * world, "ms_per_step": 1e3 * tot / ksteps,
+               "steps": ksteps, "n_gpus": world, "terminal_observations_per_step": term_rows // ksteps,
+               "note": "host wall clock around EWNVecEnv.step on every rank (max over ranks): H2D copy of the int64 actions from page-locked memory, k_vstep in 8 chunks on 3 streams, "
                        + ("results staged in HBM and copied back (D2H)" if args.e2e_staged else "results stored by the kernel straight into the page-locked host buffers over PCIe")
                        + "; PCIe-bound"}
         env.close()
+
+    if rank != 0:
+        if dist: dist.destroy_process_group()
+        return
 
     hbm, peak_src = peaks()
     achieved = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
