@@ -597,6 +597,78 @@ template <class C> EWN_HD int playout(Game<C> g, const Geo& geo, u64 seed, u32 r
 }
 
 // ------------------------------------------------------------------------------------------------
+// The reference's OWN random stream: numpy's legacy global RandomState, i.e. MT19937 seeded by `np.random.seed(seed)`
+// (init_genrand) and `np.random.randint(low, high)` = masked rejection sampling on 32-bit draws (numpy
+// random/src/distributions: buffered_bounded_masked_uint32; a range of one value consumes no draw).  With it the whole
+// eval_random.py game of a seed is reproduced from the seed alone -- dice (envs/ewn.py:90-92), agent and opponent picks
+// (random_policy.py:12-14) in the consumption order of SURVEY 3.5-20 -- without any recorded log.
+// ------------------------------------------------------------------------------------------------
+struct MT19937 {
+    u32 mt[624];
+    int idx;
+    EWN_HD void seed(u32 s) {
+        mt[0] = s;
+        for (int i = 1; i < 624; i++) mt[i] = 1812433253u * (mt[i - 1] ^ (mt[i - 1] >> 30)) + (u32)i;
+        idx = 624;
+    }
+    EWN_HD void twist() {
+        for (int k = 0; k < 624; k++) {
+            const u32 y = (mt[k] & 0x80000000u) | (mt[k == 623 ? 0 : k + 1] & 0x7fffffffu);
+            mt[k] = mt[k < 227 ? k + 397 : k - 227] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+        }
+        idx = 0;
+    }
+    EWN_HD u32 next() {
+        if (idx >= 624) twist();
+        u32 y = mt[idx++];
+        y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+        return y;
+    }
+    EWN_HD int randint(int low, int high) {                    // np.random.randint(low, high): uniform on [low, high)
+        const u32 rng = (u32)(high - 1 - low);
+        if (rng == 0) return low;
+        u32 mask = rng;
+        mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+        for (;;) { const u32 v = next() & mask; if (v <= rng) return low + (int)v; }
+    }
+};
+
+// eval_random.py:17-51 for ONE seed: env.reset(seed) (np.random.seed + first die, envs/ewn.py:488-494), then RandomAgent vs the
+// env's RandomAgent opponent until the game ends.  Returns +1 (agent = TOP_LEFT won) or -1; g = final position.
+// trace: FNV-1a over the per-step log (dice at the agent's turn, agent action, die :458, opponent action, die :483) so that
+// the whole trajectory can be compared with the recorded one, not only its result.
+EWN_HD void trace_mix(u64& h, int v) { h = (h ^ (u64)(u32)(v & 0xff)) * 0x100000001b3ull; }
+template <class C> EWN_HD int numpy_random_game(Game<C>& g, const Geo& geo, u32 seed, MT19937& rng, int& agent_steps, u64& trace) {
+    rng.seed(seed);
+    setup<C>(g, geo, rng.randint(1, geo.cube_num + 1));
+    agent_steps = 0;
+    trace = 0xcbf29ce484222325ull;
+    for (;;) {
+        int la, di, sh, t;
+        {
+            Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+            legal_pick(l, rng.randint(0, legal_count(l)), la, di, sh);
+            trace_mix(trace, g.dice); trace_mix(trace, la); trace_mix(trace, di);
+            t = apply_move<C, SIDE_TL>(g, sh, di);
+            agent_steps++;
+            if (win_after<C, SIDE_TL>(g, geo, t)) return 1;                       // envs/ewn.py:451-454
+        }
+        g.player = SIDE_BR;
+        g.dice = rng.randint(1, geo.cube_num + 1);                               // :458
+        {
+            Legal l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
+            legal_pick(l, rng.randint(0, legal_count(l)), la, di, sh);
+            trace_mix(trace, g.dice); trace_mix(trace, la); trace_mix(trace, di);
+            t = apply_move<C, SIDE_BR>(g, sh, di);
+            if (win_after<C, SIDE_BR>(g, geo, t)) return -1;                      // :475-478
+        }
+        g.player = SIDE_TL;
+        g.dice = rng.randint(1, geo.cube_num + 1);                               // :483
+        trace_mix(trace, g.dice);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // env step, envs/ewn.py:436-486 (+ envs/training_ewn.py:40-99 when shaped). Agent = TOP_LEFT.
 // ------------------------------------------------------------------------------------------------
 struct StepParams {

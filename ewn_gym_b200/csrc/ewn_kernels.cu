@@ -265,6 +265,21 @@ template <class C> __global__ void __launch_bounds__(TPB) k_decode_onehot(const 
     if (dice && g.dice >= 1 && g.dice <= cn) dice[i * cn + g.dice - 1] = 1.f;
 }
 
+// eval_random.py from seeds alone: one thread per game, the reference's MT19937 stream in local memory (2.5 KB per thread)
+template <class C> __global__ void __launch_bounds__(128) k_numpy_random_games(const u32* seeds, int64_t n, Geo geo, int8_t* result,
+                                                                               int32_t* agent_steps, u64* final_state, u64* trace) {
+    const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    if (i >= n) return;
+    MT19937 rng;
+    Game<C> g;
+    int steps; u64 h;
+    const int r = numpy_random_game<C>(g, geo, seeds[i], rng, steps, h);
+    if (result) result[i] = (int8_t)r;
+    if (agent_steps) agent_steps[i] = steps;
+    if (final_state) pack(g, final_state, i);
+    if (trace) trace[i] = h;
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_flip(const u64* in, u64* out, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
@@ -1056,6 +1071,19 @@ int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t 
     if (use_p5(N)) k_decode_onehot<P5><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
     else           k_decode_onehot<P8><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
     LAUNCHED("k_decode_onehot");
+    return EWN_OK;
+}
+
+int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_t* result, int32_t* agent_steps, uint64_t* final_state,
+                           uint64_t* trace, void* stream) {
+    if (!seeds || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned grid = (unsigned)((n + 127) / 128);
+    if (use_p5(N)) k_numpy_random_games<P5><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
+    else           k_numpy_random_games<P8><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
+    LAUNCHED("k_numpy_random_games");
     return EWN_OK;
 }
 

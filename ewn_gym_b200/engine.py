@@ -169,6 +169,17 @@ class Engine:
                   "ewn_set_dice")
         return state
 
+    def numpy_random_games(self, seeds):
+        """eval_random.py's games for `seeds`, reproduced from the seeds alone (the reference's MT19937 / randint stream).
+        -> (result i8[n] +1/-1, agent_steps i32[n], final_state, trace u64[n])"""
+        sd = self.xp.asarray(seeds, "u32")
+        n = int(sd.shape[0])
+        res, steps = self.xp.empty((n,), "i8"), self.xp.empty((n,), "i32")
+        fin, tr = self.new_state(n), self.xp.empty((n,), "u64")
+        self._chk(self.lib.ewn_numpy_random_games(self.xp.ptr(sd), n, self.N, self.L, self.xp.ptr(res), self.xp.ptr(steps), self.xp.ptr(fin),
+                                                  self.xp.ptr(tr), self.xp.stream()), "ewn_numpy_random_games")
+        return res, steps, fin, tr
+
     def flip(self, state, out=None):
         """the position as the other side sees it: np.rot90(-board, 2), side to move mirrored (envs/ewn.py:289-296)"""
         n = self._n(state)

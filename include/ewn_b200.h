@@ -174,6 +174,14 @@ EWN_API int ewn_step(const ewn_step_args *args, void *stream);
 /* *counter += k on `stream` (one tiny kernel; capturable).  See ewn_step_args.step_dev. */
 EWN_API int ewn_counter_add(uint64_t *counter, uint64_t k, void *stream);
 
+/* eval_random.py:17-51 evaluation() for n seeds, from the seeds ALONE: every game draws its dice (envs/ewn.py:90-92) and both
+ * random players' picks (random_policy.py:12-14) from the reference's own stream -- numpy's legacy global RandomState, MT19937
+ * seeded by np.random.seed(seed) in env.reset(seed) (:488-494), np.random.randint by masked rejection -- in the reference's
+ * consumption order.  result int8[n] (+1 agent = TOP_LEFT won, -1 lost), agent_steps int32[n] (env.step calls), final_state
+ * (packed, ewn_decode gives the last board), trace u64[n] (FNV-1a over the per-step dice / action log).  Any output may be NULL. */
+EWN_API int ewn_numpy_random_games(const uint32_t *seeds, int64_t n, int board_size, int cube_layer, int8_t *result, int32_t *agent_steps,
+                           uint64_t *final_state, uint64_t *trace, void *stream);
+
 /* ---- search ---------------------------------------------------------------------------------------------- */
 
 /* envs/minimax_ewn.py:29-213 evaluate(heuristic) -> f64[n] */

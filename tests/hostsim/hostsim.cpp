@@ -323,6 +323,21 @@ int ewn_step(const ewn_step_args* a, void*) {
     Geo geo = make_geo(a->board_size, a->cube_layer);
     return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
 }
+int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_t* result, int32_t* agent_steps, uint64_t* final_state,
+                           uint64_t* trace, void*) {
+    if (!seeds || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    MT19937 rng;
+    for (int64_t i = 0; i < n; i++) {
+        int steps; u64 h; int r;
+        if (use_p5(N)) { Game<P5> g; r = numpy_random_game<P5>(g, geo, seeds[i], rng, steps, h); if (final_state) pack(g, final_state, i); }
+        else           { Game<P8> g; r = numpy_random_game<P8>(g, geo, seeds[i], rng, steps, h); if (final_state) pack(g, final_state, i); }
+        if (result) result[i] = (int8_t)r;
+        if (agent_steps) agent_steps[i] = steps;
+        if (trace) trace[i] = h;
+    }
+    return EWN_OK;
+}
 int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t n, int N, int L, void*) {
     if (!state || !board || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);

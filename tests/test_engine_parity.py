@@ -382,3 +382,44 @@ def test_every_supported_board_size(backend, N, L):
         w, nch = e.mc_root_wins(e.encode(ob[:m], od[:m]), seed=3, first=0, count=16)
         ow, onch, _ = O.mc_root_wins(ob[:m], od[:m], np.arange(m, dtype=np.uint32), 3, 0, 16, N=N, L=L)
         assert np.array_equal(to_np(w).astype(np.uint32), ow) and np.array_equal(to_np(nch), onch)
+
+
+@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz"])
+def test_eval_random_from_seeds_alone(backend, name):
+    """ewn_numpy_random_games: the reference's eval_random.py games reproduced from the SEEDS (numpy legacy MT19937 + randint in
+    the reference's consumption order) -- result, number of env.step calls, final board and the whole dice / action log (as a hash)
+    of every recorded game; 5x5 seeds 0..9999 give the survey's 5,215 wins / 108,978 agent steps."""
+    d = load(name)
+    N, L = int(d["N"]), int(d["L"])
+    e = make_engine(backend, N, L)
+    n_games = len(d["game_steps"])
+    res, steps, fin, tr = e.numpy_random_games(np.arange(n_games, dtype=np.uint32))
+    res, steps, tr = to_np(res), to_np(steps), to_np(tr).view(np.uint64)
+    assert np.array_equal(res, d["game_rewards"].astype(np.int8)) and np.array_equal(steps, d["game_steps"])
+    last = np.cumsum(d["game_steps"]) - 1
+    assert np.array_equal(to_np(e.decode(fin)[0]), d["boards"][last].astype(np.int16))
+    rows = d["steps"]
+    M = (1 << 64) - 1
+    h = [0xcbf29ce484222325] * n_games
+    for game, da, a0, a1, do, o0, o1, dn, term, trunc, _ in rows.tolist():
+        x = h[game]
+        vals = [da, a0, a1] + ([do, o0, o1] if do else []) + ([dn] if dn else [])
+        for v in vals:
+            x = ((x ^ (v & 0xff)) * 0x100000001b3) & M
+        h[game] = x
+    assert np.array_equal(tr, np.array(h, dtype=np.uint64))
+    if name == "random_games_5x5.npz":
+        assert int((res > 0).sum()) == 5215 and int(steps.sum()) == 108978          # SURVEY 8c
+
+
+def test_eval_random_aggregate_counts_from_seeds(backend):
+    """120,000 more reference games (tests/golden/random_vs_random_stats.json: seeds 100000.. on 5x5 and 7x7, played by the unmodified
+    reference) reproduced from their seeds: exact win and agent-step totals."""
+    import json, os
+    ref = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "random_vs_random_stats.json")))
+    for key, N in (("5x5", 5), ("7x7", 7)):
+        r = ref[key]
+        e = make_engine(backend, N, 3)
+        seeds = np.arange(r["first_seed"], r["first_seed"] + r["games"], dtype=np.uint32)
+        res, steps, _, _ = e.numpy_random_games(seeds)
+        assert int((to_np(res) > 0).sum()) == r["wins"] and int(to_np(steps).sum()) == r["agent_steps"], key

@@ -31,12 +31,27 @@ def main():
     ap.add_argument("--cube_layer", "-cl", type=int, default=3)
     ap.add_argument("--eval_num", "-n", type=int, default=10000)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--numpy-exact", action="store_true",
+                    help="replay the reference's own random stream (np.random.seed(seed) per game, seeds 0..eval_num-1): the same games, "
+                         "dice and results as eval_random.py, from the seeds alone")
     args, _ = ap.parse_known_args()
 
     import torch
     from ewn_gym_b200.engine import Engine
     e = Engine(args.board_size, args.cube_layer)
     n = args.eval_num
+    if args.numpy_exact:
+        seeds = torch.arange(n, dtype=torch.int64, device="cuda").to(torch.int32)
+        e.numpy_random_games(seeds[:32]); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res, steps, _, _ = e.numpy_random_games(seeds)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        wins, agent_steps = int((res > 0).sum()), int(steps.sum())
+        lo, hi = wilson(wins, n)
+        print(f"[numpy-exact] games {n} (seeds 0..{n - 1})  wins {wins}  losses {n - wins}  win rate {wins / n:.4f}  95% CI [{lo:.4f}, {hi:.4f}]")
+        print(f"[numpy-exact] agent steps {agent_steps} ({agent_steps / n:.2f} per game)  1 kernel launch  wall {dt:.4f} s  {n / dt:.0f} games/s")
+        return
     t0 = time.perf_counter()
     state = e.reset(n, seed=args.seed)
     stats = torch.zeros(4, dtype=torch.int64, device=state.device)
