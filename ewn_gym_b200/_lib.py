@@ -64,6 +64,8 @@ PROTOTYPES = {
     "ewn_set_dice": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_decode_onehot": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_numpy_random_games": (C.c_int, [p_void, i64, C.c_int, C.c_int, p_void, p_void, p_void, p_void, p_void]),
+    "ewn_numpy_stream": (C.c_int, [p_void, i64, C.c_int, p_void, p_void]),
+    "ewn_numpy_draw": (C.c_int, [p_void, p_void, p_void, C.c_int, i64, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void]),
     "ewn_flip": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_random_action": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
     "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),

@@ -136,6 +136,54 @@ def play_matches(engine: Engine, agent: BatchPolicy, opponent: BatchPolicy, n_ga
             "plies": plies, "winner": w, "n": n}
 
 
+class NumpyRandom(BatchPolicy):
+    """marker policy for play_matches_numpy: the reference's RandomAgent drawing from the game's own numpy stream"""
+    name = "random(numpy stream)"
+
+
+def play_matches_numpy(engine: Engine, agent: BatchPolicy, opponent: BatchPolicy, seeds, max_plies: int = 400):
+    """The reference's evaluation loop (eval_random.py / eval_minimax.py:17-51) for the given seeds with the reference's OWN random
+    stream: game i seeds numpy's global MT19937 with seeds[i] in env.reset (envs/ewn.py:488-494) and then draws, in this order, the
+    first die (:108), per step the agent's pick if it is a RandomAgent, the die at :458, the opponent's pick if it is a RandomAgent,
+    the die at :483.  A deterministic policy (MinimaxPolicy) on the other seat draws nothing, so whole games -- and therefore win
+    counts -- are reproduced exactly.  `agent` / `opponent`: NumpyRandom() or any deterministic BatchPolicy."""
+    e, ops = engine, _Ops(engine, 0)
+    sd = np.asarray(seeds)
+    n = len(sd)
+    raw, cur = e.numpy_stream(sd.astype(np.uint32))
+    state = e.reset_dice(np.ones(n, np.int32))
+    e.numpy_draw(state, raw, cur, roll_dice=True)                                # first roll of env.reset
+    winner = ops.zeros(n, "i8")
+    done = ops.to_bool(ops.zeros(n, "u8"))
+    steps = ops.zeros(n, "i32")
+    plies = 0
+    for ply in range(max_plies):
+        side = TOP_LEFT if ply % 2 == 0 else BOTTOM_RIGHT
+        pol = agent if side == TOP_LEFT else opponent
+        if isinstance(pol, NumpyRandom):
+            act = e.numpy_draw(state, raw, cur, roll_dice=False, pick_player=side)     # RandomAgent reads the env directly
+        else:
+            act = pol.action(e, state if side == TOP_LEFT else e.flip(state), ply)
+        before = state.clone() if ops.torch is not None else state.copy()
+        valid, win, _ = e.ply(state, act, side)
+        won = ops.to_bool(win) & ops.to_bool(valid) & ~done
+        state = ops.where_rows(done, before, state)
+        if side == TOP_LEFT:
+            steps = steps + (~done).to(steps.dtype) if ops.torch is not None else steps + (~done).astype(steps.dtype)
+        if ops.torch is not None:
+            winner = ops.torch.where(won, ops.torch.full_like(winner, 1 if side == TOP_LEFT else 2), winner)
+        else:
+            winner = np.where(won, np.int8(1 if side == TOP_LEFT else 2), winner)
+        done = done | won
+        plies += 1
+        e.numpy_draw(state, raw, cur, roll_dice=True)                            # :458 / :483 (finished games: irrelevant draws)
+        if plies % 4 == 0 and bool(done.all()):
+            break
+    w = ops.host(winner)
+    return {"agent_wins": int((w == 1).sum()), "opponent_wins": int((w == 2).sum()), "unfinished": int((w == 0).sum()),
+            "plies": plies, "winner": w, "agent_steps": ops.host(steps), "n": n}
+
+
 def wilson(k: int, n: int, z: float = 1.959964):
     """Wilson score interval (statsmodels proportion_confint(method='wilson') of the eval_*.py scripts)"""
     if n == 0:

@@ -633,6 +633,20 @@ struct MT19937 {
     }
 };
 
+// The same stream consumed across kernel launches (tournament driver with the reference's RNG): the first K tempered outputs of a
+// seed are stored once (ewn_numpy_stream) and a per-game cursor walks them; randint is the same masked rejection.
+struct RawStream {
+    const u32* raw; int K; int cur;
+    EWN_HD int randint(int low, int high) {
+        const u32 rng = (u32)(high - 1 - low);
+        if (rng == 0) return low;
+        u32 mask = rng;
+        mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+        while (cur < K) { const u32 v = raw[cur++] & mask; if (v <= rng) return low + (int)v; }
+        return low;                                            // stream exhausted (never for a live game with K >= 512)
+    }
+};
+
 // eval_random.py:17-51 for ONE seed: env.reset(seed) (np.random.seed + first die, envs/ewn.py:488-494), then RandomAgent vs the
 // env's RandomAgent opponent until the game ends.  Returns +1 (agent = TOP_LEFT won) or -1; g = final position.
 // trace: FNV-1a over the per-step log (dice at the agent's turn, agent action, die :458, opponent action, die :483) so that

@@ -280,6 +280,32 @@ template <class C> __global__ void __launch_bounds__(128) k_numpy_random_games(c
     if (trace) trace[i] = h;
 }
 
+__global__ void __launch_bounds__(128) k_numpy_stream(const u32* seeds, int64_t n, int K, u32* raw) {
+    const int64_t i = (int64_t)blockIdx.x * 128 + threadIdx.x;
+    if (i >= n) return;
+    MT19937 rng; rng.seed(seeds[i]);
+    for (int k = 0; k < K; k++) raw[i * K + k] = rng.next();
+}
+// roll_dice (envs/ewn.py:90-92) and / or RandomAgent.predict (random_policy.py:12-14) for every game from its stored stream
+template <class C> __global__ void __launch_bounds__(TPB) k_numpy_draw(u64* state, const u32* raw, int32_t* cursor, int K, int64_t n, Geo geo,
+                                                                       int roll, int pick_player, int32_t* action) {
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i);
+    RawStream rs; rs.raw = raw + i * K; rs.K = K; rs.cur = cursor[i];
+    if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
+    if (pick_player) {
+        Legal l;
+        if (pick_player == EWN_BOTTOM_RIGHT) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
+        else                                 l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        const int cnt = legal_count(l);
+        int la = 0, di = 0, sh;
+        if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh);
+        action[2 * i] = la; action[2 * i + 1] = di;
+    }
+    cursor[i] = rs.cur;
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_flip(const u64* in, u64* out, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
@@ -1084,6 +1110,26 @@ int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_
     if (use_p5(N)) k_numpy_random_games<P5><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
     else           k_numpy_random_games<P8><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
     LAUNCHED("k_numpy_random_games");
+    return EWN_OK;
+}
+
+int ewn_numpy_stream(const uint32_t* seeds, int64_t n, int K, uint32_t* raw, void* stream) {
+    if (!seeds || !raw || n < 0 || K < 1) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    k_numpy_stream<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(seeds, n, K, raw);
+    LAUNCHED("k_numpy_stream");
+    return EWN_OK;
+}
+
+int ewn_numpy_draw(uint64_t* state, const uint32_t* raw, int32_t* cursor, int K, int64_t n, int N, int L, int roll_dice, int pick_player,
+                   int32_t* action, void* stream) {
+    if (!state || !raw || !cursor || n < 0 || K < 1 || !config_ok(N, L) || pick_player < 0 || pick_player > 2 || (pick_player && !action)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_p5(N)) k_numpy_draw<P5><<<blocks_for(n), TPB, 0, st>>>(state, raw, cursor, K, n, geo, roll_dice, pick_player, action);
+    else           k_numpy_draw<P8><<<blocks_for(n), TPB, 0, st>>>(state, raw, cursor, K, n, geo, roll_dice, pick_player, action);
+    LAUNCHED("k_numpy_draw");
     return EWN_OK;
 }
 

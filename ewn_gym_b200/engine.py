@@ -180,6 +180,22 @@ class Engine:
                                                   self.xp.ptr(tr), self.xp.stream()), "ewn_numpy_random_games")
         return res, steps, fin, tr
 
+    def numpy_stream(self, seeds, K: int = 512):
+        """first K outputs of numpy's legacy MT19937 per seed -> (raw u32[n,K], cursor i32[n] = 0)"""
+        sd = self.xp.asarray(seeds, "u32")
+        n = int(sd.shape[0])
+        raw, cur = self.xp.empty((n, K), "u32"), self.xp.zeros((n,), "i32")
+        self._chk(self.lib.ewn_numpy_stream(self.xp.ptr(sd), n, K, self.xp.ptr(raw), self.xp.stream()), "ewn_numpy_stream")
+        return raw, cur
+
+    def numpy_draw(self, state, raw, cursor, roll_dice=True, pick_player: int = 0):
+        """the reference's next draws for every game: the die (in place) and / or a RandomAgent action int32[n,2] for `pick_player`"""
+        n = self._n(state)
+        act = self.xp.empty((n, 2), "i32") if pick_player else None
+        self._chk(self.lib.ewn_numpy_draw(self.xp.ptr(state), self.xp.ptr(raw), self.xp.ptr(cursor), int(raw.shape[1]), n, self.N, self.L,
+                                          int(bool(roll_dice)), int(pick_player), self.xp.ptr(act), self.xp.stream()), "ewn_numpy_draw")
+        return act
+
     def flip(self, state, out=None):
         """the position as the other side sees it: np.rot90(-board, 2), side to move mirrored (envs/ewn.py:289-296)"""
         n = self._n(state)

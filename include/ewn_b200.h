@@ -182,6 +182,14 @@ EWN_API int ewn_counter_add(uint64_t *counter, uint64_t k, void *stream);
 EWN_API int ewn_numpy_random_games(const uint32_t *seeds, int64_t n, int board_size, int cube_layer, int8_t *result, int32_t *agent_steps,
                            uint64_t *final_state, uint64_t *trace, void *stream);
 
+/* The same reference stream across launches (tournament driver with a deterministic policy on one side): ewn_numpy_stream stores the
+ * first K outputs of MT19937(seed) per game, raw u32[n][K]; ewn_numpy_draw consumes them through a per-game cursor int32[n]:
+ * roll_dice != 0 -> die = randint(1, cube_num + 1) (envs/ewn.py:90-92), then pick_player (1 / 2, 0 = none) -> action int32[n][2] =
+ * RandomAgent.predict for that side: legal list[randint(0, len)] (random_policy.py:12-14). */
+EWN_API int ewn_numpy_stream(const uint32_t *seeds, int64_t n, int K, uint32_t *raw, void *stream);
+EWN_API int ewn_numpy_draw(uint64_t *state, const uint32_t *raw, int32_t *cursor, int K, int64_t n, int board_size, int cube_layer,
+                   int roll_dice, int pick_player, int32_t *action, void *stream);
+
 /* ---- search ---------------------------------------------------------------------------------------------- */
 
 /* envs/minimax_ewn.py:29-213 evaluate(heuristic) -> f64[n] */

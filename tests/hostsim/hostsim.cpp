@@ -338,6 +338,30 @@ int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_
     }
     return EWN_OK;
 }
+int ewn_numpy_stream(const uint32_t* seeds, int64_t n, int K, uint32_t* raw, void*) {
+    if (!seeds || !raw || n < 0 || K < 1) return EWN_EARG;
+    MT19937 rng;
+    for (int64_t i = 0; i < n; i++) { rng.seed(seeds[i]); for (int k = 0; k < K; k++) raw[i * K + k] = rng.next(); }
+    return EWN_OK;
+}
+int ewn_numpy_draw(uint64_t* state, const uint32_t* raw, int32_t* cursor, int K, int64_t n, int N, int L, int roll, int pick_player,
+                   int32_t* action, void*) {
+    if (!state || !raw || !cursor || n < 0 || K < 1 || !config_ok(N, L) || pick_player < 0 || pick_player > 2 || (pick_player && !action)) return EWN_EARG;
+    Geo geo = make_geo(N, L);
+    for (int64_t i = 0; i < n; i++) {
+        RawStream rs; rs.raw = raw + i * K; rs.K = K; rs.cur = cursor[i];
+        int la = 0, di = 0, sh;
+        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
+            if (pick_player) { Legal l = pick_player == EWN_BOTTOM_RIGHT ? legal<P5, SIDE_BR>(g, geo, movers<P5>(g.br, g.dice)) : legal<P5, SIDE_TL>(g, geo, movers<P5>(g.tl, g.dice));
+                int cnt = legal_count(l); if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh); } }
+        else { Game<P8> g; unpack(g, state, i); if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
+            if (pick_player) { Legal l = pick_player == EWN_BOTTOM_RIGHT ? legal<P8, SIDE_BR>(g, geo, movers<P8>(g.br, g.dice)) : legal<P8, SIDE_TL>(g, geo, movers<P8>(g.tl, g.dice));
+                int cnt = legal_count(l); if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh); } }
+        if (pick_player) { action[2 * i] = la; action[2 * i + 1] = di; }
+        cursor[i] = rs.cur;
+    }
+    return EWN_OK;
+}
 int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t n, int N, int L, void*) {
     if (!state || !board || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);

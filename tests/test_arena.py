@@ -107,3 +107,42 @@ def test_onehot_observation_matches_reference_encoding(backend, N, L):
     rd = np.zeros((n, cn), np.float32)
     rd[np.arange(n), d - 1] = 1
     assert ob.dtype == np.float32 and np.array_equal(ob, ref) and np.array_equal(od, rd)
+
+
+EXACT_CASES = {   # golden key -> (agent, opponent) with the reference's own random stream on the random seat
+    "minimax_d1_vs_random": (lambda: A.MinimaxPolicy(1), lambda: A.NumpyRandom()),
+    "minimax_d2_vs_random": (lambda: A.MinimaxPolicy(2), lambda: A.NumpyRandom()),
+    "minimax_d3_vs_random": (lambda: A.MinimaxPolicy(3), lambda: A.NumpyRandom()),
+    "minimax_d4_vs_random": (lambda: A.MinimaxPolicy(4), lambda: A.NumpyRandom()),
+    "minimax_d5_vs_random": (lambda: A.MinimaxPolicy(5), lambda: A.NumpyRandom()),
+    "random_vs_minimax_d1": (lambda: A.NumpyRandom(), lambda: A.MinimaxPolicy(1)),
+    "random_vs_minimax_d2": (lambda: A.NumpyRandom(), lambda: A.MinimaxPolicy(2)),
+    "random_vs_minimax_d3": (lambda: A.NumpyRandom(), lambda: A.MinimaxPolicy(3)),
+    "minimax_d3_min_dist_vs_random": (lambda: A.MinimaxPolicy(3, "min_dist"), lambda: A.NumpyRandom()),
+}
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("case", sorted(EXACT_CASES))
+def test_pair_win_counts_are_exactly_the_references(backend, case):
+    """Whole games of ExpectiMinimaxAgent vs RandomAgent (either seat) replayed from the reference's seeds with the reference's own
+    MT19937 stream for the dice and the random seat: the bit-exact search makes every game identical, so the WIN COUNT recorded from
+    the unmodified reference (policy_pairs_stats.json) must be reproduced exactly, not just statistically."""
+    ref = json.load(open(os.path.join(GOLD, "policy_pairs_stats.json")))[case]
+    if backend != "cuda" and any(d in case for d in ("d3", "d4", "d5")):
+        pytest.skip("depth >= 3 pairs run on the GPU tier (the host simulator is a single-thread debug build)")
+    e = make_engine(backend, 5, 3)
+    ag, op = EXACT_CASES[case]
+    seeds = np.arange(ref["first_seed"], ref["first_seed"] + ref["games"])
+    r = A.play_matches_numpy(e, ag(), op(), seeds)
+    assert r["unfinished"] == 0 and r["agent_wins"] == ref["agent_wins"], (case, r["agent_wins"], ref["agent_wins"])
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_numpy_stream_arena_equals_single_kernel_games(backend):
+    """random vs random through the multi-launch driver == ewn_numpy_random_games (one kernel) == the reference: 5,215 wins"""
+    e = make_engine(backend, 5, 3)
+    seeds = np.arange(10000)
+    r = A.play_matches_numpy(e, A.NumpyRandom(), A.NumpyRandom(), seeds)
+    res, steps, _, _ = e.numpy_random_games(seeds.astype(np.uint32))
+    assert r["agent_wins"] == 5215 and np.array_equal(r["winner"] == 1, to_np(res) > 0) and np.array_equal(r["agent_steps"], to_np(steps))
