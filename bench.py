@@ -292,6 +292,10 @@ def run_ours(args, rank, world, local_rank):
             with torch.cuda.graph(graph, stream=side):
                 rollout_stream()                    # 128 step kernels + the counter bump: the next replay draws fresh Philox counters
             graph.replay(); torch.cuda.synchronize()
+        if dist:                                    # first NCCL call on this stream sets up the communicator: not part of a rollout
+            with torch.cuda.stream(side):
+                dist.all_reduce(st_roll.clone())
+            torch.cuda.synchronize()
         res = {}
         for name, fn in (("stream", rollout_stream), ("graph", graph.replay)):
             reps = 10
