@@ -244,6 +244,15 @@ def run_ours(args, rank, world, local_rank):
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
                    "playouts_per_child": 1024, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024)}
+        try:    # on-chip kernel: the roofline is the SM issue rate; instructions per ply come from the committed ncu capture
+            prof = json.load(open(os.path.join(ROOT, "profiles", "k_playouts_issue.json")))
+            wi = prof["warp_instructions_per_ply"] * float(plies.item()) / (pms / 1e3)
+            playout["issue_roofline"] = {"bound": "issue", "achieved": wi, "peak": prof["issue_peak_warp_instructions_per_s"] * world,
+                                         "unit": "warp-instructions/s", "frac": wi / (prof["issue_peak_warp_instructions_per_s"] * world),
+                                         "warp_instructions_per_ply": prof["warp_instructions_per_ply"], "alu_pipe_pct_ncu": prof["alu_pipe_pct"],
+                                         "note": "includes launch + all-reduce + arg-max inside the timed region"}
+        except Exception:
+            pass
 
     # ---- secondary: expectiminimax depth 4 (configs[3])
     emm = None
