@@ -238,19 +238,45 @@ def run_ours(args, rank, world, local_rank):
         best = e.mc_best_action(roots, wins)
         a1.record(); torch.cuda.synchronize()
         pms = a0.elapsed_time(a1)
+        merge = {"kind": "none (one rank)"}
         if dist:
-            tt = torch.tensor([pms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); pms = float(tt.item())
+            # the same step with the merge done by ONE kernel over NVLink peer memory instead of NCCL all-reduce + arg-max
+            # (ewn_gym_b200/peer.py); both are timed, the product path is the peer kernel, and the moves must be identical
+            from ewn_gym_b200.peer import PeerExchange
+            nccl_ms = pms
+            ex = PeerExchange(e, roots_n)
+            for _ in range(3):                    # warm-up epochs (maps the peers' memory on first touch)
+                e.mc_root_wins(roots, seed=SEED, first=rank * per, count=8, wins=ex.wins_buffer())
+                ex.best_action(roots, want_total=False)
+            w = ex.wins_buffer()
+            torch.cuda.synchronize(); dist.barrier()
+            a0.record()
+            e.mc_root_wins(roots, seed=SEED, first=rank * per, count=per, wins=w)
+            best_p, tot_p = ex.best_action(roots)
+            a1.record(); torch.cuda.synchronize()
+            peer_ms = a0.elapsed_time(a1)
+            ex.check()
+            same = bool(torch.equal(best_p, best)) and bool(torch.equal(tot_p, wins))
+            tt = torch.tensor([nccl_ms, peer_ms, 0.0 if same else 1.0], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            nccl_ms, peer_ms, bad = (float(x) for x in tt.tolist())
+            if bad:
+                raise SystemExit("peer-memory merge differs from all-reduce + arg-max")
+            pms = peer_ms
+            merge = {"kind": "one kernel over NVLink peer memory (ewn_mc_best_action_peers)", "ms": peer_ms, "nccl_allreduce_argmax_ms": nccl_ms,
+                     "identical_to_nccl": True}
+            dist.barrier(); ex.close()
             dist.all_reduce(plies)
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
-                   "playouts_per_child": 1024, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024)}
+                   "playouts_per_child": 1024, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
         try:    # on-chip kernel: the roofline is the SM issue rate; instructions per ply come from the committed ncu capture
             prof = json.load(open(os.path.join(ROOT, "profiles", "k_playouts_issue.json")))
             wi = prof["warp_instructions_per_ply"] * float(plies.item()) / (pms / 1e3)
             playout["issue_roofline"] = {"bound": "issue", "achieved": wi, "peak": prof["issue_peak_warp_instructions_per_s"] * world,
                                          "unit": "warp-instructions/s", "frac": wi / (prof["issue_peak_warp_instructions_per_s"] * world),
                                          "warp_instructions_per_ply": prof["warp_instructions_per_ply"], "alu_pipe_pct_ncu": prof["alu_pipe_pct"],
-                                         "note": "includes launch + all-reduce + arg-max inside the timed region"}
+                                         "note": "includes launch + root-statistics merge + arg-max inside the timed region"}
         except Exception:
             pass
 

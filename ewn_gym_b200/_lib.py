@@ -67,6 +67,12 @@ PROTOTYPES = {
     "ewn_numpy_stream": (C.c_int, [p_void, i64, C.c_int, p_void, p_void]),
     "ewn_numpy_draw": (C.c_int, [p_void, p_void, p_void, C.c_int, i64, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void]),
     "ewn_flip": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, p_void]),
+    "ewn_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(p_void), p_void]),
+    "ewn_peer_open": (C.c_int, [p_void, C.POINTER(p_void)]),
+    "ewn_peer_close": (C.c_int, [p_void]),
+    "ewn_peer_free": (C.c_int, [p_void]),
+    "ewn_mc_best_action_peers": (C.c_int, [p_void, p_void, p_void, C.c_int, C.c_int, C.c_uint32, C.c_uint32, p_void, p_void, i64, C.c_int,
+                                           C.c_int, p_void]),
     "ewn_random_action": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
     "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),
     "ewn_counter_add": (C.c_int, [p_void, u64, p_void]),

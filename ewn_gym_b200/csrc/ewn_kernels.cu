@@ -919,6 +919,61 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best(const u64* s
     action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di;
 }
 
+// root-statistics merge fused with the arg-max: one-shot all-reduce of the win counters over NVLink peer loads
+struct PeerSet { const u32* wins[EWN_MAX_PEERS]; u32* flags[EWN_MAX_PEERS]; };
+
+__device__ __forceinline__ void st_release_sys(u32* p, u32 v) { asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ u32 ld_acquire_sys(const u32* p) { u32 v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ unsigned long long global_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const u64* state, PeerSet ps, int rank, int world, u32 epoch,
+                                                                           unsigned long long timeout_ns, u32* total, int8_t* action, int64_t n, Geo geo) {
+    // publish: the playout kernel that filled my counters precedes this kernel on the stream, so they are complete
+    if (blockIdx.x == 0 && threadIdx.x < world) { __threadfence_system(); st_release_sys(ps.flags[threadIdx.x] + rank, epoch); }
+    // wait for the same epoch of every rank; the flag words live in MY memory, the spin never crosses NVLink
+    if (threadIdx.x < world) {
+        const u32* f = ps.flags[rank] + threadIdx.x;
+        unsigned long long t0 = global_ns();
+        while ((int)(ld_acquire_sys(f) - epoch) < 0) {
+            if (global_ns() - t0 > timeout_ns) { atomicExch(ps.flags[rank] + EWN_PEER_ERR_WORD, epoch); break; }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    uint2 w[EWN_MAX_PEERS][3];                                   // 24-byte rows: three 8-byte peer loads per rank, all in flight together
+#pragma unroll
+    for (int r = 0; r < EWN_MAX_PEERS; r++)
+        if (r < world) {
+            const uint2* src = reinterpret_cast<const uint2*>(ps.wins[r]) + i * 3;
+#pragma unroll
+            for (int k = 0; k < 3; k++) w[r][k] = __ldcg(src + k);
+        }
+    u32 sum[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < EWN_MAX_PEERS; r++)
+        if (r < world) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) { sum[2 * k] += w[r][k].x; sum[2 * k + 1] += w[r][k].y; }
+        }
+    if (total) {
+        uint2* dst = reinterpret_cast<uint2*>(total) + i * 3;
+#pragma unroll
+        for (int k = 0; k < 3; k++) dst[k] = make_uint2(sum[2 * k], sum[2 * k + 1]);
+    }
+    Game<C> g; unpack(g, state, i);
+    int la = -1, di = -1;
+    if (!full_win<C>(g, geo)) {
+        Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        int cnt = legal_count(l), best = 0;
+#pragma unroll
+        for (int j = 1; j < 6; j++) if (j < cnt && sum[j] > sum[best]) best = j;                  // np.argmax: first maximum
+        int sh; legal_pick(l, best, la, di, sh);
+    }
+    action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di;
+}
+
 // ------------------------------------------------------------------------------------------------
 // library-owned scratch (one per device), grown on demand; used when the caller passes no workspace
 // ------------------------------------------------------------------------------------------------
@@ -1363,6 +1418,61 @@ int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* acti
     if (use_p5(N)) k_mc_best<P5><<<blocks_for(n), TPB, 0, st>>>(state, wins, action, n, geo);
     else           k_mc_best<P8><<<blocks_for(n), TPB, 0, st>>>(state, wins, action, n, geo);
     LAUNCHED("k_mc_best");
+    return EWN_OK;
+}
+
+int ewn_peer_alloc(size_t bytes, void** ptr, ewn_peer_handle* handle) {
+    if (!ptr || !handle || bytes == 0) return EWN_EARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(ewn_peer_handle), "handle size");
+    void* p = nullptr;
+    CU(cudaMalloc(&p, bytes));
+    cudaError_t e = cudaMemset(p, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); CU(e); }
+    memset(handle, 0, sizeof(*handle));
+    memcpy(handle->bytes, &h, sizeof(h));
+    *ptr = p;
+    return EWN_OK;
+}
+
+int ewn_peer_open(const ewn_peer_handle* handle, void** ptr) {
+    if (!handle || !ptr) return EWN_EARG;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle->bytes, sizeof(h));
+    CU(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return EWN_OK;
+}
+
+int ewn_peer_close(void* ptr) {
+    if (!ptr) return EWN_EARG;
+    CU(cudaIpcCloseMemHandle(ptr));
+    return EWN_OK;
+}
+
+int ewn_peer_free(void* ptr) {
+    if (!ptr) return EWN_EARG;
+    CU(cudaFree(ptr));
+    return EWN_OK;
+}
+
+int ewn_mc_best_action_peers(const uint64_t* state, const uint32_t* const* wins_peers, uint32_t* const* flag_peers, int rank, int world,
+                             uint32_t epoch, uint32_t timeout_ms, uint32_t* wins_total, int8_t* action, int64_t n, int N, int L, void* stream) {
+    if (!state || !wins_peers || !flag_peers || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (world < 1 || world > EWN_MAX_PEERS || rank < 0 || rank >= world || epoch == 0) return EWN_EARG;
+    PeerSet ps;
+    for (int r = 0; r < EWN_MAX_PEERS; r++) {
+        ps.wins[r] = r < world ? wins_peers[r] : nullptr;
+        ps.flags[r] = r < world ? flag_peers[r] : nullptr;
+        if (r < world && (!ps.wins[r] || !ps.flags[r])) return EWN_EARG;
+    }
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long ns = (unsigned long long)(timeout_ms ? timeout_ms : 2000u) * 1000000ull;
+    int64_t blocks = n ? blocks_for(n) : 1;                                                        // n == 0 still takes part in the epoch
+    if (use_p5(N)) k_mc_best_peers<P5><<<blocks, TPB, 0, st>>>(state, ps, rank, world, epoch, ns, wins_total, action, n, geo);
+    else           k_mc_best_peers<P8><<<blocks, TPB, 0, st>>>(state, ps, rank, world, epoch, ns, wins_total, action, n, geo);
+    LAUNCHED("k_mc_best_peers");
     return EWN_OK;
 }
 

@@ -221,6 +221,34 @@ EWN_API int ewn_mc_root_wins(const uint64_t *state, const uint32_t *root_ids, in
 EWN_API int ewn_mc_best_action(const uint64_t *state, const uint32_t *wins, int8_t *action, int64_t n, int board_size, int cube_layer,
                        void *stream);
 
+/* ---- root-statistics merge over NVLink peer memory (the one exchange step of the path) ----------- */
+/* mcts.py:59-68 sums the wins of all env copies and takes np.argmax.  With the playout range of every (root, action) split
+ * over the GPUs of one node, that sum is an all-reduce of u32[n][6] followed by the arg-max.  ewn_mc_best_action_peers does
+ * both in ONE kernel: every rank publishes "my wins of epoch e are complete" into each peer's flag words, waits for the
+ * peers' flags in its own memory, then reads all ranks' win counters with peer loads, sums and picks the first maximum.
+ * No NCCL call, no intermediate buffer.
+ *
+ * Buffers come from ewn_peer_alloc (cudaMalloc, zero-filled) and travel between the processes of a node as 64-byte handles
+ * (cudaIpcMemHandle_t) which the host layer exchanges (torch.distributed all_gather_object in ewn_gym_b200/peer.py).
+ * flags: u32[EWN_PEER_FLAG_WORDS] per rank; word s = last epoch published by rank s, word EWN_PEER_ERR_WORD = the epoch at
+ * which a wait timed out (0 = never).  Epochs start at 1 and increase; the caller alternates between two win buffers so
+ * that a rank never rewrites counters a peer may still be reading (the wait of epoch e+1 proves every peer finished e). */
+#define EWN_MAX_PEERS 8
+#define EWN_PEER_FLAG_WORDS 32
+#define EWN_PEER_ERR_WORD 16
+typedef struct ewn_peer_handle { unsigned char bytes[64]; } ewn_peer_handle;
+EWN_API int ewn_peer_alloc(size_t bytes, void **ptr, ewn_peer_handle *handle);
+EWN_API int ewn_peer_open(const ewn_peer_handle *handle, void **ptr);     /* another process's buffer, mapped on the current device */
+EWN_API int ewn_peer_close(void *ptr);                                    /* undo ewn_peer_open  */
+EWN_API int ewn_peer_free(void *ptr);                                     /* undo ewn_peer_alloc */
+/* wins_peers / flag_peers: HOST arrays of `world` device pointers, index = rank (entry `rank` is the caller's own buffer).
+ * wins_total: optional u32[n][6] out (the summed counters); action: int8[n][2] as ewn_mc_best_action.
+ * timeout_ms: bound on the wait for the peers (0 = 2000); on expiry the kernel records the epoch in its error word and
+ * returns without hanging the device -- results of that call are undefined. */
+EWN_API int ewn_mc_best_action_peers(const uint64_t *state, const uint32_t *const *wins_peers, uint32_t *const *flag_peers, int rank,
+                             int world, uint32_t epoch, uint32_t timeout_ms, uint32_t *wins_total, int8_t *action, int64_t n,
+                             int board_size, int cube_layer, void *stream);
+
 /* ---- host-buffer vector environment (the call a numpy / SB3 user makes) ----------------------------------- */
 /* Owns device state, pinned staging buffers and streams for n games on the current device.  step: actions come from
  * host memory, observations / rewards / dones land in host memory; copies and the kernel are pipelined in chunks. */

@@ -37,6 +37,10 @@ class NumpyArrays:
     def stream(self):
         return None
 
+    def guard(self):
+        import contextlib
+        return contextlib.nullcontext()
+
 
 def build_hostsim():
     src = os.path.join(HOSTSIM_DIR, "hostsim.cpp")

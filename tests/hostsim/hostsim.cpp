@@ -4,6 +4,7 @@
 // kernel bodies can be stepped in gdb / run under sanitizers.  Never loaded by the ewn_gym_b200 package; the
 // product has no CPU path (libewn_b200.so returns EWN_ECUDA without a device).
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -423,5 +424,38 @@ int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* acti
     if (!state || !wins || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
     return BY_CODEC(N, t_mc_best<P5>(state, wins, action, n, geo), t_mc_best<P8>(state, wins, action, n, geo));
+}
+// peer exchange on the host: "handles" carry the pointer itself (one process plays all ranks)
+int ewn_peer_alloc(size_t bytes, void** ptr, ewn_peer_handle* handle) {
+    if (!ptr || !handle || bytes == 0) return EWN_EARG;
+    void* p = calloc(1, bytes);
+    if (!p) return EWN_ECUDA;
+    memset(handle, 0, sizeof(*handle));
+    memcpy(handle->bytes, &p, sizeof(p));
+    *ptr = p;
+    return EWN_OK;
+}
+int ewn_peer_open(const ewn_peer_handle* handle, void** ptr) {
+    if (!handle || !ptr) return EWN_EARG;
+    memcpy(ptr, handle->bytes, sizeof(*ptr));
+    return EWN_OK;
+}
+int ewn_peer_close(void* ptr) { return ptr ? EWN_OK : EWN_EARG; }
+int ewn_peer_free(void* ptr) { if (!ptr) return EWN_EARG; free(ptr); return EWN_OK; }
+int ewn_mc_best_action_peers(const uint64_t* state, const uint32_t* const* wins_peers, uint32_t* const* flag_peers, int rank, int world,
+                             uint32_t epoch, uint32_t, uint32_t* wins_total, int8_t* action, int64_t n, int N, int L, void*) {
+    if (!state || !wins_peers || !flag_peers || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (world < 1 || world > EWN_MAX_PEERS || rank < 0 || rank >= world || epoch == 0) return EWN_EARG;
+    for (int r = 0; r < world; r++) if (!wins_peers[r] || !flag_peers[r]) return EWN_EARG;
+    for (int r = 0; r < world; r++) flag_peers[r][rank] = epoch;
+    for (int r = 0; r < world; r++)                                   // a sequential host cannot wait: an unpublished peer is the time-out case
+        if ((int)(flag_peers[rank][r] - epoch) < 0) { flag_peers[rank][EWN_PEER_ERR_WORD] = epoch; break; }
+    uint32_t* sum = (uint32_t*)calloc((size_t)(n ? n : 1) * 6, sizeof(uint32_t));
+    for (int r = 0; r < world; r++) for (int64_t k = 0; k < n * 6; k++) sum[k] += wins_peers[r][k];
+    if (wins_total) memcpy(wins_total, sum, (size_t)n * 6 * sizeof(uint32_t));
+    Geo geo = make_geo(N, L);
+    int rc = BY_CODEC(N, t_mc_best<P5>(state, sum, action, n, geo), t_mc_best<P8>(state, sum, action, n, geo));
+    free(sum);
+    return rc;
 }
 }  // extern "C"
