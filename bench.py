@@ -226,37 +226,46 @@ def run_ours(args, rank, world, local_rank):
         for s in range(1, 5):                     # a few random plies so that roots are mid-game positions
             e.step(roots, None, seed=SEED + 1, step=s, agent_random=True, autoreset=True, want=())
         per = 1024 // world
+        iters = 8                                 # Monte-Carlo decisions back to back (fresh playout streams each), as an arena makes them
         wins = torch.zeros(roots_n, 6, dtype=torch.int32, device=dev)
         plies = torch.zeros(1, dtype=torch.int64, device=dev)
-        e.mc_root_wins(roots, seed=SEED, first=rank * per, count=8, wins=wins.clone())          # warm-up
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        if dist: dist.barrier()
-        a0.record()
-        _, nch = e.mc_root_wins(roots, seed=SEED, first=rank * per, count=per, wins=wins, plies=plies)
-        if dist: dist.all_reduce(wins)            # root statistics merge
-        best = e.mc_best_action(roots, wins)
-        a1.record(); torch.cuda.synchronize()
-        pms = a0.elapsed_time(a1)
+
+        def decide_nccl(it, count, pl=None):
+            wins.zero_()
+            _, k = e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=wins, plies=pl)
+            if dist: dist.all_reduce(wins)        # root statistics merge
+            return e.mc_best_action(roots, wins), k
+
+        def timed(fn):
+            fn(0, 8)                              # warm-up
+            torch.cuda.synchronize()
+            if dist: dist.barrier()
+            a0.record()
+            for it in range(iters):
+                out = fn(it, per)
+            a1.record(); torch.cuda.synchronize()
+            return a0.elapsed_time(a1) / iters, out
+
+        pms, (best, nch) = timed(decide_nccl)
+        decide_nccl(iters - 1, per, plies)        # plies of one decision (untimed)
+        tot_ref = wins.clone()
         merge = {"kind": "none (one rank)"}
         if dist:
-            # the same step with the merge done by ONE kernel over NVLink peer memory instead of NCCL all-reduce + arg-max
+            # the same decisions with the merge done by ONE kernel over NVLink peer memory instead of NCCL all-reduce + arg-max
             # (ewn_gym_b200/peer.py); both are timed, the product path is the peer kernel, and the moves must be identical
             from ewn_gym_b200.peer import PeerExchange
             nccl_ms = pms
             ex = PeerExchange(e, roots_n)
-            for _ in range(3):                    # warm-up epochs (maps the peers' memory on first touch)
-                e.mc_root_wins(roots, seed=SEED, first=rank * per, count=8, wins=ex.wins_buffer())
-                ex.best_action(roots, want_total=False)
-            w = ex.wins_buffer()
-            torch.cuda.synchronize(); dist.barrier()
-            a0.record()
-            e.mc_root_wins(roots, seed=SEED, first=rank * per, count=per, wins=w)
-            best_p, tot_p = ex.best_action(roots)
-            a1.record(); torch.cuda.synchronize()
-            peer_ms = a0.elapsed_time(a1)
+
+            def decide_peers(it, count):
+                e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=ex.wins_buffer())
+                return ex.best_action(roots)
+
+            decide_peers(0, 8); decide_peers(0, 8)        # maps the peers' memory on first touch
+            peer_ms, (best_p, tot_p) = timed(decide_peers)
             ex.check()
-            same = bool(torch.equal(best_p, best)) and bool(torch.equal(tot_p, wins))
+            same = bool(torch.equal(best_p, best)) and bool(torch.equal(tot_p, tot_ref))
             tt = torch.tensor([nccl_ms, peer_ms, 0.0 if same else 1.0], device=dev, dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             nccl_ms, peer_ms, bad = (float(x) for x in tt.tolist())
@@ -269,7 +278,7 @@ def run_ours(args, rank, world, local_rank):
             dist.all_reduce(plies)
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
-                   "playouts_per_child": 1024, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
+                   "playouts_per_child": 1024, "decisions_timed": iters, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
         try:    # on-chip kernel: the roofline is the SM issue rate; instructions per ply come from the committed ncu capture
             prof = json.load(open(os.path.join(ROOT, "profiles", "k_playouts_issue.json")))
             wi = prof["warp_instructions_per_ply"] * float(plies.item()) / (pms / 1e3)
