@@ -368,7 +368,8 @@ def run_ours(args, rank, world, local_rank):
     from ewn_gym_b200.vec_env import EWNVecEnv
     e2e = None
     if not args.skip_e2e:
-        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank, env_id0=env_id0, staged=args.e2e_staged, chunks=args.e2e_chunks)
+        env = EWNVecEnv(n, N_BOARD, N_LAYER, seed=SEED, device=local_rank, env_id0=env_id0, staged=args.e2e_staged, chunks=args.e2e_chunks,
+                        numa_bind=world > 1 and os.environ.get("EWN_NUMA_BIND", "1") != "0")
         env.reset()
         rng = np.random.default_rng(7 + rank)
         pool = [np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64) for _ in range(2)]
@@ -389,7 +390,7 @@ def run_ours(args, rank, world, local_rank):
         nn = N_BOARD * N_BOARD
         e2e = {"value": world * n / (tot / ksteps), "unit": "env steps/s", "h2d_bytes_per_step": 16 * n * world,
                "d2h_bytes_per_step": ((2 * nn + 8 + 4 + 1 + 1) * n + (2 * nn + 8 + 4) * (term_rows // ksteps) + 4) * world, "ms_per_step": 1e3 * tot / ksteps,
-               "steps": ksteps, "n_gpus": world, "terminal_observations_per_step": term_rows // ksteps,
+               "steps": ksteps, "n_gpus": world, "terminal_observations_per_step": term_rows // ksteps, "numa_bind": env.numa,
                "note": "host wall clock around EWNVecEnv.step on every rank (max over ranks): H2D copy of the int64 actions from page-locked memory, k_vstep in 8 chunks on 3 streams, "
                        + ("results staged in HBM and copied back (D2H)" if args.e2e_staged else "results stored by the kernel straight into the page-locked host buffers over PCIe")
                        + "; PCIe-bound"}

@@ -52,6 +52,7 @@ PROTOTYPES = {
     "ewn_strerror": (C.c_char_p, [C.c_int]),
     "ewn_last_cuda_error": (C.c_char_p, []),
     "ewn_device_count": (C.c_int, []),
+    "ewn_device_pci_bus_id": (C.c_int, [C.c_int, C.c_char_p, C.c_int]),
     "ewn_state_words": (C.c_int, [C.c_int]),
     "ewn_launch_count": (i64, []),
     "ewn_reset": (C.c_int, [p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
@@ -94,7 +95,7 @@ PROTOTYPES = {
 }
 # entry points a host simulator (tests/hostsim) does not provide
 _VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_host_alloc", "ewn_host_free",
-             "ewn_vec_state", "ewn_vec_step_index"}
+             "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id"}
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

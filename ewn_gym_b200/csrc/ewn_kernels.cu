@@ -1053,6 +1053,11 @@ int ewn_device_count(void) {
     if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
     return n;
 }
+int ewn_device_pci_bus_id(int device, char* out, int len) {
+    if (!out || len < 13) return EWN_EARG;
+    CU(cudaDeviceGetPCIBusId(out, len, device));
+    return EWN_OK;
+}
 int ewn_state_words(int N) { return (N >= 3 && N <= EWN_MAX_BOARD) ? (use_p5(N) ? 1 : 2) : EWN_EARG; }
 int64_t ewn_launch_count(void) { return g_launches.load(); }
 

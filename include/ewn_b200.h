@@ -64,6 +64,9 @@ EWN_API const char *ewn_strerror(int code);
 EWN_API const char *ewn_last_cuda_error(void);
 /* number of CUDA devices visible, or EWN_ECUDA */
 EWN_API int ewn_device_count(void);
+/* "dddd:bb:dd.f" of a CUDA device (len >= 13): lets the host layer find the NUMA node the GPU hangs off
+ * (/sys/bus/pci/devices/<id>/numa_node) and keep its page-locked buffers and stepping thread there (vec_env.py) */
+EWN_API int ewn_device_pci_bus_id(int device, char *out, int len);
 /* u64 words per game for this board size (1 or 2), or EWN_EARG */
 EWN_API int ewn_state_words(int board_size);
 /* total kernels launched by this library in this process (bench.py reports it as gpu_launches) */

@@ -66,3 +66,33 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in txt.lower(), os.path.join(dirpath, f)
+
+
+def test_numa_binding_helper(tmp_path):
+    """bind_host_to_device reads the GPU's NUMA node from sysfs; a node that covers every allowed CPU changes nothing"""
+    import os
+    from ewn_gym_b200.vec_env import _parse_cpulist, bind_host_to_device
+    assert _parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11} and _parse_cpulist("\n") == set()
+
+    class FakeLib:
+        def __init__(self, rc=0):
+            self.rc = rc
+
+        def ewn_device_pci_bus_id(self, device, buf, n):
+            buf.value = b"0000:1B:00.0"
+            return self.rc
+
+    dev = tmp_path / "bus" / "pci" / "devices" / "0000:1b:00.0"
+    dev.mkdir(parents=True)
+    node = tmp_path / "devices" / "system" / "node" / "node1"
+    node.mkdir(parents=True)
+    allowed = sorted(os.sched_getaffinity(0))
+    (node / "cpulist").write_text(",".join(map(str, allowed)) + "\n")
+    (dev / "numa_node").write_text("1\n")
+    r = bind_host_to_device(FakeLib(), 0, sysfs=str(tmp_path))
+    assert r == {"pci": "0000:1b:00.0", "node": 1, "cpus": len(allowed), "changed": False}
+    assert sorted(os.sched_getaffinity(0)) == allowed
+    (dev / "numa_node").write_text("-1\n")
+    assert bind_host_to_device(FakeLib(), 0, sysfs=str(tmp_path)) is None
+    assert bind_host_to_device(FakeLib(rc=-2), 0, sysfs=str(tmp_path)) is None
+    assert bind_host_to_device(FakeLib(), 0, sysfs=str(tmp_path / "nowhere")) is None

@@ -149,3 +149,4 @@ def test_full_size_properties_1mi_games():
         assert s[3] == fin_total and s[0] + s[1] + s[2] == s[3] and s[0] > 0 and s[1] > 0
         sums.append((int(acc.item()), tuple(s), int(st.sum().item())))
     assert sums[0] == sums[1]
+
