@@ -202,7 +202,8 @@ EWN_API int ewn_evaluate(const uint64_t *state, double *value, int64_t n, int bo
  * pruned != 0 reproduces the reference's alpha/beta hand-through at chance nodes bit for bit; 0 = textbook.
  * value: f64[n]; action: int8[n][2] (-1,-1 = None for a finished root).
  * workspace: device scratch of at least ewn_expectiminimax_workspace(n, depth) bytes, or NULL / 0 to let the library
- * use its own cached allocation. */
+ * use its own cached allocation (one per device: such calls must be ordered on one stream; pass a workspace to run several
+ * searches concurrently). */
 EWN_API size_t ewn_expectiminimax_workspace(int64_t n, int depth);
 EWN_API int ewn_expectiminimax(const uint64_t *state, int64_t n, int board_size, int cube_layer, int depth, int heuristic, int pruned,
                        double *value, int8_t *action, void *workspace, size_t workspace_bytes, void *stream);
