@@ -1575,6 +1575,9 @@ int ewn_vec_reset(ewn_vec* v, int16_t* obs_board, int64_t* obs_dice) {
         rc = ewn_evaluate(v->state, v->prev_score, c.n, c.board_size, c.cube_layer, EWN_H_HYBRID, st);
         if (rc) return rc;
     }
+    // a reset shifts the parity of the step index: neither append counter may carry a count over (the step that would have
+    // cleared it never ran)
+    CU(cudaMemsetAsync(v->term_count, 0, 2 * sizeof(uint32_t), st));
     rc = ewn_decode(v->state, v->obs_board, v->obs_dice, nullptr, c.n, c.board_size, c.cube_layer, st);
     if (rc) return rc;
     if (obs_board) CU(cudaMemcpyAsync(obs_board, v->obs_board, (size_t)c.n * NN * 2, cudaMemcpyDeviceToHost, st));

@@ -150,3 +150,52 @@ def test_full_size_properties_1mi_games():
         sums.append((int(acc.item()), tuple(s), int(st.sum().item())))
     assert sums[0] == sums[1]
 
+
+
+@pytest.mark.parametrize("N,L,shaped,term", [(5, 3, False, True), (5, 3, True, True), (7, 3, True, True), (6, 3, False, False)])
+def test_device_env_equals_host_env(N, L, shaped, term):
+    """EWNDeviceVecEnv (tensors stay in HBM) and EWNVecEnv (host buffers) are the same environment"""
+    import torch
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.vec_env import EWNVecEnv
+    n = 3000
+    kw = dict(board_size=N, cube_layer=L, seed=77, shaped=shaped, illegal_move_tolerance=3, env_id0=12345, terminal_observation=term)
+    host, devv = EWNVecEnv(n, **kw), EWNDeviceVecEnv(n, **kw)
+    try:
+        oh, od = host.reset(), devv.reset()
+        assert np.array_equal(oh["board"], od["board"].cpu().numpy()) and np.array_equal(oh["dice_roll"], od["dice_roll"].cpu().numpy())
+        rng = np.random.default_rng(5)
+        episodes = 0
+        for t in range(60):
+            a = np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+            oh, rh, dh, ih = host.step(a)
+            od, rd, dd, idv = devv.step(torch.from_numpy(a).cuda())
+            assert np.array_equal(oh["board"], od["board"].cpu().numpy()), t
+            assert np.array_equal(oh["dice_roll"], od["dice_roll"].cpu().numpy())
+            assert np.array_equal(rh, rd.cpu().numpy()) and np.array_equal(dh, dd.cpu().numpy())
+            k = int(dh.sum())
+            episodes += k
+            assert idv.terminal_count() == k
+            if term:
+                idx, tb, td = (x.cpu().numpy() for x in idv.terminal_rows())
+                assert sorted(idx.tolist()) == np.flatnonzero(dh).tolist()
+                for i in np.flatnonzero(dh)[:5]:
+                    a_, b_ = ih[int(i)], idv[int(i)]
+                    assert a_["message"] == b_["message"] and a_["TimeLimit.truncated"] == b_["TimeLimit.truncated"]
+                    assert np.array_equal(a_["terminal_observation"]["board"], b_["terminal_observation"]["board"])
+                    assert a_["terminal_observation"]["dice_roll"] == b_["terminal_observation"]["dice_roll"]
+            live = int(np.flatnonzero(~dh)[0])
+            assert idv[live] == {} and ih[live] == {}
+        st = devv.stats.cpu().numpy()
+        assert st[3] == episodes > 0 and st[0] + st[1] + st[2] == st[3]
+        oh, od = host.reset(), devv.reset()                        # a second reset draws fresh first dice, identically
+        assert np.array_equal(oh["dice_roll"], od["dice_roll"].cpu().numpy())
+        a = np.zeros((n, 2), np.int64)
+        oh, rh, dh, _ = host.step(a)
+        od, rd, dd, idv = devv.step(a)                            # numpy actions are accepted too
+        assert np.array_equal(oh["board"], od["board"].cpu().numpy()) and np.array_equal(rh, rd.cpu().numpy())
+        assert idv.terminal_count() == int(dh.sum())                # the append counters start from zero after a reset
+        if term:
+            assert int(host._b["tcount"].array[0]) == int(dh.sum())
+    finally:
+        host.close(); devv.close()
