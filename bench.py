@@ -396,6 +396,31 @@ def run_ours(args, rank, world, local_rank):
                        + "; PCIe-bound"}
         env.close()
 
+    # ---- the same step through the device-resident VecEnv class (CUDA tensors in and out: what a policy on the GPU calls)
+    device_env = None
+    if not args.skip_e2e:
+        from ewn_gym_b200.device_env import EWNDeviceVecEnv
+        denv = EWNDeviceVecEnv(n, N_BOARD, N_LAYER, seed=SEED, env_id0=env_id0, engine=e)
+        denv.reset()
+        denv.action_buffer.copy_(sets[0]["act"])
+        for _ in range(5):
+            denv.step(denv.action_buffer)
+        ksteps = max(10, min(args.steps, 100))
+        d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        if dist: dist.barrier()
+        d0.record()
+        for _ in range(ksteps):
+            denv.step(denv.action_buffer)        # the policy wrote its actions into the env's action tensor
+        d1.record(); torch.cuda.synchronize()
+        dms = d0.elapsed_time(d1) / ksteps
+        if dist:
+            tt = torch.tensor([dms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); dms = float(tt.item())
+        device_env = {"value": world * n / (dms / 1e3), "unit": "env steps/s", "ms_per_step": dms, "steps": ksteps,
+                      "note": "EWNDeviceVecEnv.step(action tensor) -> (obs, reward, done, infos) as CUDA tensors, one env set of 154 MB (> L2), "
+                              "Python call overhead included, no host copies"}
+        denv.close()
+
     if rank != 0:
         if dist: dist.destroy_process_group()
         return
@@ -420,7 +445,7 @@ def run_ours(args, rank, world, local_rank):
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env steps/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
+            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout, "device_env": device_env,
             "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3]},
             "wall_s_timed_region": wall}
     print(json.dumps(line), flush=True)
