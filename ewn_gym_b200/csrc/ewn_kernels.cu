@@ -797,16 +797,39 @@ template <class C, int M> __global__ void __launch_bounds__(128) k_emm_replay(co
 // per pair with one lane per game.  Lanes that finish pull the next game of their warp's contiguous range, so a
 // warp stays full until its range is exhausted; results depend only on (seed, root id, child, playout index).
 // ------------------------------------------------------------------------------------------------
+// One (root, child) pair = one AoS record, so that a lane picks up its next game with ONE vector load:
+//   P5: 16 B {packed state, root id | (slot * 8 + child) << 32};   P8: 32 B {word 0, word 1, the same meta word, unused}
 struct PairBuf {
-    u64* state;          // [pairs][WORDS]
-    u32* root_id;        // [pairs]
-    u32* slot;           // [pairs]  index into wins; low 3 bits of child kept in child[]
-    u32* child;          // [pairs]
+    void* rec;           // [pairs] records
     int* n_pairs;        // device counter
 };
+template <class C> struct PairRec;
+template <> struct PairRec<P5> {
+    static __device__ __forceinline__ void store(void* rec, u32 s, const Game<P5>& g, u32 rid, u32 sc) {
+        reinterpret_cast<ulonglong2*>(rec)[s] = make_ulonglong2(pack_word(g), (u64)rid | ((u64)sc << 32));
+    }
+    static __device__ __forceinline__ void load(const void* rec, u32 s, Game<P5>& g, u32& rid, u32& sc) {
+        const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(rec) + s);
+        unpack_regs(g, v.x, 0); rid = (u32)v.y; sc = (u32)(v.y >> 32);
+    }
+};
+template <> struct PairRec<P8> {
+    static __device__ __forceinline__ void store(void* rec, u32 s, const Game<P8>& g, u32 rid, u32 sc) {
+        u64 w0, w1; pack_words(g, w0, w1);
+        ulonglong2* p = reinterpret_cast<ulonglong2*>(rec) + 2 * (size_t)s;
+        p[0] = make_ulonglong2(w0, w1); p[1] = make_ulonglong2((u64)rid | ((u64)sc << 32), 0);
+    }
+    static __device__ __forceinline__ void load(const void* rec, u32 s, Game<P8>& g, u32& rid, u32& sc) {
+        const ulonglong2* p = reinterpret_cast<const ulonglong2*>(rec) + 2 * (size_t)s;
+        const ulonglong2 a = __ldg(p), b = __ldg(p + 1);
+        unpack_words(g, a.x, a.y); rid = (u32)b.x; sc = (u32)(b.x >> 32);
+    }
+};
 
+// `count`: playouts this launch sequence will play per pair.  A child that already ends the game (the agent's move wins,
+// mcts.py:28: the playout loop body never runs) is settled here -- all its playouts have the same result -- and gets no record.
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64* state, const u32* root_ids, int64_t n, Geo geo,
-                                                                      PairBuf pb, int32_t* n_children) {
+                                                                      PairBuf pb, int32_t* n_children, u32 count, u32* wins) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
     Game<C> g; unpack(g, state, i);
@@ -821,34 +844,51 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64*
             int la, di, sh; legal_pick(l, j, la, di, sh);
             apply_move<C, SIDE_TL>(c, sh, di);
             c.player = SIDE_BR;
-            int s = atomicAdd(pb.n_pairs, 1);
-            pack(c, pb.state, s);
-            pb.root_id[s] = rid; pb.child[s] = (u32)j; pb.slot[s] = (u32)(i * 6 + j);
+            const u32 slot = (u32)(i * 6 + j);
+            if (full_win<C>(c, geo)) {
+                if (count && tl_won<C>(c, geo)) atomicAdd(&wins[slot], count);
+                continue;
+            }
+            const int s = atomicAdd(pb.n_pairs, 1);
+            PairRec<C>::store(pb.rec, (u32)s, c, rid, slot * 8u + (u32)j);
         }
     }
     if (n_children) n_children[i] = cnt;
 }
 
-template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* pair_state, const u32* pair_root, const u32* pair_child,
-                                                                     const u32* pair_slot, const int* n_pairs_dev, int64_t n_pairs_host,
-                                                                     u32 first, u32 count, u32* wins, unsigned long long* plies,
-                                                                     Geo geo, const RoundKeys rk) {
+// q = n / d for n < 2^31 as one wide multiply and a shift: m = floor(2^sh / d) + 1, sh = 31 + ceil(log2 d)
+// (the error m * d - 2^sh is in (0, d] <= 2^(sh-31), so n * error < 2^sh for every n < 2^31)
+struct Div31 { u32 m, sh; };
+inline Div31 make_div31(u32 d) {
+    int L = 0;
+    while ((1ull << L) < d) L++;
+    Div31 r; r.sh = 31u + (u32)L; r.m = (u32)(((1ull << r.sh) / d) + 1ull);
+    return r;
+}
+
+// DIRECT: `pairs` is the caller's packed state array (ewn_playouts): Philox root id from root_ids (or the index), child tag 7,
+// result slot = index, and a state that is already finished is settled when it is picked up.
+// otherwise: `pairs` are the records k_mc_expand wrote (never finished states).
+// n_pairs * count < 2^31 (the host slices larger jobs), so all game indexing is 32-bit.
+template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playouts(const void* pairs, const u32* root_ids, const int* n_pairs_dev,
+                                                                                  u32 n_pairs_host, u32 first, u32 count, Div31 dv, u32* wins,
+                                                                                  unsigned long long* plies, Geo geo, const RoundKeys rk) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
     const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);       // legal directions of a cube: one LDS (two cubes per ply)
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int64_t warp_id = ((int64_t)blockIdx.x * TPB + threadIdx.x) >> 5;
-    const int64_t n_warps = ((int64_t)gridDim.x * TPB) >> 5;
-    const int64_t n_pairs = n_pairs_dev ? (int64_t)*n_pairs_dev : n_pairs_host;
-    const int64_t total = n_pairs * (int64_t)count;
+    const u32 warp_id = (blockIdx.x * TPB + threadIdx.x) >> 5;
+    const u32 n_warps = (gridDim.x * TPB) >> 5;
+    const u32 n_pairs = n_pairs_dev ? (u32)*n_pairs_dev : n_pairs_host;
+    const u32 total = n_pairs * count;
     // Games are dealt to warps in chunks of CH consecutive games, round-robin (chunk c belongs to warp c % n_warps): playout
     // length depends on the root position, so a warp that owned ONE contiguous range of ~1,500 games of one or two roots
     // would finish much earlier or later than its neighbours; many small chunks average over the roots.
-    constexpr int CH = 128;
-    const int64_t n_chunks = (total + CH - 1) / CH;
-    const int64_t my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
-    int64_t tnext = 0;                                         // warp-uniform cursor over the warp's local game indices
-    const int64_t tend = my_chunks * CH;
+    constexpr u32 CH = 128;
+    const u32 n_chunks = (total + CH - 1) / CH;
+    const u32 my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
+    u32 tnext = 0;                                             // warp-uniform cursor over the warp's local game indices
+    const u32 tend = my_chunks * CH;
     if (tend == 0) return;
 
     Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
@@ -859,26 +899,30 @@ template <class C> __global__ void __launch_bounds__(TPB) k_playouts(const u64* 
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !busy);
         if (need) {
-            const u32 rank = (u32)__popc(need & lt), taken = (u32)__popc(need);
-            const int64_t t = tnext + rank;
+            const u32 t = tnext + (u32)__popc(need & lt);
             if (!busy && t < tend) {
-                const int64_t gi = ((t / CH) * n_warps + warp_id) * CH + (t % CH);      // global game index
+                const u32 gi = ((t / CH) * n_warps + warp_id) * CH + (t % CH);          // global game index
                 if (gi < total) {
-                    const int64_t pair = gi / count;
-                    pidx = first + (u32)(gi - pair * count);
-                    unpack(g, pair_state, pair);
-                    rid = pair_root ? pair_root[pair] : (u32)pair;
-                    child = pair_child ? pair_child[pair] : 7u;
-                    slot = pair_slot ? pair_slot[pair] : (u32)pair;
+                    const u32 pair = (u32)(((u64)gi * dv.m) >> dv.sh);
+                    pidx = first + (gi - pair * count);
                     j = 0;
                     busy = true;
-                    if (full_win<C>(g, geo)) {                   // mcts.py:28: the loop body never runs
-                        if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
-                        busy = false;
+                    if (DIRECT) {
+                        unpack(g, reinterpret_cast<const u64*>(pairs), pair);
+                        rid = root_ids ? root_ids[pair] : pair;
+                        child = 7u; slot = pair;
+                        if (full_win<C>(g, geo)) {               // mcts.py:28: the loop body never runs
+                            if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
+                            busy = false;
+                        }
+                    } else {
+                        u32 sc;
+                        PairRec<C>::load(pairs, pair, g, rid, sc);
+                        child = sc & 7u; slot = sc >> 3;
                     }
                 }
             }
-            tnext += taken;
+            tnext += (u32)__popc(need);
             if (!__ballot_sync(0xffffffffu, busy) && tnext >= tend) break;
         }
         if (busy) {
@@ -1021,6 +1065,24 @@ template <class C> int playout_grid(int64_t total_games) {
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return (int)blocks;
+}
+
+// k_playouts indexes games with 32 bits: a job of 2^31 games or more runs as several launches over slices of the playout
+// index range (results depend only on the global playout index, so the slicing is invisible)
+template <class C, bool DIRECT>
+static int launch_playouts(const void* pairs, const uint32_t* root_ids, const int* n_pairs_dev, int64_t max_pairs, uint32_t first, uint32_t count,
+                           uint32_t* wins, unsigned long long* plies, const Geo& geo, uint64_t seed, cudaStream_t st) {
+    const RoundKeys rk = make_round_keys(seed);
+    const int64_t lim = (((int64_t)1 << 31) - 256) / (max_pairs > 0 ? max_pairs : 1);
+    if (lim < 1) return EWN_ENOSUP;                       // more than 2^31 pairs in one call
+    for (uint64_t done = 0; done < count;) {
+        const uint32_t c = (uint32_t)((count - done) < (uint64_t)lim ? (count - done) : (uint64_t)lim);
+        const int grid = playout_grid<C>(max_pairs * (int64_t)c);
+        k_playouts<C, DIRECT><<<grid, TPB, 0, st>>>(pairs, root_ids, n_pairs_dev, (u32)max_pairs, first + (uint32_t)done, c, make_div31(c), wins, plies, geo, rk);
+        LAUNCHED("k_playouts");
+        done += c;
+    }
+    return EWN_OK;
 }
 
 #define DISPATCH(N, expr_p5, expr_p8) \
@@ -1367,7 +1429,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
 
 size_t ewn_mc_workspace(int64_t n) {
     if (n <= 0) return 0;
-    return 256 + (size_t)n * 6 * (16 + 4 + 4 + 4);
+    return 256 + (size_t)n * 6 * 32;      // counter + one record (16 B for board_size <= 5, 32 B above) per (root, child)
 }
 
 int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
@@ -1377,11 +1439,8 @@ int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int
     if (n == 0 || count == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    const int grid = use_p5(N) ? playout_grid<P5>(n * (int64_t)count) : playout_grid<P8>(n * (int64_t)count);
-    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
-    else           k_playouts<P8><<<grid, TPB, 0, st>>>(state, root_ids, nullptr, nullptr, nullptr, n, first, count, wins, plies, geo, make_round_keys(seed));
-    LAUNCHED("k_playouts");
-    return EWN_OK;
+    return use_p5(N) ? launch_playouts<P5, true>(state, root_ids, nullptr, n, first, count, wins, plies, geo, seed, st)
+                     : launch_playouts<P8, true>(state, root_ids, nullptr, n, first, count, wins, plies, geo, seed, st);
 }
 
 int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
@@ -1389,6 +1448,7 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
     if (L != 3) return EWN_ENOSUP;
     if (n == 0) return EWN_OK;
+    if (n > ((int64_t)1 << 28)) return EWN_ENOSUP;        // slot * 8 + child is a 32-bit word
     const size_t need = ewn_mc_workspace(n);
     if (!workspace || workspace_bytes == 0) {
         int rc = scratch_get(need, &workspace);
@@ -1399,20 +1459,14 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     char* w = (char*)workspace;
     PairBuf pb;
     pb.n_pairs = (int*)w;
-    pb.state = (u64*)(w + 256);
-    pb.root_id = (u32*)(w + 256 + (size_t)n * 6 * 16);
-    pb.child = pb.root_id + (size_t)n * 6;
-    pb.slot = pb.child + (size_t)n * 6;
+    pb.rec = w + 256;
     CU(cudaMemsetAsync(pb.n_pairs, 0, sizeof(int), st));
-    if (use_p5(N)) k_mc_expand<P5><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children);
-    else           k_mc_expand<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children);
+    if (use_p5(N)) k_mc_expand<P5><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children, count, wins);
+    else           k_mc_expand<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children, count, wins);
     LAUNCHED("k_mc_expand");
     if (count == 0) return EWN_OK;
-    const int grid = use_p5(N) ? playout_grid<P5>(n * 6 * (int64_t)count) : playout_grid<P8>(n * 6 * (int64_t)count);
-    if (use_p5(N)) k_playouts<P5><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
-    else           k_playouts<P8><<<grid, TPB, 0, st>>>(pb.state, pb.root_id, pb.child, pb.slot, pb.n_pairs, 0, first, count, wins, plies, geo, make_round_keys(seed));
-    LAUNCHED("k_playouts");
-    return EWN_OK;
+    return use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st)
+                     : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st);
 }
 
 int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void* stream) {
