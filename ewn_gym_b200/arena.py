@@ -56,13 +56,19 @@ class MinimaxPolicy(BatchPolicy):
 class MonteCarloPolicy(BatchPolicy):
     """num_simulations * num_env_copies playouts per root action, first arg-max (mcts.py:47-69)"""
 
-    def __init__(self, num_simulations: int = 10, num_env_copies: int = 5, seed: int = 0):
-        self.playouts, self.seed = int(num_simulations) * int(num_env_copies), int(seed)
+    def __init__(self, num_simulations: int = 10, num_env_copies: int = 5, seed: int = 0, exchange=None):
+        """exchange: a peer.PeerExchange sized for the batch -> every rank of the node plays 1/world of each root action's playouts
+        and the counters are merged by one kernel over NVLink peer memory (all ranks hold the same games and get the same moves)"""
+        self.playouts, self.seed, self.exchange = int(num_simulations) * int(num_env_copies), int(seed), exchange
         self.name = f"mcts({self.playouts})"
 
     def action(self, engine, state, ply):
         n = int(state.shape[0])
         rid = engine.xp.asarray((np.arange(n, dtype=np.int64) + ply * n).astype(np.uint32), "u32")   # fresh playout streams per ply
+        if self.exchange is not None:
+            from .sharding import mc_predict_peers
+            a, _ = mc_predict_peers(engine, self.exchange, state, self.seed, self.playouts, root_ids=rid)
+            return engine.xp.asarray(a, "i32")
         wins, _ = engine.mc_root_wins(state, self.seed, 0, self.playouts, root_ids=rid)
         return engine.xp.asarray(engine.mc_best_action(state, wins), "i32")
 

@@ -123,9 +123,14 @@ def _worker(rank, world, port, q):
             a2, w2 = mc_predict_sharded(e, roots, SEED + it, 40)
             out.append((to_np(a).copy(), to_np(tot).copy(), to_np(a2).copy(), to_np(w2).copy()))
         ex.check()
+        # a whole arena with the Monte-Carlo agent sharded over the ranks: same games, same moves, same winners as one rank
+        from ewn_gym_b200.arena import MonteCarloPolicy, RandomPolicy, play_matches
+        ex2 = PeerExchange(e, 512)
+        r = play_matches(e, MonteCarloPolicy(4, 5, seed=3, exchange=ex2), RandomPolicy(seed=5), 512, seed=11)
+        ex2.check()
         dist.barrier()
-        ex.close()
-        q.put((rank, out))
+        ex.close(); ex2.close()
+        q.put((rank, out, r["winner"].copy()))
     finally:
         dist.destroy_process_group()
 
@@ -147,10 +152,15 @@ def test_processes_merge_over_nvlink(world):
         assert p.exitcode == 0
     e = make_engine("cuda", 5, 3)
     roots = _roots(e, 1000)
+    from ewn_gym_b200.arena import MonteCarloPolicy, RandomPolicy, play_matches
+    solo = play_matches(e, MonteCarloPolicy(4, 5, seed=3), RandomPolicy(seed=5), 512, seed=11)
+    assert solo["unfinished"] == 0 and solo["agent_wins"] > 300                 # 20 playouts per action already beat random
+    for rank, out, winner in res:
+        assert np.array_equal(winner, solo["winner"])
     for it in range(5):
         one, _ = e.mc_root_wins(roots, SEED + it, 0, 40)
         want = to_np(e.mc_best_action(roots, one))
-        for rank, out in res:
+        for rank, out, _w in res:
             a, tot, a2, w2 = out[it]
             assert np.array_equal(tot, to_np(one)) and np.array_equal(w2, to_np(one))
             assert np.array_equal(a, want) and np.array_equal(a2, want)
