@@ -423,3 +423,30 @@ def test_eval_random_aggregate_counts_from_seeds(backend):
         seeds = np.arange(r["first_seed"], r["first_seed"] + r["games"], dtype=np.uint32)
         res, steps, _, _ = e.numpy_random_games(seeds)
         assert int((to_np(res) > 0).sum()) == r["wins"] and int(to_np(steps).sum()) == r["agent_steps"], key
+
+
+def test_playout_jobs_beyond_2_31_games_are_sliced(backend):
+    """k_playouts indexes games with 32 bits; the library slices a bigger job over the playout index range (ewn_kernels.cu
+    launch_playouts).  A sliced call must equal the same range played as explicit pieces that each fit one launch."""
+    if backend != "cuda":
+        pytest.skip("2^31 playouts: GPU only")
+    z = load("minimax_5x5.npz")
+    e = make_engine(backend, 5, 3)
+    # Monte-Carlo path: 4,096 roots -> the launch limit is (2^31 - 256) / 24,576 = 87,381 playouts per child
+    n = 4096
+    idx = np.arange(n) % len(z["boards"])
+    st = e.encode(z["boards"][idx].astype(np.int16), z["dice"][idx].astype(np.int32))
+    whole, nch = e.mc_root_wins(st, seed=5, first=3, count=100_000)
+    parts, _ = e.mc_root_wins(st, seed=5, first=3, count=50_000)
+    e.mc_root_wins(st, seed=5, first=50_003, count=50_000, wins=parts)
+    w = to_np(whole).view(np.uint32)
+    assert np.array_equal(w, to_np(parts).view(np.uint32))
+    assert 0 < w.max() <= 100_000 and int(to_np(nch).sum()) > n
+    # direct path (ewn_playouts): 40,000 states x 60,000 playouts = 2.4e9 games, limit 53,687 per launch
+    m = 40_000
+    idx = np.arange(m) % len(z["boards"])
+    st = e.encode(z["boards"][idx].astype(np.int16), z["dice"][idx].astype(np.int32), np.full(m, 2, np.int32))
+    whole = e.playouts(st, seed=6, first=0, count=60_000)
+    parts = e.playouts(st, seed=6, first=0, count=30_000)
+    parts = e.playouts(st, seed=6, first=30_000, count=30_000, wins=parts)
+    assert np.array_equal(to_np(whole), to_np(parts))
