@@ -801,17 +801,32 @@ EWN_HD u64 f64_to_bits(double d) {
 }
 EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
 
-// Phase 1, one call per slot t of the deepest move level of one root (g = non-terminal root, TOP_LEFT to move):
-// walk the path root -> slot and write the record of every position this slot owns into v (the root's region).
+// Phase 1, one call per PARENT tp of the deepest move level of one root (g = non-terminal root, TOP_LEFT to move; the level
+// has 6 * 36^(m-1) slots, slot = tp * 6 + a): walk the path root -> parent once, write the record of every earlier position this
+// path owns, build the parent's legal list once and write the records of its (up to six) children.
 //   last level      : value of the chance node on that position (evaluate, six-folded when depth is even and the
 //                     game is not over: minimax.py:22-23 + :64-73 over six identical depth-0 leaves)
 //   earlier levels  : EMM_INTERIOR, or evaluate() if the game ended there (minimax.py:22-23)
 //   a >= #legal     : EMM_ABSENT
-template <class C, class G> EWN_HD void emm_expand_slot(Game<C> g, const G& geo, int depth, int heuristic, u32 t, double* v) {
+template <class C, int SIDE, class G> EWN_HD void emm_expand_children(const Game<C>& g, const G& geo, int depth, int heuristic, double* out) {
+    const Legal l = legal<C, SIDE>(g, geo, movers<C>(SIDE == SIDE_TL ? g.tl : g.br, g.dice));
+    const int cnt = legal_count(l);
+    for (int a = 0; a < 6; a++) {
+        if (a >= cnt) { out[a] = bits_to_f64(EMM_ABSENT); continue; }
+        Game<C> c = g;
+        int la, di, sh; legal_pick(l, a, la, di, sh);
+        const int tc = apply_move<C, SIDE>(c, sh, di);
+        const bool over = win_after<C, SIDE>(c, geo, tc);
+        out[a] = leaf_value<C>(c, geo, heuristic, over, SIDE == SIDE_TL ? 0 : 1, !(depth & 1) && !over);
+    }
+}
+
+template <class C, class G> EWN_HD void emm_expand_parent(Game<C> g, const G& geo, int depth, int heuristic, u32 tp, double* v) {
     const int m = emm_levels(depth);
-    u32 pow36 = (u32)emm_level_size(m) / 6;        // 36^(m-k) at level k; t % pow36 == 0 <=> this slot owns its level-k node
+    const u32 t = tp * 6u;                         // first slot of this parent at the last level
+    u32 pow36 = (u32)emm_level_size(m) / 6;        // 36^(m-k) at level k; t % pow36 == 0 <=> this path owns its level-k node
     long off = 0, lvl = 6;
-    for (int k = 1; k <= m; k++) {
+    for (int k = 1; k < m; k++) {
         const u32 idx = t / pow36;                 // node index at level k
         const bool owner = (t - idx * pow36) == 0;
         const int a = (int)(idx % 6);
@@ -827,14 +842,13 @@ template <class C, class G> EWN_HD void emm_expand_slot(Game<C> g, const G& geo,
             if (a < cnt) { int la, di, sh; legal_pick(l, a, la, di, sh); int tc = apply_move<C, SIDE_BR>(g, sh, di); over = win_after<C, SIDE_BR>(g, geo, tc); }
         }
         if (a >= cnt) { if (owner) v[off + idx] = bits_to_f64(EMM_ABSENT); return; }
-        if (k == m) {
-            v[off + idx] = leaf_value<C>(g, geo, heuristic, over, (k & 1) ? 0 : 1, !(depth & 1) && !over);
-            return;
-        }
         if (over) { if (owner) v[off + idx] = leaf_value<C>(g, geo, heuristic, true, (k & 1) ? 0 : 1, false); return; }
         if (owner) v[off + idx] = bits_to_f64(EMM_INTERIOR);
         off += lvl; lvl *= 36; pow36 /= 36;
     }
+    if (m > 1) g.dice = 1 + (int)(tp % 6);         // (slot / 6) % 6 of every child
+    if (m & 1) emm_expand_children<C, SIDE_TL>(g, geo, depth, heuristic, v + off + t);
+    else       emm_expand_children<C, SIDE_BR>(g, geo, depth, heuristic, v + off + t);
 }
 
 // Phase 2: classical_policies/minimax.py:19-73 replayed over the stored records of one root.

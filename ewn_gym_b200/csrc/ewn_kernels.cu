@@ -753,8 +753,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* 
 }
 
 // ------------------------------------------------------------------------------------------------
-// K4 expectiminimax.  Phase 1 (k_emm_expand): one thread per slot of the deepest move level walks its path from the
-// root (<= 4 plies), writes the value of every position it owns; all positions of a level are produced in parallel,
+// K4 expectiminimax.  Phase 1 (k_emm_expand): one thread per parent of the deepest move level walks its path from the
+// root (<= 3 plies), writes the value of every position it owns, then expands its up-to-six children from ONE legal list
+// (a thread per child would redo the whole path and the list six times, and 40 % of them would find no such child);
 // no inter-thread communication.  Phase 2 (k_emm_replay): one thread per root replays minimax.py:19-73 over the
 // stored values, so the reference's window hand-through at chance nodes is reproduced bit for bit.
 // ------------------------------------------------------------------------------------------------
@@ -770,14 +771,14 @@ template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64
     geol.vt = vt;
     __syncthreads();
     const int m = emm_levels(depth);
-    const u32 slots = (u32)emm_level_size(m);
+    const u32 parents = (u32)emm_level_size(m) / 6;
     const u32 gid = blockIdx.x * (u32)TPB + threadIdx.x;          // host keeps n_roots * slots below 2^31
-    if (gid >= (u32)n_roots * slots) return;
-    const u32 root = gid / slots, t = gid - root * slots;
+    if (gid >= (u32)n_roots * parents) return;
+    const u32 root = gid / parents, tp = gid - root * parents;
     Game<C> g; unpack(g, state, (long)root);
     g.player = SIDE_TL;
     if (full_win<C>(g, geo)) return;               // finished root: phase 2 evaluates it directly
-    emm_expand_slot<C>(g, geol, depth, heuristic, t, vals + (int64_t)root * emm_level_offset(m + 1));
+    emm_expand_parent<C>(g, geol, depth, heuristic, tp, vals + (int64_t)root * emm_level_offset(m + 1));
 }
 
 template <class C, int M> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const double* vals, int64_t n_roots,
@@ -1406,7 +1407,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
     for (int64_t r0 = 0; r0 < n; r0 += chunk) {
         const int64_t nr = (n - r0 < chunk) ? (n - r0) : chunk;
         const uint64_t* s0 = state + r0 * (use_p5(N) ? 1 : 2);
-        const unsigned grid1 = blocks_for(nr * slots);
+        const unsigned grid1 = blocks_for(nr * (slots / 6));
         const unsigned grid2 = (unsigned)((nr + 127) / 128);
         double* vals = (double*)workspace;
 #define LAUNCH_EMM(C)                                                                                              \

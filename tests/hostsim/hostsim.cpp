@@ -174,7 +174,7 @@ template <class C> int t_emm(const uint64_t* state, int64_t n, const Geo& geo, i
         for (int64_t r = 0; r < nr; r++) {
             Game<C> g; unpack(g, state, r0 + r); g.player = SIDE_TL;
             if (full_win<C>(g, geo)) continue;
-            for (long t = 0; t < slots; t++) emm_expand_slot<C>(g, geo, depth, heuristic, (u32)t, vals.data() + r * per_root);
+            for (long tp = 0; tp < slots / 6; tp++) emm_expand_parent<C>(g, geo, depth, heuristic, (u32)tp, vals.data() + r * per_root);
         }
         const uint64_t* s0 = state + r0 * C::WORDS;
         double* v0 = value + r0; int8_t* a0 = action ? action + 2 * r0 : nullptr;
