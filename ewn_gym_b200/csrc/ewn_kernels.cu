@@ -973,14 +973,21 @@ __device__ __forceinline__ unsigned long long global_ns() { unsigned long long t
 
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const u64* state, PeerSet ps, int rank, int world, u32 epoch,
                                                                            unsigned long long timeout_ns, u32* total, int8_t* action, int64_t n, Geo geo) {
+    // (selects instead of a run-time index: kernel parameters indexed dynamically would be copied to local memory)
+    u32* mine = ps.flags[0]; u32* theirs = ps.flags[0];
+#pragma unroll
+    for (int r = 1; r < EWN_MAX_PEERS; r++) {
+        if (r == rank) mine = ps.flags[r];
+        if (r == (int)threadIdx.x) theirs = ps.flags[r];
+    }
     // publish: the playout kernel that filled my counters precedes this kernel on the stream, so they are complete
-    if (blockIdx.x == 0 && threadIdx.x < world) { __threadfence_system(); st_release_sys(ps.flags[threadIdx.x] + rank, epoch); }
+    if (blockIdx.x == 0 && threadIdx.x < world) { __threadfence_system(); st_release_sys(theirs + rank, epoch); }
     // wait for the same epoch of every rank; the flag words live in MY memory, the spin never crosses NVLink
     if (threadIdx.x < world) {
-        const u32* f = ps.flags[rank] + threadIdx.x;
+        const u32* f = mine + threadIdx.x;
         unsigned long long t0 = global_ns();
         while ((int)(ld_acquire_sys(f) - epoch) < 0) {
-            if (global_ns() - t0 > timeout_ns) { atomicExch(ps.flags[rank] + EWN_PEER_ERR_WORD, epoch); break; }
+            if (global_ns() - t0 > timeout_ns) { atomicExch(mine + EWN_PEER_ERR_WORD, epoch); break; }
             __nanosleep(64);
         }
     }
@@ -1012,8 +1019,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
     if (!full_win<C>(g, geo)) {
         Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
         int cnt = legal_count(l), best = 0;
+        u32 bv = sum[0];
 #pragma unroll
-        for (int j = 1; j < 6; j++) if (j < cnt && sum[j] > sum[best]) best = j;                  // np.argmax: first maximum
+        for (int j = 1; j < 6; j++) if (j < cnt && sum[j] > bv) { best = j; bv = sum[j]; }       // np.argmax: first maximum
         int sh; legal_pick(l, best, la, di, sh);
     }
     action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di;
