@@ -256,25 +256,34 @@ def run_ours(args, rank, world, local_rank):
             # (ewn_gym_b200/peer.py); both are timed, the product path is the peer kernel, and the moves must be identical
             from ewn_gym_b200.peer import PeerExchange
             nccl_ms = pms
-            ex = PeerExchange(e, roots_n)
+            try:
+                ex = PeerExchange(e, roots_n)     # raises on every rank or on none
+            except Exception as err:              # noqa: BLE001 - e.g. CUDA IPC not permitted on this box: the NCCL numbers stand
+                ex, merge = None, {"kind": "NCCL all-reduce + k_mc_best", "ms": nccl_ms, "peer_memory": f"unavailable: {err}"[:300]}
+            if ex is not None:
+                def decide_peers(it, count):
+                    e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=ex.wins_buffer())
+                    return ex.best_action(roots)
 
-            def decide_peers(it, count):
-                e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=ex.wins_buffer())
-                return ex.best_action(roots)
-
-            decide_peers(0, 8); decide_peers(0, 8)        # maps the peers' memory on first touch
-            peer_ms, (best_p, tot_p) = timed(decide_peers)
-            ex.check()
-            same = bool(torch.equal(best_p, best)) and bool(torch.equal(tot_p, tot_ref))
-            tt = torch.tensor([nccl_ms, peer_ms, 0.0 if same else 1.0], device=dev, dtype=torch.float64)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            nccl_ms, peer_ms, bad = (float(x) for x in tt.tolist())
-            if bad:
-                raise SystemExit("peer-memory merge differs from all-reduce + arg-max")
-            pms = peer_ms
-            merge = {"kind": "one kernel over NVLink peer memory (ewn_mc_best_action_peers)", "ms": peer_ms, "nccl_allreduce_argmax_ms": nccl_ms,
-                     "identical_to_nccl": True}
-            dist.barrier(); ex.close()
+                decide_peers(0, 8); decide_peers(0, 8)    # maps the peers' memory on first touch
+                peer_ms, (best_p, tot_p) = timed(decide_peers)
+                try:
+                    ex.check(); waited = 0.0
+                except RuntimeError:
+                    waited = 1.0                   # a wait for the peers hit its time limit: results of that decision are void
+                same = bool(torch.equal(best_p, best)) and bool(torch.equal(tot_p, tot_ref))
+                tt = torch.tensor([nccl_ms, peer_ms, 0.0 if same else 1.0, waited], device=dev, dtype=torch.float64)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                nccl_ms, peer_ms, bad, waited = (float(x) for x in tt.tolist())
+                if waited:
+                    merge = {"kind": "NCCL all-reduce + k_mc_best", "ms": nccl_ms, "peer_memory": "a wait for the peers timed out"}
+                elif bad:
+                    raise SystemExit("peer-memory merge differs from all-reduce + arg-max")
+                else:
+                    pms = peer_ms
+                    merge = {"kind": "one kernel over NVLink peer memory (ewn_mc_best_action_peers)", "ms": peer_ms,
+                             "nccl_allreduce_argmax_ms": nccl_ms, "identical_to_nccl": True}
+                dist.barrier(); ex.close()
             dist.all_reduce(plies)
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,

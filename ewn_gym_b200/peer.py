@@ -44,24 +44,46 @@ class PeerExchange:
         self.bytes = FLAG_WORDS * 4 + 2 * self.row_bytes
         self.epoch = 0
         self._own = C.c_void_p()
-        h = (C.c_ubyte * 64)()
-        with engine.xp.guard():
-            _lib.check(self.lib.ewn_peer_alloc(self.bytes, C.byref(self._own), h), "ewn_peer_alloc", self.lib)
-        mine = bytes(h)
         self._opened = []
+        h = (C.c_ubyte * 64)()
+
+        def alloc():
+            with engine.xp.guard():
+                _lib.check(self.lib.ewn_peer_alloc(self.bytes, C.byref(self._own), h), "ewn_peer_alloc", self.lib)
+            return bytes(h)
+
         if handles is not None:                                   # several ranks in one process (tests)
             self.rank, self.world = int(rank), int(world)
-            handles.append((mine, self._own.value))
+            handles.append((alloc(), self._own.value))
             self._all = None
         else:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
+                # every step below either succeeds on all ranks or raises on all ranks: a rank that failed alone would leave the
+                # others waiting in the next collective
                 self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+                try:
+                    mine, err = alloc(), None
+                except Exception as ex:                           # noqa: BLE001 - reported to every rank below
+                    mine, err = None, ex
                 every = [None] * self.world
                 dist.all_gather_object(every, mine, group=group)
+                if any(b is None for b in every):
+                    self.close()
+                    raise RuntimeError(f"peer buffer allocation failed on rank(s) {[r for r, b in enumerate(every) if b is None]}: {err}")
+                try:
+                    self._map([(b, None) for b in every])
+                    ok, err = True, None
+                except Exception as ex:                           # noqa: BLE001
+                    ok, err = False, ex
+                oks = [None] * self.world
+                dist.all_gather_object(oks, ok, group=group)
+                if not all(oks):
+                    self.close()
+                    raise RuntimeError(f"mapping the peers' buffers (CUDA IPC) failed on rank(s) {[r for r, o in enumerate(oks) if not o]}: {err}")
             else:
-                self.rank, self.world, every = 0, 1, [mine]
-            self._map([(b, None) for b in every])
+                self.rank, self.world = 0, 1
+                self._map([(alloc(), None)])
         if self.world > MAX_PEERS:
             raise ValueError(f"at most {MAX_PEERS} ranks (one NVSwitch domain)")
 
@@ -140,7 +162,8 @@ class PeerExchange:
         with xp.guard():
             for p in self._opened:
                 self.lib.ewn_peer_close(p)
-            self.lib.ewn_peer_free(self._own)
+            if self._own.value:
+                self.lib.ewn_peer_free(self._own)
         self._opened, self._own = [], None
 
     def __del__(self):
