@@ -367,12 +367,16 @@ def run_ours(args, rank, world, local_rank):
                 a1.record()
                 tot = st_roll.clone()
                 if dist: dist.all_reduce(tot)       # wins / losses / illegal endings / episodes of the whole job
-                a2.record()
+                a2.record()                         # a1..a2 = the collective PLUS the wait for the slowest rank's rollouts
+                if dist:
+                    a3, a4 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a3.record(); dist.all_reduce(tot.clone()); a4.record()     # ranks are aligned now: the collective alone
             torch.cuda.synchronize()
             ms, ar = a0.elapsed_time(a1) / reps, a0.elapsed_time(a2) - a0.elapsed_time(a1)
             if dist:
                 tt = torch.tensor([ms, ar], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms, ar = tt.tolist()
             res[name] = {"ms_per_rollout": ms, "env_steps_per_s": n7 * world * T / (ms / 1e3), "allreduce_us": 1e3 * ar,
+                         "allreduce_alone_us": 1e3 * a3.elapsed_time(a4) if dist else None,
                          "episodes": int(tot[3].item()) // reps}
         rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
                                "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
