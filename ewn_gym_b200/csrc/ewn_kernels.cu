@@ -884,8 +884,10 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     const u32 total = n_pairs * count;
     // Games are dealt to warps in chunks of CH consecutive games, round-robin (chunk c belongs to warp c % n_warps): playout
     // length depends on the root position, so a warp that owned ONE contiguous range of ~1,500 games of one or two roots
-    // would finish much earlier or later than its neighbours; many small chunks average over the roots.
-    constexpr u32 CH = 128;
+    // would finish much earlier or later than its neighbours; many small chunks average over the roots.  One warp-wide
+    // pick-up per chunk is the finest useful grain and measured best at every job size (profiles/r1_playout_chunk_sweep.txt):
+    // a decision split over 8 GPUs leaves only ~190 games per warp, and 128-game chunks then give half the warps twice the work.
+    constexpr u32 CH = 32;
     const u32 n_chunks = (total + CH - 1) / CH;
     const u32 my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
     u32 tnext = 0;                                             // warp-uniform cursor over the warp's local game indices
