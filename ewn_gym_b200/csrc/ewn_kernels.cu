@@ -551,6 +551,64 @@ template <class C, int NT> __device__ __forceinline__ void scatter_row(const Gam
     }
 }
 
+#ifndef EWN_VFLUSH
+#define EWN_VFLUSH 1
+#endif
+// Terminal rows of one block, after its loop: thread r owns finished game r of the pass (its dice, its env index and the
+// scatter of its twelve cubes into the staging tile), then the tile leaves as 16-byte vectors.  Kept out of line so that its
+// registers and schedule do not disturb the step loop.
+template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* term_board, int64_t* term_dice, int32_t* term_index, int64_t index_base,
+                                                                    Geo geo, int16_t* smb, const u64* s_term, const u32* s_who,
+                                                                    const unsigned* s_wcnt, unsigned seg, int F, int64_t row0) {
+    const int tid = (int)threadIdx.x;
+    const int NN = NT ? NT * NT : geo.N * geo.N;
+    unsigned pre[VTPB / 32 + 1];
+    pre[0] = 0;
+#pragma unroll
+    for (int w = 0; w < VTPB / 32; w++) pre[w + 1] = pre[w] + s_wcnt[w];
+    auto src = [&](int r) -> int {                                 // row r of this block's output <-> entry of the segmented list
+        int w = 0;
+#pragma unroll
+        for (int k = 1; k < VTPB / 32; k++) w += (unsigned)r >= pre[k];
+        unsigned base = 0;
+#pragma unroll
+        for (int k = 1; k < VTPB / 32; k++) base = w == k ? pre[k] : base;
+        return w * (int)seg + (r - (int)base);
+    };
+    for (int r0 = 0; r0 < F; r0 += VTPB) {                         // VTPB rows per pass through the staging tile
+        const int Fc = min(VTPB, F - r0);
+        const int64_t rowc = row0 + r0;
+        const int head = (int)(((unsigned)rowc * (unsigned)NN) & 7u);   // 16-byte phase of the destination
+        uint4* v = reinterpret_cast<uint4*>(smb);
+        const int nvec = (head + Fc * NN + 7) >> 3;
+        if (term_board) for (int k = tid; k < nvec; k += VTPB) v[k] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        if (tid < Fc) {
+            const int e = src(r0 + tid);
+            Game<C> t; unpack(t, s_term, (long)e);
+            if (term_dice) __stcs(reinterpret_cast<long long*>(term_dice) + rowc + tid, (long long)t.dice);
+            __stcs(term_index + rowc + tid, (int32_t)(index_base + (int64_t)s_who[e]));
+            if (term_board) scatter_row<C, NT>(t, geo, smb + head, tid);
+        }
+        if (!term_board) continue;
+        __syncthreads();
+        int16_t* const dst = term_board + rowc * NN - head;        // element e of the staging tile goes to dst[e]
+        const int lo = head, hi = head + Fc * NN;
+        if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+            const int v0 = (lo + 7) >> 3, v1 = hi >> 3;            // full 16-byte vectors [v0, v1)
+            const uint4* sv = reinterpret_cast<const uint4*>(smb);
+            uint4* dv = reinterpret_cast<uint4*>(dst);
+            for (int k = v0 + tid; k < v1; k += VTPB) __stcs(dv + k, sv[k]);
+            const int h1 = min(v0 << 3, hi), t0 = max(v1 << 3, h1);
+            if (tid < 8) { const int e = lo + tid; if (e < h1) dst[e] = smb[e]; }
+            else if (tid < 16) { const int e = t0 + (tid - 8); if (e < hi) dst[e] = smb[e]; }
+        } else {
+            for (int e = lo + tid; e < hi; e += VTPB) dst[e] = smb[e];
+        }
+        if (r0 + VTPB < F) __syncthreads();
+    }
+}
+
 // asynchronous copy of one game's packed state and int64 action pair into the thread's 32-byte shared slot
 template <class C> __device__ __forceinline__ void prefetch_game(unsigned slot, const u64* state, const int64_t* action, int i) {
     if (C::WORDS == 1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(slot), "l"(state + i) : "memory");
@@ -688,6 +746,11 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     }
     if (!compact) return;
     if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+#if EWN_VFLUSH
+    __syncthreads();
+    vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, F, (int64_t)s_row0);
+}
+#else
     // row r of this block's output <-> entry src(r) of the segmented list
     auto src = [&](int r) -> int {
         int w = 0;
@@ -741,6 +804,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
         if (r0 + VTPB < F) __syncthreads();
     }
 }
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // evaluate
