@@ -487,22 +487,28 @@ template <class C> EWN_HD double leaf_value(const Game<C>& g, const Geo& geo, in
     double e = evaluate<C>(g, geo, heuristic);
     return fold ? six_fold(e) : e;
 }
+#if defined(__CUDA_ARCH__)
+// index of a LIVE position's 'hybrid' value in vt (min(x, y) per cell from the shared-memory table behind geo.lut)
+template <class C> __device__ __forceinline__ long leaf_table_index(const Game<C>& g, const GeoLut& geo, bool fold) {
+    int pb = -1, nb = -1;
+    const u32 mn = geo.lut + 2u * (u32)C::LUT;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+        int a, b;
+        asm("ld.shared.s8 %0, [%1];" : "=r"(a) : "r"(mn + (u32)((g.tl >> (C::FB * k)) & C::FM)));
+        asm("ld.shared.s8 %0, [%1];" : "=r"(b) : "r"(mn + (u32)((g.br >> (C::FB * k)) & C::FM)));
+        pb = a > pb ? a : pb; nb = b > nb ? b : nb;
+    }
+    const int pc = popc(C::dead(g.tl) ^ C::ONES), nc = popc(C::dead(g.br) ^ C::ONES);
+    return emm_table_index(geo.N, fold ? 1 : 0, pb, pc, nb, nc);
+}
+#endif
 template <class C> EWN_HD double leaf_value(const Game<C>& g, const GeoLut& geo, int heuristic, bool over, int mover_br, bool fold) {
 #if defined(__CUDA_ARCH__)
     if (heuristic == H_HYBRID && geo.vt) {
         // a move that does not win from a live position leaves a live position: evaluate()'s terminal tests are `over`
         if (over) return mover_br ? -10.0 : 10.0;                          // minimax_ewn.py:42-47 (never six-folded: fold implies !over)
-        int pb = -1, nb = -1;
-        const u32 mn = geo.lut + 2u * (u32)C::LUT;
-#pragma unroll
-        for (int k = 0; k < 6; k++) {
-            int a, b;
-            asm("ld.shared.s8 %0, [%1];" : "=r"(a) : "r"(mn + (u32)((g.tl >> (C::FB * k)) & C::FM)));
-            asm("ld.shared.s8 %0, [%1];" : "=r"(b) : "r"(mn + (u32)((g.br >> (C::FB * k)) & C::FM)));
-            pb = a > pb ? a : pb; nb = b > nb ? b : nb;
-        }
-        const int pc = popc(C::dead(g.tl) ^ C::ONES), nc = popc(C::dead(g.br) ^ C::ONES);
-        return __ldg(geo.vt + emm_table_index(geo.N, fold ? 1 : 0, pb, pc, nb, nc));
+        return __ldg(geo.vt + leaf_table_index<C>(g, geo, fold));
     }
 #endif
     return leaf_value<C>(g, static_cast<const Geo&>(geo), heuristic, over, mover_br, fold);
@@ -801,6 +807,33 @@ EWN_HD u64 f64_to_bits(double d) {
 }
 EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
 
+// Record codecs.  double: the value itself (any heuristic).  uint16_t ('hybrid' with the value table vt, device only): the
+// table index of a live position, or one of four marks -- a quarter of the bytes, and sixteen records per 32-byte sector.
+static constexpr uint16_t EMM16_ABSENT = 0xFFFF, EMM16_INTERIOR = 0xFFFE, EMM16_WIN = 0xFFFD, EMM16_LOSS = 0xFFFC;
+EWN_HD void emm_mark(double* p, bool absent) { *p = bits_to_f64(absent ? EMM_ABSENT : EMM_INTERIOR); }
+EWN_HD void emm_mark(uint16_t* p, bool absent) { *p = absent ? EMM16_ABSENT : EMM16_INTERIOR; }
+EWN_HD bool emm_is_absent(double r) { return f64_to_bits(r) == EMM_ABSENT; }
+EWN_HD bool emm_is_absent(uint16_t r) { return r == EMM16_ABSENT; }
+EWN_HD bool emm_is_interior(double r) { return f64_to_bits(r) == EMM_INTERIOR; }
+EWN_HD bool emm_is_interior(uint16_t r) { return r == EMM16_INTERIOR; }
+EWN_HD double emm_value(double r, const double*) { return r; }
+EWN_HD double emm_value(uint16_t r, const double* vt) {
+    if (r >= EMM16_LOSS) return r == EMM16_WIN ? 10.0 : -10.0;
+#if defined(__CUDA_ARCH__)
+    return __ldg(vt + r);
+#else
+    return vt[r];
+#endif
+}
+template <class C, class G> EWN_HD void emm_leaf(double* p, const Game<C>& g, const G& geo, int heuristic, bool over, int mover_br, bool fold) {
+    *p = leaf_value<C>(g, geo, heuristic, over, mover_br, fold);
+}
+#if defined(__CUDA_ARCH__)
+template <class C> __device__ __forceinline__ void emm_leaf(uint16_t* p, const Game<C>& g, const GeoLut& geo, int, bool over, int mover_br, bool fold) {
+    *p = over ? (mover_br ? EMM16_LOSS : EMM16_WIN) : (uint16_t)leaf_table_index<C>(g, geo, fold);
+}
+#endif
+
 // Phase 1, one call per PARENT tp of the deepest move level of one root (g = non-terminal root, TOP_LEFT to move; the level
 // has 6 * 36^(m-1) slots, slot = tp * 6 + a): walk the path root -> parent once, write the record of every earlier position this
 // path owns, build the parent's legal list once and write the records of its (up to six) children.
@@ -808,20 +841,20 @@ EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
 //                     game is not over: minimax.py:22-23 + :64-73 over six identical depth-0 leaves)
 //   earlier levels  : EMM_INTERIOR, or evaluate() if the game ended there (minimax.py:22-23)
 //   a >= #legal     : EMM_ABSENT
-template <class C, int SIDE, class G> EWN_HD void emm_expand_children(const Game<C>& g, const G& geo, int depth, int heuristic, double* out) {
+template <class C, int SIDE, class G, class R> EWN_HD void emm_expand_children(const Game<C>& g, const G& geo, int depth, int heuristic, R* out) {
     const Legal l = legal<C, SIDE>(g, geo, movers<C>(SIDE == SIDE_TL ? g.tl : g.br, g.dice));
     const int cnt = legal_count(l);
     for (int a = 0; a < 6; a++) {
-        if (a >= cnt) { out[a] = bits_to_f64(EMM_ABSENT); continue; }
+        if (a >= cnt) { emm_mark(out + a, true); continue; }
         Game<C> c = g;
         int la, di, sh; legal_pick(l, a, la, di, sh);
         const int tc = apply_move<C, SIDE>(c, sh, di);
         const bool over = win_after<C, SIDE>(c, geo, tc);
-        out[a] = leaf_value<C>(c, geo, heuristic, over, SIDE == SIDE_TL ? 0 : 1, !(depth & 1) && !over);
+        emm_leaf<C>(out + a, c, geo, heuristic, over, SIDE == SIDE_TL ? 0 : 1, !(depth & 1) && !over);
     }
 }
 
-template <class C, class G> EWN_HD void emm_expand_parent(Game<C> g, const G& geo, int depth, int heuristic, u32 tp, double* v) {
+template <class C, class G, class R> EWN_HD void emm_expand_parent(Game<C> g, const G& geo, int depth, int heuristic, u32 tp, R* v) {
     const int m = emm_levels(depth);
     const u32 t = tp * 6u;                         // first slot of this parent at the last level
     u32 pow36 = (u32)emm_level_size(m) / 6;        // 36^(m-k) at level k; t % pow36 == 0 <=> this path owns its level-k node
@@ -841,38 +874,38 @@ template <class C, class G> EWN_HD void emm_expand_parent(Game<C> g, const G& ge
             cnt = legal_count(l);
             if (a < cnt) { int la, di, sh; legal_pick(l, a, la, di, sh); int tc = apply_move<C, SIDE_BR>(g, sh, di); over = win_after<C, SIDE_BR>(g, geo, tc); }
         }
-        if (a >= cnt) { if (owner) v[off + idx] = bits_to_f64(EMM_ABSENT); return; }
-        if (over) { if (owner) v[off + idx] = leaf_value<C>(g, geo, heuristic, true, (k & 1) ? 0 : 1, false); return; }
-        if (owner) v[off + idx] = bits_to_f64(EMM_INTERIOR);
+        if (a >= cnt) { if (owner) emm_mark(v + off + idx, true); return; }
+        if (over) { if (owner) emm_leaf<C>(v + off + idx, g, geo, heuristic, true, (k & 1) ? 0 : 1, false); return; }
+        if (owner) emm_mark(v + off + idx, false);
         off += lvl; lvl *= 36; pow36 /= 36;
     }
     if (m > 1) g.dice = 1 + (int)(tp % 6);         // (slot / 6) % 6 of every child
-    if (m & 1) emm_expand_children<C, SIDE_TL>(g, geo, depth, heuristic, v + off + t);
-    else       emm_expand_children<C, SIDE_BR>(g, geo, depth, heuristic, v + off + t);
+    if (m & 1) emm_expand_children<C, SIDE_TL, G, R>(g, geo, depth, heuristic, v + off + t);
+    else       emm_expand_children<C, SIDE_BR, G, R>(g, geo, depth, heuristic, v + off + t);
 }
 
 // Phase 2: classical_policies/minimax.py:19-73 replayed over the stored records of one root.
 template <int K, int M> struct Emm {
     static constexpr long OFF = (K == 1) ? 0 : (K == 2) ? 6 : (K == 3) ? 222 : 7998;
     // value of the chance node sitting on position `idx` of level K
-    static EWN_HD double chance(const double* v, long idx, double alpha, double beta, int pruned) {
-        double rec = v[OFF + idx];
-        if (K == M) return rec;
-        if (f64_to_bits(rec) != EMM_INTERIOR) return rec;             // finished game: minimax.py:22-23
+    template <class R> static EWN_HD double chance(const R* v, const double* vt, long idx, double alpha, double beta, int pruned) {
+        const R rec = v[OFF + idx];
+        if (K == M) return emm_value(rec, vt);
+        if (!emm_is_interior(rec)) return emm_value(rec, vt);         // finished game: minimax.py:22-23
         double e = 0.0;
         for (int die = 0; die < 6; die++) {                           // minimax.py:64-73
-            double val = Emm<K + 1, M>::move(v, idx * 6 + die, alpha, beta, pruned, nullptr);
+            double val = Emm<K + 1, M>::move(v, vt, idx * 6 + die, alpha, beta, pruned, nullptr);
             e = f64_add(e, f64_div(val, 6.0));
         }
         return e;
     }
     // value of the move node whose children are positions base*6 + a of level K (K odd: TOP_LEFT maximises)
-    static EWN_HD double move(const double* v, long base, double alpha, double beta, int pruned, int* best_a) {
+    template <class R> static EWN_HD double move(const R* v, const double* vt, long base, double alpha, double beta, int pruned, int* best_a) {
         if (K & 1) {                                                  // minimax.py:26-43
             double best = -f64_inf();
             for (int a = 0; a < 6; a++) {
-                if (f64_to_bits(v[OFF + base * 6 + a]) == EMM_ABSENT) break;
-                double val = chance(v, base * 6 + a, alpha, beta, pruned);
+                if (emm_is_absent(v[OFF + base * 6 + a])) break;
+                double val = chance(v, vt, base * 6 + a, alpha, beta, pruned);
                 if (val > best) { best = val; if (best_a) *best_a = a; }
                 alpha = alpha > best ? alpha : best;
                 if (pruned && beta <= alpha) break;
@@ -881,8 +914,8 @@ template <int K, int M> struct Emm {
         } else {                                                      // minimax.py:45-62
             double worst = f64_inf();
             for (int a = 0; a < 6; a++) {
-                if (f64_to_bits(v[OFF + base * 6 + a]) == EMM_ABSENT) break;
-                double val = chance(v, base * 6 + a, alpha, beta, pruned);
+                if (emm_is_absent(v[OFF + base * 6 + a])) break;
+                double val = chance(v, vt, base * 6 + a, alpha, beta, pruned);
                 if (val < worst) worst = val;
                 beta = beta < worst ? beta : worst;
                 if (pruned && beta <= alpha) break;
@@ -892,17 +925,17 @@ template <int K, int M> struct Emm {
     }
 };
 template <int M> struct Emm<5, M> {
-    static EWN_HD double chance(const double*, long, double, double, int) { return 0.0; }
-    static EWN_HD double move(const double*, long, double, double, int, int*) { return 0.0; }
+    template <class R> static EWN_HD double chance(const R*, const double*, long, double, double, int) { return 0.0; }
+    template <class R> static EWN_HD double move(const R*, const double*, long, double, double, int, int*) { return 0.0; }
 };
 
 // ExpectiMinimaxAgent.predict (minimax.py:89-93) for one root; (la, di) = (-1,-1) when the root is finished (action None)
-template <class C, int M> EWN_HD double emm_root(const Game<C>& g, const Geo& geo, int heuristic, int pruned, const double* v,
-                                                  int& la, int& di) {
+template <class C, int M, class R> EWN_HD double emm_root(const Game<C>& g, const Geo& geo, int heuristic, int pruned, const R* v,
+                                                           int& la, int& di, const double* vt = nullptr) {
     la = -1; di = -1;
     if (full_win<C>(g, geo)) return evaluate<C>(g, geo, heuristic);   // minimax.py:22-23
     int best_a = 0;
-    double val = Emm<1, M>::move(v, 0, -f64_inf(), f64_inf(), pruned, &best_a);
+    double val = Emm<1, M>::move(v, vt, 0, -f64_inf(), f64_inf(), pruned, &best_a);
     Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
     int sh; legal_pick(l, best_a, la, di, sh);
     return val;

@@ -828,8 +828,8 @@ __global__ void __launch_bounds__(TPB) k_emm_table(double* vt, int N) {
     if (i < emm_table_size(N)) vt[i] = emm_table_entry(N, i);
 }
 
-template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, double* vals, int64_t n_roots, Geo geo,
-                                                                       int depth, int heuristic, const double* vt) {
+template <class C, class R> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, R* vals, int64_t n_roots, Geo geo,
+                                                                                int depth, int heuristic, const double* vt) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
     GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
     geol.vt = vt;
@@ -845,15 +845,15 @@ template <class C> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64
     emm_expand_parent<C>(g, geol, depth, heuristic, tp, vals + (int64_t)root * emm_level_offset(m + 1));
 }
 
-template <class C, int M> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const double* vals, int64_t n_roots,
-                                                                               int64_t root0, Geo geo, int heuristic, int pruned,
-                                                                               double* value, int8_t* action) {
+template <class C, int M, class R> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const R* vals, const double* vt, int64_t n_roots,
+                                                                                        int64_t root0, Geo geo, int heuristic, int pruned,
+                                                                                        double* value, int8_t* action) {
     int64_t r = (int64_t)blockIdx.x * 128 + threadIdx.x;
     if (r >= n_roots) return;
     Game<C> g; unpack(g, state, root0 + r);
     g.player = SIDE_TL;
     int la, di;
-    value[root0 + r] = emm_root<C, M>(g, geo, heuristic, pruned, vals + r * emm_level_offset(M + 1), la, di);
+    value[root0 + r] = emm_root<C, M>(g, geo, heuristic, pruned, vals + r * emm_level_offset(M + 1), la, di, vt);
     if (action) { action[2 * (root0 + r)] = (int8_t)la; action[2 * (root0 + r) + 1] = (int8_t)di; }
 }
 
@@ -1465,7 +1465,9 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
     cudaStream_t st = (cudaStream_t)stream;
     const int m = emm_levels(depth);
     const double* vt = heuristic == H_HYBRID ? emm_value_table(N, st) : nullptr;      // nullptr: leaves are computed in place
-    const size_t per_root = (size_t)emm_level_offset(m + 1) * sizeof(double);
+    // 'hybrid' with the value table: 16-bit records (table index or mark) instead of doubles -- a quarter of the record traffic
+    const bool compact = vt != nullptr && emm_table_size(N) < (long)EMM16_LOSS;
+    const size_t per_root = (size_t)emm_level_offset(m + 1) * (compact ? sizeof(uint16_t) : sizeof(double));
     if (!workspace || workspace_bytes == 0) {
         size_t want = per_root * (size_t)n;
         const size_t cap = (size_t)1 << 30;
@@ -1483,20 +1485,21 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
         const uint64_t* s0 = state + r0 * (use_p5(N) ? 1 : 2);
         const unsigned grid1 = blocks_for(nr * (slots / 6));
         const unsigned grid2 = (unsigned)((nr + 127) / 128);
-        double* vals = (double*)workspace;
-#define LAUNCH_EMM(C)                                                                                              \
+#define LAUNCH_EMM(C, R)                                                                                           \
     do {                                                                                                           \
-        k_emm_expand<C><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic, vt);                               \
+        R* vals = (R*)workspace;                                                                                   \
+        k_emm_expand<C, R><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic, vt);                        \
         LAUNCHED("k_emm_expand");                                                                                  \
         switch (m) {                                                                                               \
-            case 1: k_emm_replay<C, 1><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
-            case 2: k_emm_replay<C, 2><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
-            case 3: k_emm_replay<C, 3><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
-            default: k_emm_replay<C, 4><<<grid2, 128, 0, st>>>(state, vals, nr, r0, geo, heuristic, pruned, value, action); break; \
+            case 1: k_emm_replay<C, 1, R><<<grid2, 128, 0, st>>>(state, vals, vt, nr, r0, geo, heuristic, pruned, value, action); break; \
+            case 2: k_emm_replay<C, 2, R><<<grid2, 128, 0, st>>>(state, vals, vt, nr, r0, geo, heuristic, pruned, value, action); break; \
+            case 3: k_emm_replay<C, 3, R><<<grid2, 128, 0, st>>>(state, vals, vt, nr, r0, geo, heuristic, pruned, value, action); break; \
+            default: k_emm_replay<C, 4, R><<<grid2, 128, 0, st>>>(state, vals, vt, nr, r0, geo, heuristic, pruned, value, action); break; \
         }                                                                                                          \
         LAUNCHED("k_emm_replay");                                                                                  \
     } while (0)
-        if (use_p5(N)) LAUNCH_EMM(P5); else LAUNCH_EMM(P8);
+        if (use_p5(N)) { if (compact) LAUNCH_EMM(P5, uint16_t); else LAUNCH_EMM(P5, double); }
+        else           { if (compact) LAUNCH_EMM(P8, uint16_t); else LAUNCH_EMM(P8, double); }
 #undef LAUNCH_EMM
     }
     return EWN_OK;
