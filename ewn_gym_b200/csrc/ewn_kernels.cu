@@ -554,6 +554,9 @@ template <class C, int NT> __device__ __forceinline__ void scatter_row(const Gam
 #ifndef EWN_VFLUSH
 #define EWN_VFLUSH 1
 #endif
+#ifndef EWN_VPRE
+#define EWN_VPRE 1
+#endif
 // Terminal rows of one block, after its loop: thread r owns finished game r of the pass (its dice, its env index and the
 // scatter of its twelve cubes into the staging tile), then the tile leaves as 16-byte vectors.  Kept out of line so that its
 // registers and schedule do not disturb the step loop.
@@ -639,6 +642,18 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     // before the PREVIOUS grid has completed and flushed.  Both are no-ops for launches without the PDL attribute.
     asm volatile("griddepcontrol.launch_dependents;");
     if (tid == 0) { s_won = 0; s_lost = 0; }
+#if EWN_VPRE
+    // Pull the first unit's lines into L2 while the previous grid is still draining.  A prefetch has no architectural effect
+    // and L2 is the coherence point, so this is safe although the previous grid may still be writing these very addresses;
+    // the loads proper stay behind griddepcontrol.wait.
+    {
+        const int i0 = (int)blockIdx.x * VTPB + (int)tid;
+        if (i0 < n) {
+            if ((tid & 15u) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.state + (size_t)i0 * C::WORDS));
+            if ((tid & 7u) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.action_i64 + 2 * (size_t)i0));
+        }
+    }
+#endif
     const GeoLut geol = make_geo_lut<C, VTPB>(geo, s_dirs);
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (tid == 0 && a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
