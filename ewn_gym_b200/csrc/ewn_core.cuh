@@ -18,6 +18,10 @@
 //   P8 (board_size <= 9): two u64 per game (16-byte vector). word0 = TL side, word1 = BR side.
 //        side word bits [8k,8k+8) = cell of cube k+1, cell = (x<<4)|y, 0xFF = captured.
 //        word0[50:48] = dice-1, word1[48] = side to move.
+//   PG (cube_layer >= 4, i.e. 10..28 cubes per side; envs/ewn.py:47,51 allow any cube_layer < board_size - 1):
+//        2 * cw + 1 u64 per game, cw = ceil(cube_num / 8): cw TL words, cw BR words (byte k of a side = cell of cube k+1 as in P8,
+//        0xFF = captured or no such cube), then one meta word: bits [7:0] = dice, bit 8 = side to move.
+//        P5 / P8 stay the specialised six-cube fast paths; PG runs the same rule code on byte arrays.
 #pragma once
 #include <stdint.h>
 
@@ -51,14 +55,14 @@ EWN_HD int ctz_nz(u64 x) {
 }
 EWN_HD int msb_nz(u32 x) {
 #if defined(__CUDA_ARCH__)
-    return 31 - __clz((int)x);
+    int r; asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x)); return r;        // one FLO; -1 for x == 0
 #else
     return x ? 31 - __builtin_clz(x) : -1;
 #endif
 }
 EWN_HD int msb_nz(u64 x) {
 #if defined(__CUDA_ARCH__)
-    return 63 - __clzll((long long)x);
+    int r; asm("bfind.u64 %0, %1;" : "=r"(r) : "l"(x)); return r;
 #else
     return x ? 63 - __builtin_clzll(x) : -1;
 #endif
@@ -121,7 +125,9 @@ struct Geo {
     int32_t N, L, cube_num;
     int32_t corner;                          // packed cell of (N-1, N-1)
     u32 tl_col, tl_row, br_col, br_row;      // P5 only: cells from which dir 0 / dir 1 leaves the board
-    u64 tl0, br0;                            // side words of the initial layout (envs/ewn.py:94-107)
+    u64 tl0, br0;                            // side words of the initial layout (envs/ewn.py:94-107); PG: word 0 of g_tl0 / g_br0
+    int32_t cw, sw;                          // PG: u64 words per side / per game (P5: 0 / 1, P8: 0 / 2)
+    u64 g_tl0[4], g_br0[4];                  // PG: the initial layout, unused bytes 0xFF
 };
 
 // Geo plus the shared-memory address of a per-block table  dirs[side][cell]  (k_vstep, k_playouts): the legal-direction set of
@@ -153,6 +159,12 @@ struct P5 {
         u32 ok0 = ~(e0 >> c) & 1u, ok1 = ~(e1 >> c) & 1u;
         return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
     }
+    static constexpr bool GENERIC = false;
+    static constexpr int MAXC = 6;
+    static EWN_HD W all() { return ALL; }
+    static EWN_HD int get(W s, int k) { return (int)((s >> (FB * k)) & FM); }
+    static EWN_HD void set(W& s, int k, int c) { s = (s & ~(FM << (FB * k))) | ((W)c << (FB * k)); }
+    static EWN_HD int ncubes(const Geo&) { return 6; }
     static constexpr int LUT = 32;                                   // table entries per side (every 5-bit field value)
     template <int BR> static EWN_HD int dirs(const GeoLut& g, int c) {
 #if defined(__CUDA_ARCH__)
@@ -177,6 +189,12 @@ struct P8 {
         u32 ok0 = BR ? (y > 0) : (y < g.N - 1), ok1 = BR ? (x > 0) : (x < g.N - 1);
         return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
     }
+    static constexpr bool GENERIC = false;
+    static constexpr int MAXC = 6;
+    static EWN_HD W all() { return ALL; }
+    static EWN_HD int get(W s, int k) { return (int)((s >> (FB * k)) & FM); }
+    static EWN_HD void set(W& s, int k, int c) { s = (s & ~(FM << (FB * k))) | ((W)c << (FB * k)); }
+    static EWN_HD int ncubes(const Geo&) { return 6; }
     static constexpr int LUT = 256;
     template <int BR> static EWN_HD int dirs(const GeoLut& g, int c) {
 #if defined(__CUDA_ARCH__)
@@ -185,6 +203,54 @@ struct P8 {
         return dirs<BR>(static_cast<const Geo&>(g), c);
 #endif
     }
+};
+
+// Generic codec: up to 32 cubes per side, one byte per cube ((x << 4) | y, 0xFF = captured / no such cube), four u64 words per
+// side in registers (words are picked with selects, never with a run-time index, so nothing spills to local memory).
+struct PG {
+    struct W { u64 w[4]; };
+    static constexpr bool GENERIC = true;
+    static constexpr int FB = 8, S = 16, WORDS = 9, MAXN = 9, MAXC = 32, LUT = 256;
+    static constexpr u64 FM = 0xFFull, ONES = 0x0101010101010101ull, LOWS = ONES * 0x7Full, HIGHS = ONES << 7;
+    static EWN_HD int cell(int x, int y) { return (x << 4) | y; }
+    static EWN_HD int x_of(int c) { return c >> 4; }
+    static EWN_HD int y_of(int c) { return c & 15; }
+    template <int BR, class G> static EWN_HD int dirs(const G& g, int c) {
+        int x = c >> 4, y = c & 15;
+        u32 ok0 = BR ? (y > 0) : (y < g.N - 1), ok1 = BR ? (x > 0) : (x < g.N - 1);
+        return (int)(ok0 | (ok1 << 1) | ((ok0 & ok1) << 2));
+    }
+    static EWN_HD W all() { W s; s.w[0] = s.w[1] = s.w[2] = s.w[3] = ~0ull; return s; }
+    static EWN_HD int ncubes(const Geo& g) { return g.cube_num; }
+    static EWN_HD u64 word(const W& s, int j) { return j == 0 ? s.w[0] : j == 1 ? s.w[1] : j == 2 ? s.w[2] : s.w[3]; }
+    static EWN_HD int get(const W& s, int k) { return (int)((word(s, k >> 3) >> (8 * (k & 7))) & 0xFFull); }
+    static EWN_HD void set(W& s, int k, int c) {
+        const int j = k >> 3, sh = 8 * (k & 7);
+        const u64 clr = ~(0xFFull << sh), ins = (u64)c << sh;
+#pragma unroll
+        for (int q = 0; q < 4; q++) if (q == j) s.w[q] = (s.w[q] & clr) | ins;
+    }
+    // bit k set <=> cube k+1 stands on the board
+    static EWN_HD u32 alive(const W& s) {
+        u32 dead = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            u64 t = s.w[q] & (s.w[q] >> 4); t &= t >> 2; t &= t >> 1; t &= ONES;       // bit 8i <=> byte i == 0xFF
+            dead |= (u32)((t * 0x0102040810204080ull) >> 56) << (8 * q);               // gather the eight flags into one byte
+        }
+        return ~dead;
+    }
+    static EWN_HD u64 match1(u64 w, u64 rep) { u64 x = w ^ rep; return ((((x & LOWS) + LOWS) | x) & HIGHS) ^ HIGHS; }
+    static EWN_HD bool any_at(const W& s, int c) {
+        const u64 rep = (u64)c * ONES;
+        return (match1(s.w[0], rep) | match1(s.w[1], rep) | match1(s.w[2], rep) | match1(s.w[3], rep)) != 0;
+    }
+    static EWN_HD void capture(W& s, int c) {                        // envs/ewn.py:254-258
+        const u64 rep = (u64)c * ONES;
+#pragma unroll
+        for (int q = 0; q < 4; q++) { const u64 z = match1(s.w[q], rep); s.w[q] |= (z << 1) - (z >> 7); }
+    }
+    static EWN_HD bool all_dead(const W& s) { return (s.w[0] & s.w[1] & s.w[2] & s.w[3]) == ~0ull; }
 };
 
 template <class C> struct Game {
@@ -939,6 +1005,168 @@ template <class C, int M, class R> EWN_HD double emm_root(const Game<C>& g, cons
     Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
     int sh; legal_pick(l, best_a, la, di, sh);
     return val;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused depth-3 / depth-4 expectiminimax (the closed-form prefix rule).  Tree of minimax.py:19-73 at these depths:
+//   root MAX (TOP_LEFT, <= 6 moves a1)  ->  CHANCE (6 faces d2)  ->  MIN (BOTTOM_RIGHT, <= 6 moves a2)  ->  leaf
+//   leaf = evaluate (depth 3), or the chance node over six identical depth-0 evaluations (depth 4: six_fold), or +-10 when the
+//   move ended the game.  Leaf values do not depend on the (alpha, beta) window, beta is +inf everywhere (the root never lowers
+//   it), so the only cut is the MIN node's `beta <= alpha` against the ROOT's running alpha: a MIN node returns its first
+//   prefix-minimum <= alpha, else its full minimum (minimax.py:53-58).  alpha only changes between root children, so the a1 loop
+//   is the one sequential dimension; the six dice of one root child are independent given alpha.
+// Leaves are not materialised: a MIN-level move changes one cube of the mover and captures at most one cube, and every heuristic
+// of envs/minimax_ewn.py depends only on the per-side multiset of min(x, y) over alive cubes, kept as a histogram word.
+// ------------------------------------------------------------------------------------------------
+// histogram word of one side: 3-bit field v = number of alive cubes with min(x, y) == v (v <= 8, count <= 6)
+EWN_HD u32 hist_unit(int mn) { return 1u << (3 * mn); }
+EWN_HD int hist_best(u32 h) { return (msb_nz(h | 1u) * 11) >> 5; }                          // largest v with a non-zero field (0 if none)
+EWN_HD int hist_second(u32 h) { return hist_best(h - hist_unit(hist_best(h))); }             // second largest, multiplicity counted
+
+// per-block tables of the fused kernel (shared memory on the device, plain arrays on the host):
+//   inc[cell] = hist_unit(min(x, y)), 0 for the captured sentinel and for cells off the board
+//   v / q     = 'hybrid' leaf values of the fold the depth needs and their quotients v / 6 (what minimax.py:72 adds up; looked up,
+//               so the hot loop has no fp64 division), index [pb][pc-1][nb][nc-1]; both pointers are EMM_PAD(N) entries into
+//               their arrays so that the summaries of slots that are not legal (pc - 1 = -1 ...) still index allocated memory;
+//               entry -1 holds the value of a lost game (-10).  v == nullptr: values are computed in place.
+struct EmmTabs { const u32* inc; const double* v; const double* q; };
+EWN_HD int emm_pad(int N) { return 12 * N + 8; }
+EWN_HD int emm_tab_entries(int N) { return N * 6 * N * 6; }
+template <class C> EWN_HD u32 emm_inc_entry(int N, int c) {
+    const int x = C::x_of(c), y = C::y_of(c);
+    if (c == (int)C::FM || x >= N || y >= N) return 0u;
+    return hist_unit(x < y ? x : y);
+}
+template <class C> EWN_HD u32 side_hist(typename C::W side, const EmmTabs& tb) {
+    u32 h = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) h += tb.inc[(int)((side >> (C::FB * k)) & C::FM)];
+    return h;
+}
+// occupancy bit board of one side (P5 only: cell < 32; bit 31 collects the captured cubes and is never a target)
+EWN_HD u32 side_occ(u32 side) {
+    u32 o = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) o |= 1u << ((side >> (5 * k)) & 31u);
+    return o;
+}
+EWN_HD u32 side_occ(u64) { return 0u; }
+// envs/minimax_ewn.py:29-213 on the summary of a LIVE position (N - min_dist = 1 + best), computed in place;
+// fold = minimax.py:64-73 over six equal leaves
+EWN_HD double emm_summary_value(int heuristic, int N, u32 htl, int pc, u32 hbr, int nc, bool fold) {
+    const int pb = hist_best(htl), nb = hist_best(hbr);
+    double v;
+    if (heuristic == H_HYBRID) v = f64_sub(f64_mul((double)(1 + pb), inv_count(pc)), f64_mul((double)(1 + nb), inv_count(nc)));
+    else if (heuristic == H_MIN_DIST) v = (double)(pb - nb);
+    else if (heuristic == H_TWO_MIN_DIST) {
+        const int sp = (N - 1 - pb) + (pc >= 2 ? (N - 1 - hist_second(htl)) : 0);
+        const int sn = (N - 1 - nb) + (nc >= 2 ? (N - 1 - hist_second(hbr)) : 0);
+        v = (double)(sn - sp);
+    } else v = (double)(-(pc + nc));
+    return fold ? six_fold(v) : v;
+}
+
+// what the six (root child, die) workers need to know about one root child: the position after TOP_LEFT's move and its summaries.
+// meta: bits 0-15 = 1024 + (pc - 1) * 6N + (nc - 1) (the count part of the value-table index), 16-18 = pc, 19-21 = nc,
+//       30 = the move ended the game (TOP_LEFT won), 31 = the child exists (a1 < #legal)
+template <class C> struct EmmChild {
+    typename C::W tl, br;
+    u32 htl, hbr, otl, obr, meta;
+};
+static constexpr u32 EMMC_EXISTS = 0x80000000u, EMMC_OVER = 0x40000000u;
+
+template <class C, class G> EWN_HD EmmChild<C> emm2_child(const Game<C>& root, const G& geo, const EmmTabs& tb, int k) {
+    EmmChild<C> ch;
+    Game<C> g = root;
+    const Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+    u32 flags = 0;
+    if (k < legal_count(l)) {
+        int la, di, sh; legal_pick(l, k, la, di, sh);
+        const int t = apply_move<C, SIDE_TL>(g, sh, di);
+        flags = EMMC_EXISTS | (win_after<C, SIDE_TL>(g, geo, t) ? EMMC_OVER : 0u);
+    }
+    ch.tl = g.tl; ch.br = g.br;
+    ch.htl = side_hist<C>(g.tl, tb); ch.hbr = side_hist<C>(g.br, tb);
+    ch.otl = side_occ(g.tl); ch.obr = side_occ(g.br);
+    const int pc = popc(C::dead(g.tl) ^ C::ONES), nc = popc(C::dead(g.br) ^ C::ONES);
+    ch.meta = (u32)(1024 + (pc - 1) * 6 * geo.N + (nc - 1)) | ((u32)pc << 16) | ((u32)nc << 19) | flags;
+    return ch;
+}
+
+// MIN node under root child `ch` with die `die` (1..6): minimax.py:45-62 with beta = +inf on entry.  `alpha` = the root's running
+// alpha (-inf for the unpruned search).  Six fixed slots = (larger neighbour | dice cube, smaller neighbour) x direction, in the
+// order of the legal list (envs/ewn.py:338-375); slots that are not legal never update the minimum.  Returns the node's value
+// and, through q, value / 6.
+template <bool TAB, class C, class G> EWN_HD double emm2_min(const EmmChild<C>& ch, const G& geo, const EmmTabs& tb, int die, int heuristic, bool fold,
+                                                              double alpha, double& q) {
+    typedef typename C::W W;
+    Game<C> g; g.tl = ch.tl; g.br = ch.br; g.dice = die; g.player = SIDE_BR;
+    const Legal l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, die));
+    const int N = geo.N;
+    const int kbase = (int)(ch.meta & 0xFFFFu) - 1024, pc = (int)((ch.meta >> 16) & 7u), nc = (int)((ch.meta >> 19) & 7u);
+    double worst = f64_inf();
+    int worst_i = -1;
+    bool cut = false;
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+        const int set = s ? l.second : l.first, sh = s ? l.sh_second : l.sh_first;
+        const int c = cell_at<C>(g.br, sh & (int)(8 * sizeof(W) - 1));
+        const u32 inc_c = sh >= 0 ? tb.inc[c] : 0u;                            // no such mover: keep the histogram arithmetic borrow-free
+#pragma unroll
+        for (int dir = 0; dir < 3; dir++) {
+            const int delta = (dir != 1) + C::S * (dir != 0);                 // envs/ewn.py:301-319, BOTTOM_RIGHT moves towards (0, 0)
+            const int t = (c - delta) & (C::LUT - 1);                          // in range for every legal slot; wrapped garbage otherwise
+            bool cap_t, cap_b;                                                 // envs/ewn.py:254-258: whatever stands on t is captured
+            if (C::WORDS == 1) { cap_t = (ch.otl >> t) & 1u; cap_b = (ch.obr >> t) & 1u; }
+            else { const W rep = (W)t * C::ONES; cap_t = match<C>(g.tl, rep) != 0; cap_b = match<C>(g.br, rep) != 0; }
+            const u32 inc_t = tb.inc[t];
+            const u32 h_tl = ch.htl - (cap_t ? inc_t : 0u);
+            const u32 h_br = ch.hbr - inc_c + (cap_b ? 0u : inc_t);
+            const bool over = t == 0 || (cap_t && pc == 1);                    // check_win after BOTTOM_RIGHT's move
+            double v; int idx = -1;
+            if (TAB) {
+                idx = hist_best(h_tl) * (36 * N) + hist_best(h_br) * 6 + kbase - (cap_t ? 6 * N : 0) - (cap_b ? 1 : 0);
+                idx = over ? -1 : idx;                                         // entry -1: minimax_ewn.py:45-47, -10
+                v = tb.v[idx];
+            } else {
+                v = over ? -10.0 : emm_summary_value(heuristic, N, h_tl, pc - (cap_t ? 1 : 0), h_br, nc - (cap_b ? 1 : 0), fold);
+            }
+            const bool take = ((set >> dir) & 1) && !cut;
+            if (take && v < worst) { worst = v; worst_i = idx; }
+            cut = cut || (take && worst <= alpha);
+        }
+    }
+    q = TAB ? tb.q[worst_i] : f64_div(worst, 6.0);
+    return worst;
+}
+
+// ExpectiMinimaxAgent.predict at depth 3 or 4 for one root, one worker doing everything (host simulator; the CUDA kernel spreads the
+// same calls over six lanes per root, see k_emm_fused)
+template <class C, class G> EWN_HD double emm2_root_serial(const Game<C>& root, const G& geo, const EmmTabs& tb, int depth, int heuristic, int pruned,
+                                                            int& la, int& di) {
+    la = -1; di = -1;
+    if (full_win<C>(root, geo)) return evaluate<C>(root, geo, heuristic);       // minimax.py:22-23
+    const bool fold = !(depth & 1);
+    double best = -f64_inf(), alpha = -f64_inf();
+    int best_a = 0;
+    for (int a1 = 0; a1 < 6; a1++) {
+        const EmmChild<C> ch = emm2_child<C>(root, geo, tb, a1);
+        if (!(ch.meta & EMMC_EXISTS)) break;
+        double e = 0.0;
+        if (ch.meta & EMMC_OVER) e = 10.0;                                        // minimax.py:22-23 at the chance node: TOP_LEFT has won
+        else
+            for (int die = 1; die <= 6; die++) {                                  // minimax.py:64-73
+                double q;
+                if (tb.v) emm2_min<true, C>(ch, geo, tb, die, heuristic, fold, pruned ? alpha : -f64_inf(), q);
+                else      emm2_min<false, C>(ch, geo, tb, die, heuristic, fold, pruned ? alpha : -f64_inf(), q);
+                e = f64_add(e, q);
+            }
+        if (e > best) { best = e; best_a = a1; }
+        alpha = alpha > best ? alpha : best;
+    }
+    const Legal l = legal<C, SIDE_TL>(root, geo, movers<C>(root.tl, root.dice));
+    int sh; legal_pick(l, best_a, la, di, sh);
+    return best;
 }
 
 }  // namespace ewn

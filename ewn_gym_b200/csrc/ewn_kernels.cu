@@ -13,6 +13,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <atomic>
+#include <mutex>
 #include <new>
 
 #include "../../include/ewn_b200.h"
@@ -872,6 +873,91 @@ template <class C, int M, class R> __global__ void __launch_bounds__(128) k_emm_
     if (action) { action[2 * (root0 + r)] = (int8_t)la; action[2 * (root0 + r) + 1] = (int8_t)di; }
 }
 
+// K4f  depth 3 / 4 in ONE kernel, nothing but the roots and the results touches HBM (18 B per root).  Six lanes per root, lane d
+// owns die face d + 1; five roots per warp (lanes 30, 31 idle).  Lane d first plays root child d (one TOP_LEFT ply + the two
+// histogram words); then the a1 loop runs in lock step: the child of the round reaches all six lanes by shuffle, every lane
+// evaluates ITS MIN node against the running alpha (emm2_min: six move slots, leaf values from the shared 'hybrid' table),
+// and the expectation is the six v / 6 added in face order (minimax.py:64-73) from shuffles -- every lane of the group ends the
+// round with the same best / alpha, so the cut rule of minimax.py:53-58 sees exactly the reference's window.
+constexpr int FTPB = 256, FROOTS = (FTPB / 32) * 5;       // threads and roots per block
+
+// `tabs` (global, built once per board size by k_emm_fused_table): [fold][2][pad + N*6*N*6] doubles = values, then quotients
+template <class C, int H> __global__ void __launch_bounds__(FTPB) k_emm_fused(const u64* state, int64_t n_roots, Geo geo, int depth, int pruned,
+                                                                               const double* tabs, double* value, int8_t* action) {
+    extern __shared__ double s_tab[];                                 // 'hybrid' only: values [pad + entries], quotients [pad + entries]
+    __shared__ u32 s_inc[C::LUT];
+    __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
+    const GeoLut geol = make_geo_lut<C, FTPB>(geo, s_dirs);
+    for (int c = threadIdx.x; c < C::LUT; c += FTPB) s_inc[c] = emm_inc_entry<C>(geo.N, c);
+    const bool fold = !(depth & 1);
+    const int span = emm_pad(geo.N) + emm_tab_entries(geo.N);
+    if (H == H_HYBRID) {
+        const double2* src = reinterpret_cast<const double2*>(tabs + (fold ? 2 * span : 0));      // span is even
+        double2* dst = reinterpret_cast<double2*>(s_tab);
+        for (int k = threadIdx.x; k < span; k += FTPB) dst[k] = __ldg(src + k);
+    }
+    __syncthreads();
+    EmmTabs tb; tb.inc = s_inc;
+    tb.v = H == H_HYBRID ? s_tab + emm_pad(geo.N) : nullptr;
+    tb.q = H == H_HYBRID ? s_tab + span + emm_pad(geo.N) : nullptr;
+    const unsigned lane = threadIdx.x & 31u, grp = lane / 6u, d = lane - 6u * grp;
+    const int64_t r = ((int64_t)blockIdx.x * (FTPB / 32) + (threadIdx.x >> 5)) * 5 + grp;
+    const bool active = lane < 30u && r < n_roots;
+    Game<C> root; setup<C>(root, geo, 1);                             // idle lanes search the initial position and drop the result
+    if (active) { unpack(root, state, (long)r); root.player = SIDE_TL; }
+    const bool fin = full_win<C>(root, geo);
+    Game<C> work = root;
+    if (fin) setup<C>(work, geo, 1);                                  // finished roots too: every summary the tables see is of a live position
+    EmmChild<C> mine = emm2_child<C>(work, geol, tb, (int)d);
+    if (fin || !active) mine.meta &= ~EMMC_EXISTS;
+    const double ninf = -f64_inf();
+    double best = ninf, alpha = ninf;
+    int best_a = 0;
+    const unsigned g0 = grp * 6u;
+    for (unsigned a1 = 0; a1 < 6u; a1++) {
+        EmmChild<C> ch;
+        const unsigned src = g0 + a1;
+        ch.br = __shfl_sync(0xffffffffu, mine.br, src);
+        ch.htl = __shfl_sync(0xffffffffu, mine.htl, src); ch.hbr = __shfl_sync(0xffffffffu, mine.hbr, src);
+        ch.meta = __shfl_sync(0xffffffffu, mine.meta, src);
+        if (C::WORDS == 1) { ch.otl = __shfl_sync(0xffffffffu, mine.otl, src); ch.obr = __shfl_sync(0xffffffffu, mine.obr, src); ch.tl = 0; }
+        else { ch.tl = __shfl_sync(0xffffffffu, mine.tl, src); ch.otl = 0; ch.obr = 0; }
+        const bool exists = (ch.meta & EMMC_EXISTS) != 0;
+        if (!__any_sync(0xffffffffu, exists)) break;                  // children exist for a1 < #legal: no root of this warp has more
+        double q;
+        emm2_min<H == H_HYBRID, C>(ch, geol, tb, (int)d + 1, H, fold, pruned ? alpha : ninf, q);
+        double e = 0.0;
+#pragma unroll
+        for (unsigned f = 0; f < 6u; f++) e = f64_add(e, __shfl_sync(0xffffffffu, q, g0 + f));      // minimax.py:64-73, face order
+        if (ch.meta & EMMC_OVER) e = 10.0;                            // minimax.py:22-23 at the chance node: TOP_LEFT has just won
+        if (exists) {
+            if (e > best) { best = e; best_a = (int)a1; }
+            alpha = alpha > best ? alpha : best;
+        }
+    }
+    if (active && d == 0) {
+        int la = -1, di = -1;
+        if (fin) best = evaluate<C>(root, geo, H);                    // minimax.py:22-23 at the root: action None
+        else { const Legal l = legal<C, SIDE_TL>(root, geol, movers<C>(root.tl, root.dice)); int sh; legal_pick(l, best_a, la, di, sh); }
+        value[r] = best;
+        if (action) reinterpret_cast<char2*>(action)[r] = make_char2((signed char)la, (signed char)di);
+    }
+}
+
+// builds `tabs` for k_emm_fused from the value table vt[fold][pb][pc-1][nb][nc-1] (k_emm_table): per fold the padded values, then
+// the padded quotients v / 6 (IEEE division, once per entry per process instead of once per MIN node); entry pad-1 = a lost game
+__global__ void __launch_bounds__(TPB) k_emm_fused_table(const double* vt, double* tabs, int N) {
+    const int pad = emm_pad(N), ent = emm_tab_entries(N), span = pad + ent;
+    const int i = (int)(blockIdx.x * TPB + threadIdx.x);
+    if (i >= 2 * span) return;
+    const int fold = i / span, k = i - fold * span;
+    double v = 0.0;
+    if (k >= pad) v = vt[(long)fold * ent + (k - pad)];
+    else if (k == pad - 1) v = -10.0;
+    tabs[(long)fold * 2 * span + k] = v;
+    tabs[(long)fold * 2 * span + span + k] = f64_div(v, 6.0);
+}
+
 // ------------------------------------------------------------------------------------------------
 // K3 flat Monte-Carlo.  k_mc_expand turns roots into (root, child) pairs; k_playouts plays `count` random games
 // per pair with one lane per game.  Lanes that finish pull the next game of their warp's contiguous range, so a
@@ -1454,19 +1540,25 @@ size_t ewn_expectiminimax_workspace(int64_t n, int depth) {
 }
 
 // 'hybrid' leaf-value table of one board size, built once per device on first use (k_emm_table) and kept for the process
-static const double* emm_value_table(int N, cudaStream_t st) {
+// (the fused kernel's padded value / quotient tables follow the value table in the same allocation: *fused_out)
+static std::mutex g_table_mutex;
+static const double* emm_value_table(int N, cudaStream_t st, const double** fused_out = nullptr) {
     static double* tab[64][EWN_MAX_BOARD + 1] = {{nullptr}};
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    const long cnt = emm_table_size(N);
+    std::lock_guard<std::mutex> lock(g_table_mutex);
     if (!tab[dev][N]) {
         double* p = nullptr;
-        const long cnt = emm_table_size(N);
-        if (cudaMalloc(&p, (size_t)cnt * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        const long fused = 4L * (emm_pad(N) + emm_tab_entries(N));
+        if (cudaMalloc(&p, (size_t)(cnt + fused) * sizeof(double)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
         k_emm_table<<<(unsigned)((cnt + TPB - 1) / TPB), TPB, 0, st>>>(p, N);
-        g_launches.fetch_add(1, std::memory_order_relaxed);
+        k_emm_fused_table<<<(unsigned)((fused / 2 + TPB - 1) / TPB), TPB, 0, st>>>(p, p + cnt, N);
+        g_launches.fetch_add(2, std::memory_order_relaxed);
         if (cudaStreamSynchronize(st) != cudaSuccess) { cudaGetLastError(); cudaFree(p); return nullptr; }
         tab[dev][N] = p;
     }
+    if (fused_out) *fused_out = tab[dev][N] + cnt;
     return tab[dev][N];
 }
 
@@ -1479,7 +1571,26 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
     const int m = emm_levels(depth);
-    const double* vt = heuristic == H_HYBRID ? emm_value_table(N, st) : nullptr;      // nullptr: leaves are computed in place
+    const double* tabs = nullptr;
+    const double* vt = heuristic == H_HYBRID ? emm_value_table(N, st, &tabs) : nullptr;      // nullptr: leaves are computed in place
+    if (m == 2 && !(pruned & EWN_EMM_REPLAY_PATH) && (heuristic != H_HYBRID || vt)) {  // depth 3 / 4: fused, on-chip (k_emm_fused)
+        const unsigned grid = (unsigned)((n + FROOTS - 1) / FROOTS);
+        const size_t sm = heuristic == H_HYBRID ? (size_t)2 * (emm_pad(N) + emm_tab_entries(N)) * sizeof(double) : 0;
+        const int pr = pruned & 1;
+#define LAUNCH_FUSED(C)                                                                                                     \
+    if (sm > 48 * 1024) CU(cudaFuncSetAttribute(k_emm_fused<C, H_HYBRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); /* 9x9 */ \
+    switch (heuristic) {                                                                                                    \
+        case H_HYBRID: k_emm_fused<C, H_HYBRID><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break; \
+        case H_MIN_DIST: k_emm_fused<C, H_MIN_DIST><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break; \
+        case H_TWO_MIN_DIST: k_emm_fused<C, H_TWO_MIN_DIST><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break; \
+        default: k_emm_fused<C, H_ATTK><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break;          \
+    }
+        if (use_p5(N)) { LAUNCH_FUSED(P5) } else { LAUNCH_FUSED(P8) }
+#undef LAUNCH_FUSED
+        LAUNCHED("k_emm_fused");
+        return EWN_OK;
+    }
+    pruned &= 1;
     // 'hybrid' with the value table: 16-bit records (table index or mark) instead of doubles -- a quarter of the record traffic
     const bool compact = vt != nullptr && emm_table_size(N) < (long)EMM16_LOSS;
     const size_t per_root = (size_t)emm_level_offset(m + 1) * (compact ? sizeof(uint16_t) : sizeof(double));

@@ -290,11 +290,13 @@ class Engine:
                   "ewn_evaluate")
         return v
 
-    def expectiminimax(self, state, depth: int, heuristic="hybrid", pruned=True):
-        """-> (value f64[n], action i8[n,2]); action (-1,-1) = None for finished roots (minimax.py:22-23)."""
+    def expectiminimax(self, state, depth: int, heuristic="hybrid", pruned=True, replay_path=False, out=None):
+        """-> (value f64[n], action i8[n,2]); action (-1,-1) = None for finished roots (minimax.py:22-23).
+        replay_path: run depth 3 / 4 on the record + replay kernels (the depth >= 5 path) instead of the fused kernel (A/B)."""
         n = self._n(state)
-        v, a = self.xp.empty((n,), "f64"), self.xp.empty((n, 2), "i8")
-        self._chk(self.lib.ewn_expectiminimax(self.xp.ptr(state), n, self.N, self.L, depth, HEURISTICS[heuristic], int(bool(pruned)),
+        v, a = out if out is not None else (self.xp.empty((n,), "f64"), self.xp.empty((n, 2), "i8"))
+        self._chk(self.lib.ewn_expectiminimax(self.xp.ptr(state), n, self.N, self.L, depth, HEURISTICS[heuristic],
+                                              int(bool(pruned)) | (2 if replay_path else 0),
                                               self.xp.ptr(v), self.xp.ptr(a), None, 0, self.xp.stream()), "ewn_expectiminimax")
         return v, a
 

@@ -199,11 +199,15 @@ EWN_API int ewn_numpy_draw(uint64_t *state, const uint32_t *raw, int32_t *cursor
 EWN_API int ewn_evaluate(const uint64_t *state, double *value, int64_t n, int board_size, int cube_layer, int heuristic, void *stream);
 
 /* classical_policies/minimax.py:19-93 ExpectiMinimaxAgent.predict on n roots (TOP_LEFT to move, die from the state).
- * pruned != 0 reproduces the reference's alpha/beta hand-through at chance nodes bit for bit; 0 = textbook.
+ * pruned bit 0 set reproduces the reference's alpha/beta hand-through at chance nodes bit for bit; clear = textbook.
+ * Depth 3 and 4 run in one kernel with the whole tree on chip (no workspace is touched); other depths store 2-byte / 8-byte node
+ * records in the workspace and replay minimax.py over them.
  * value: f64[n]; action: int8[n][2] (-1,-1 = None for a finished root).
  * workspace: device scratch of at least ewn_expectiminimax_workspace(n, depth) bytes, or NULL / 0 to let the library
  * use its own cached allocation (one per device: such calls must be ordered on one stream; pass a workspace to run several
  * searches concurrently). */
+/* `pruned` bit 1: run depth 3 / 4 on the record + replay kernels that serve depth >= 5 instead of the fused on-chip kernel (A/B) */
+#define EWN_EMM_REPLAY_PATH 2
 EWN_API size_t ewn_expectiminimax_workspace(int64_t n, int depth);
 EWN_API int ewn_expectiminimax(const uint64_t *state, int64_t n, int board_size, int cube_layer, int depth, int heuristic, int pruned,
                        double *value, int8_t *action, void *workspace, size_t workspace_bytes, void *stream);

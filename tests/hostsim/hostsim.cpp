@@ -164,8 +164,31 @@ template <class C, int M> void emm_replay_all(const uint64_t* state, const doubl
     }
 }
 
+// depth 3 / 4: the closed-form prefix rule (emm2_*), one worker per root; every second root looks its 'hybrid' values up in a table
+// built like the device's (k_emm_table), the others compute them in place -- both paths of emm_summary_value are exercised
+template <class C> int t_emm_fused(const uint64_t* state, int64_t n, const Geo& geo, int depth, int heuristic, int pruned, double* value, int8_t* action) {
+    std::vector<u32> inc(C::LUT);
+    for (int c = 0; c < C::LUT; c++) inc[c] = emm_inc_entry<C>(geo.N, c);
+    const int half = emm_tab_entries(geo.N), pad = emm_pad(geo.N);
+    std::vector<double> tv((size_t)(pad + half), 0.0), tq((size_t)(pad + half), 0.0);
+    const bool fold = !(depth & 1);
+    for (int i = 0; i < half; i++) { tv[pad + i] = emm_table_entry(geo.N, (fold ? half : 0) + i); tq[pad + i] = f64_div(tv[pad + i], 6.0); }
+    tv[pad - 1] = -10.0; tq[pad - 1] = f64_div(-10.0, 6.0);
+    for (int64_t r = 0; r < n; r++) {
+        Game<C> g; unpack(g, state, r); g.player = SIDE_TL;
+        const bool tab = (r & 1) && heuristic == H_HYBRID;
+        EmmTabs tb; tb.inc = inc.data(); tb.v = tab ? tv.data() + pad : nullptr; tb.q = tab ? tq.data() + pad : nullptr;
+        int la, di;
+        value[r] = emm2_root_serial<C>(g, geo, tb, depth, heuristic, pruned, la, di);
+        if (action) { action[2 * r] = (int8_t)la; action[2 * r + 1] = (int8_t)di; }
+    }
+    return EWN_OK;
+}
+
 template <class C> int t_emm(const uint64_t* state, int64_t n, const Geo& geo, int depth, int heuristic, int pruned, double* value, int8_t* action) {
     const int m = emm_levels(depth);
+    if (m == 2 && !(pruned & 2)) return t_emm_fused<C>(state, n, geo, depth, heuristic, pruned & 1, value, action);
+    pruned &= 1;
     const long slots = emm_level_size(m), per_root = emm_level_offset(m + 1);
     const int64_t chunk = 256;
     std::vector<double> vals((size_t)chunk * per_root);

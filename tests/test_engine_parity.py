@@ -124,6 +124,25 @@ def test_expectiminimax_golden_bits(backend, name):
         assert np.array_equal(to_np(a), want_a[:n]), key
 
 
+@pytest.mark.parametrize("N", [5, 7])
+def test_expectiminimax_fused_equals_replay_path(backend, N):
+    """Depth 3 / 4: the fused on-chip kernel (closed-form prefix rule, six lanes per root) against the record + replay kernels that
+    restate minimax.py:19-73 literally -- value bits and actions, every heuristic, pruned and unpruned, on positions from random play
+    (ragged root count so that partly filled warps and idle lane groups are exercised)."""
+    e = make_engine(backend, N, 3)
+    n = 333 if backend == "hostsim" else 20011
+    st = e.reset(n, seed=5)
+    for s in range(1, 7):
+        e.step(st, None, seed=5, step=s, agent_random=True, autoreset=(s % 3 != 0), want=())     # some roots are finished games
+    for depth in (3, 4):
+        for heuristic in ("hybrid", "min_dist", "two_min_dist", "attk"):
+            for pruned in (True, False):
+                v, a = e.expectiminimax(st, depth, heuristic, pruned=pruned)
+                rv, ra = e.expectiminimax(st, depth, heuristic, pruned=pruned, replay_path=True)
+                assert np.array_equal(bits(v), bits(rv)), (depth, heuristic, pruned)
+                assert np.array_equal(to_np(a), to_np(ra)), (depth, heuristic, pruned)
+
+
 def test_expectiminimax_vs_oracle_unpruned_and_deep(backend):
     """Oracle cross-check beyond the golden set: unpruned mode, depth 6, finished roots (action None)."""
     z = load("minimax_5x5.npz")
