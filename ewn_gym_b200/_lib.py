@@ -34,7 +34,7 @@ class StepArgs(C.Structure):
         ("inject_dice_opp", p_void), ("inject_opp_action", p_void), ("inject_dice_next", p_void),
         ("reward", C.c_double), ("illegal_move_reward", C.c_double),
         ("seed", u64), ("step", u64), ("env_id0", u64),
-        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("flags", i32), ("step_dev", p_void),
+        ("agent_random", i32), ("autoreset", i32), ("shaped", i32), ("flags", i32), ("step_dev", p_void), ("term_code", p_void),
     ]
 
 
@@ -54,6 +54,7 @@ PROTOTYPES = {
     "ewn_device_count": (C.c_int, []),
     "ewn_device_pci_bus_id": (C.c_int, [C.c_int, C.c_char_p, C.c_int]),
     "ewn_state_words": (C.c_int, [C.c_int]),
+    "ewn_state_words_cfg": (C.c_int, [C.c_int, C.c_int]),
     "ewn_launch_count": (i64, []),
     "ewn_reset": (C.c_int, [p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
     "ewn_reset_dice": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, p_void]),
@@ -77,6 +78,7 @@ PROTOTYPES = {
     "ewn_random_action": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void]),
     "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),
     "ewn_counter_add": (C.c_int, [p_void, u64, p_void]),
+    "ewn_step_dice": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void, p_void]),
     "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
     "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
     "ewn_expectiminimax": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void, p_void, C.c_size_t, p_void]),
@@ -88,13 +90,15 @@ PROTOTYPES = {
     "ewn_vec_destroy": (None, [p_void]),
     "ewn_vec_reset": (C.c_int, [p_void, p_void, p_void]),
     "ewn_vec_step": (C.c_int, [p_void] * 11),
+    "ewn_vec_step2": (C.c_int, [p_void] * 12),
+    "ewn_vec_set_seed": (C.c_int, [p_void, u64]),
     "ewn_host_alloc": (C.c_int, [C.POINTER(p_void), C.c_size_t]),
     "ewn_host_free": (C.c_int, [p_void]),
     "ewn_vec_state": (p_void, [p_void]),
     "ewn_vec_step_index": (u64, [p_void]),
 }
 # entry points a host simulator (tests/hostsim) does not provide
-_VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_host_alloc", "ewn_host_free",
+_VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_vec_step2", "ewn_vec_set_seed", "ewn_host_alloc", "ewn_host_free",
              "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id"}
 
 

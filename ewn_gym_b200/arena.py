@@ -135,11 +135,21 @@ def play_matches(engine: Engine, agent: BatchPolicy, opponent: BatchPolicy, n_ga
         done = done | won
         plies += 1
         e.set_dice(state, ops.dice(n, e.cube_num), None)                         # roll_dice for the next mover (:458, :483)
-        if plies % 4 == 0 and bool(done.all()):
+        if plies % 4 == 0 and bool(done.all()):                                  # the loop's one synchronisation point
+            _check_exchanges(agent, opponent)
             break
     w = ops.host(winner)
+    _check_exchanges(agent, opponent)
     return {"agent_wins": int((w == 1).sum()), "opponent_wins": int((w == 2).sum()), "unfinished": int((w == 0).sum()),
             "plies": plies, "winner": w, "n": n}
+
+
+def _check_exchanges(*policies):
+    """a peer-memory merge whose wait timed out leaves (-1, -1) actions and an error word behind: raise instead of playing on"""
+    for p in policies:
+        ex = getattr(p, "exchange", None)
+        if ex is not None:
+            ex.check()
 
 
 class NumpyRandom(BatchPolicy):

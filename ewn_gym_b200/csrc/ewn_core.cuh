@@ -259,6 +259,7 @@ template <class C> struct Game {
     int player;    // SIDE_TL / SIDE_BR: side to move
 };
 
+inline int codec_of(int N, int L) { return L > 3 ? 2 : (N <= 5 ? 0 : 1); }      // 0 = P5, 1 = P8, 2 = PG
 EWN_HD void unpack_regs(Game<P5>& g, u64 v, u64) {     // from words already in registers (prefetching kernels)
     u32 lo = (u32)v, hi = (u32)(v >> 32);
     g.tl = lo & P5::ALL; g.br = hi & P5::ALL;
@@ -266,6 +267,7 @@ EWN_HD void unpack_regs(Game<P5>& g, u64 v, u64) {     // from words already in 
     g.player = (int)(hi >> 31);
 }
 EWN_HD void unpack(Game<P5>& g, const u64* p, long i) { unpack_regs(g, p[i], 0); }
+EWN_HD void unpack(Game<P5>& g, const u64* p, long i, const Geo&) { unpack_regs(g, p[i], 0); }
 EWN_HD u64 pack_word(const Game<P5>& g) {
     u32 d = (u32)(g.dice - 1);
     u32 lo = g.tl | ((d & 3u) << 30);
@@ -273,6 +275,7 @@ EWN_HD u64 pack_word(const Game<P5>& g) {
     return (u64)lo | ((u64)hi << 32);
 }
 EWN_HD void pack(const Game<P5>& g, u64* p, long i) { p[i] = pack_word(g); }
+EWN_HD void pack(const Game<P5>& g, u64* p, long i, const Geo&) { p[i] = pack_word(g); }
 
 EWN_HD void unpack_words(Game<P8>& g, u64 w0, u64 w1) {
     g.tl = w0 & P8::ALL; g.br = w1 & P8::ALL;
@@ -301,8 +304,30 @@ EWN_HD void pack(const Game<P8>& g, u64* p, long i) {
 #endif
 }
 
+EWN_HD void unpack(Game<P8>& g, const u64* p, long i, const Geo&) { unpack(g, p, i); }
+EWN_HD void pack(const Game<P8>& g, u64* p, long i, const Geo&) { pack(g, p, i); }
+
+EWN_HD void unpack(Game<PG>& g, const u64* p, long i, const Geo& geo) {
+    const u64* q = p + i * geo.sw;
+    g.tl = PG::all(); g.br = PG::all();
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (j < geo.cw) { g.tl.w[j] = q[j]; g.br.w[j] = q[geo.cw + j]; }
+    const u64 meta = q[2 * geo.cw];
+    g.dice = (int)(meta & 0xFFull); g.player = (int)((meta >> 8) & 1ull);
+}
+EWN_HD void pack(const Game<PG>& g, u64* p, long i, const Geo& geo) {
+    u64* q = p + i * geo.sw;
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (j < geo.cw) { q[j] = g.tl.w[j]; q[geo.cw + j] = g.br.w[j]; }
+    q[2 * geo.cw] = (u64)(g.dice & 0xFF) | ((u64)(g.player & 1) << 8);
+}
+
 template <class C> EWN_HD void setup(Game<C>& g, const Geo& geo, int dice) {   // envs/ewn.py:94-107
-    g.tl = (typename C::W)geo.tl0; g.br = (typename C::W)geo.br0; g.dice = dice; g.player = SIDE_TL;
+    if constexpr (C::GENERIC) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) { g.tl.w[j] = geo.g_tl0[j]; g.br.w[j] = geo.g_br0[j]; }
+    } else { g.tl = (typename C::W)geo.tl0; g.br = (typename C::W)geo.br0; }
+    g.dice = dice; g.player = SIDE_TL;
 }
 
 inline bool use_p5(int N) { return N <= 5; }
@@ -322,6 +347,21 @@ inline Geo make_geo(int N, int L) {
             g.br_row |= 1u << cell(0, k);       // x == 0  : BR cannot go dir 1
         }
     }
+    if (codec_of(N, L) == 2) {
+        g.cw = (g.cube_num + 7) / 8; g.sw = 2 * g.cw + 1;
+        PG::W tl = PG::all(), br = PG::all();
+        int cnt = 0;
+        for (int i = 1; i <= L; i++)
+            for (int j = 0; j < i; j++) {
+                PG::set(tl, cnt, PG::cell(j, i - j - 1));
+                PG::set(br, cnt, PG::cell(N - 1 - j, N - i + j));
+                cnt++;
+            }
+        for (int j = 0; j < 4; j++) { g.g_tl0[j] = tl.w[j]; g.g_br0[j] = br.w[j]; }
+        g.tl0 = tl.w[0]; g.br0 = br.w[0];
+        return g;
+    }
+    g.cw = 0; g.sw = p5 ? 1 : 2;
     const int fb = p5 ? P5::FB : P8::FB;
     u64 tl = p5 ? (u64)P5::ALL : P8::ALL, br = tl;
     const u64 fm = p5 ? (u64)P5::FM : P8::FM;
@@ -353,22 +393,45 @@ template <class C> EWN_HD typename C::W capture(typename C::W w, typename C::W r
 }
 
 // envs/ewn.py:131-142 check_win on an arbitrary state
+// is one of the side's cubes standing on `cell`? / has the side no cube left?
+template <class C> EWN_HD bool any_at(const typename C::W& side, int cell) {
+    if constexpr (C::GENERIC) return C::any_at(side, cell);
+    else return match<C>(side, (typename C::W)cell * C::ONES) != 0;
+}
+template <class C> EWN_HD bool all_dead(const typename C::W& side) {
+    if constexpr (C::GENERIC) return C::all_dead(side);
+    else return side == C::ALL;
+}
 template <class C> EWN_HD bool full_win(const Game<C>& g, const Geo& geo) {
-    typedef typename C::W W;
-    W at_corner = match<C>(g.tl, (W)geo.corner * C::ONES);     // board[-1,-1] > 0
-    W at_origin = match<C>(g.br, (W)0);                         // board[0,0] < 0
-    return (at_corner | at_origin) != 0 || g.tl == C::ALL || g.br == C::ALL;
+    if constexpr (C::GENERIC) return any_at<C>(g.tl, geo.corner) || any_at<C>(g.br, 0) || all_dead<C>(g.tl) || all_dead<C>(g.br);
+    else {
+        typedef typename C::W W;
+        W at_corner = match<C>(g.tl, (W)geo.corner * C::ONES);     // board[-1,-1] > 0
+        W at_origin = match<C>(g.br, (W)0);                         // board[0,0] < 0
+        return (at_corner | at_origin) != 0 || g.tl == C::ALL || g.br == C::ALL;
+    }
 }
 // winner test used after a terminal state is known (mcts.py:39-41, minimax_ewn.py:42-47): did TOP_LEFT win?
 template <class C> EWN_HD bool tl_won(const Game<C>& g, const Geo& geo) {
-    typedef typename C::W W;
-    return match<C>(g.tl, (W)geo.corner * C::ONES) != 0 || g.br == C::ALL;
+    return any_at<C>(g.tl, geo.corner) || all_dead<C>(g.br);
 }
 
 // Shifts (bit offsets of the cube's field) of the cubes the side may move with the current die.
 // envs/ewn.py:144-176 find_near_cube, :202-215 find_cube_to_move.
 struct Movers { int d, hi, lo; };   // d >= 0: the dice cube itself is alive; else hi / lo = nearest larger / smaller (or -1)
-template <class C> EWN_HD Movers movers(typename C::W side, int dice) {      // branch-free: lanes of a warp do not diverge here
+template <class C> EWN_HD Movers movers(const typename C::W& side, int dice) {      // branch-free: lanes of a warp do not diverge here
+    if constexpr (C::GENERIC) {                           // one alive bit per cube; shifts are byte offsets (8 * cube index)
+        const u32 alive = C::alive(side);
+        const int k = dice - 1;
+        const bool has = (alive >> k) & 1u;
+        const u32 above = k >= 31 ? 0u : alive & (~0u << (k + 1));
+        const u32 below = alive & ((1u << k) - 1u);
+        Movers m;
+        m.d = has ? 8 * k : -1;
+        m.hi = (has || !above) ? -1 : 8 * ctz_nz(above);
+        m.lo = (has || !below) ? -1 : 8 * msb_nz(below);
+        return m;
+    } else {
     typedef typename C::W W;
     W alive = C::dead(side) ^ C::ONES;
     int sh = C::FB * (dice - 1);
@@ -380,6 +443,7 @@ template <class C> EWN_HD Movers movers(typename C::W side, int dice) {      // 
     m.hi = has ? -1 : ctz_nz(above);
     m.lo = has ? -1 : msb_nz(below);
     return m;
+    }
 }
 // envs/ewn.py:178-215: the flag is only consulted when the dice cube is gone, and falls back to the other side
 EWN_HD int cube_to_move(const Movers& m, bool larger) {
@@ -388,14 +452,17 @@ EWN_HD int cube_to_move(const Movers& m, bool larger) {
     return m.lo >= 0 ? m.lo : m.hi;
 }
 
-template <class C> EWN_HD int cell_at(typename C::W side, int sh) { return (int)((side >> sh) & C::FM); }
+template <class C> EWN_HD int cell_at(const typename C::W& side, int sh) {
+    if constexpr (C::GENERIC) return C::get(side, (sh >> 3) & 31);
+    else return (int)((side >> sh) & C::FM);
+}
 
 // Ordered legal list of envs/ewn.py:338-375 as two 3-bit direction sets: `first` is listed before `second`.
 //   dice cube alive : first = dirs(dice cube) with flag 0, second = empty
 //   otherwise       : first = dirs(larger neighbour) with flag 1, second = dirs(smaller neighbour) with flag 0
 struct Legal { int first, second, first_flag, sh_first, sh_second; };
 template <class C, int BR, class G> EWN_HD Legal legal(const Game<C>& g, const G& geo, const Movers& m) {
-    typename C::W side = BR ? g.br : g.tl;
+    const typename C::W& side = BR ? g.br : g.tl;
     Legal l;
     const bool has = m.d >= 0;
     l.first_flag = has ? 0 : 1;
@@ -425,6 +492,16 @@ EWN_HD void legal_pick(const Legal& l, int idx, int& larger, int& dir, int& sh) 
 // envs/ewn.py:217-263 execute_move for a move already known to stay on the board. Returns the target cell.
 // dir 3 is the reference's "no branch matches" case (:229-247): (x, y) stays put, the cube is lifted and put back.
 template <class C, int BR> EWN_HD int apply_move(Game<C>& g, int sh, int dir) {
+    if constexpr (C::GENERIC) {
+        const int k = (sh >> 3) & 31;
+        const int c = C::get(BR ? g.br : g.tl, k);
+        int delta = (dir != 1) + C::S * (dir != 0);        // envs/ewn.py:301-319 update_position
+        delta = dir > 2 ? 0 : delta;
+        const int t = BR ? c - delta : c + delta;
+        C::capture(g.tl, t); C::capture(g.br, t);          // :254-258 (the mover itself too when dir 3 keeps it in place ...)
+        if (BR) C::set(g.br, k, t); else C::set(g.tl, k, t);   // ... and is put back here, :259-261
+        return t;
+    } else {
     typedef typename C::W W;
     W own = BR ? g.br : g.tl;
     int c = (int)((own >> sh) & C::FM);
@@ -437,10 +514,11 @@ template <class C, int BR> EWN_HD int apply_move(Game<C>& g, int sh, int dir) {
     if (BR) g.br = (g.br & ~(C::FM << sh)) | ((W)t << sh);
     else    g.tl = (g.tl & ~(C::FM << sh)) | ((W)t << sh);
     return t;
+    }
 }
 // check_win right after `BR ? BOTTOM_RIGHT : TOP_LEFT` moved to cell t from a non-terminal position
 template <class C, int BR> EWN_HD bool win_after(const Game<C>& g, const Geo& geo, int t) {
-    return BR ? (t == 0 || g.tl == C::ALL) : (t == geo.corner || g.br == C::ALL);
+    return BR ? (t == 0 || all_dead<C>(g.tl)) : (t == geo.corner || all_dead<C>(g.br));
 }
 
 // One ply with an externally chosen action (find_cube_to_move + execute_move, envs/ewn.py:439-442).
@@ -449,7 +527,7 @@ template <class C, int BR> EWN_HD bool win_after(const Game<C>& g, const Geo& ge
 // put back where it stood -- a VALID no-op move (the action space never produces it; parity keeps it).  It is folded
 // into the data path as pseudo-direction 3 (always "on the board", displacement 0) so that the ply stays branch-free.
 template <class C, int BR, class G> EWN_HD bool ply_action(Game<C>& g, const G& geo, int larger, int dir, int& t_out, int& sh_out) {
-    typename C::W side = BR ? g.br : g.tl;
+    const typename C::W side = BR ? g.br : g.tl;
     Movers m = movers<C>(side, g.dice);
     int sh = cube_to_move(m, larger == 1);
     sh_out = sh;
@@ -462,16 +540,25 @@ template <class C, int BR, class G> EWN_HD bool ply_action(Game<C>& g, const G& 
 
 // The board as the other side sees it: np.rot90(-board, 2) (envs/ewn.py:289-296 opponent_action).  Cube k of one side at
 // (x, y) becomes cube k of the other side at (N-1-x, N-1-y); the die is kept, the side to move is mirrored.
-template <class C> EWN_HD typename C::W flip_side(typename C::W side, const Geo& geo) {
+template <class C> EWN_HD typename C::W flip_side(const typename C::W& side, const Geo& geo) {
     typedef typename C::W W;
+    if constexpr (C::GENERIC) {
+        W out = C::all();
+        for (int k = 0; k < geo.cube_num; k++) {
+            const int c = C::get(side, k);
+            if (c != (int)C::FM) C::set(out, k, geo.corner - c);
+        }
+        return out;
+    } else {
     W out = 0;
 #pragma unroll
     for (int k = 0; k < 6; k++) {
         int c = (int)((side >> (C::FB * k)) & C::FM);
-        int f = c == (int)C::FM ? (int)C::FM : geo.corner - c;      // both codecs: cell(N-1-x, N-1-y) = corner - cell(x, y)
+        int f = c == (int)C::FM ? (int)C::FM : geo.corner - c;      // every codec: cell(N-1-x, N-1-y) = corner - cell(x, y)
         out |= (W)f << (C::FB * k);
     }
     return out;
+    }
 }
 template <class C> EWN_HD void flip_game(Game<C>& g, const Geo& geo) {
     typename C::W tl = flip_side<C>(g.br, geo), br = flip_side<C>(g.tl, geo);
@@ -482,11 +569,11 @@ template <class C> EWN_HD void flip_game(Game<C>& g, const Geo& geo) {
 // leaf evaluation, envs/minimax_ewn.py:29-213 (agent is always TOP_LEFT: minimax_ewn.py:17-19)
 // ------------------------------------------------------------------------------------------------
 struct SideStats { int cnt, best, second; };   // best/second = two largest values of min(x,y) over alive cubes (-1 if none)
-template <class C> EWN_HD SideStats side_stats(typename C::W side) {
+template <class C> EWN_HD SideStats side_stats(const typename C::W& side) {
     SideStats s; s.cnt = 0; s.best = -1; s.second = -1;
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
-        int c = (int)((side >> (C::FB * k)) & C::FM);
+    for (int k = 0; k < C::MAXC; k++) {
+        int c = C::get(side, k);
         if (c != (int)C::FM) {
             int x = C::x_of(c), y = C::y_of(c);
             int mn = x < y ? x : y;
@@ -497,15 +584,16 @@ template <class C> EWN_HD SideStats side_stats(typename C::W side) {
     }
     return s;
 }
-EWN_HD double inv_count(int c) {   // 1.0 / c, correctly rounded (compile-time IEEE division)
+EWN_HD double inv_count(int c) {   // 1.0 / c, correctly rounded (compile-time IEEE division up to six cubes, f64_div above)
     switch (c) {
         case 1: return 1.0; case 2: return 1.0 / 2.0; case 3: return 1.0 / 3.0;
-        case 4: return 1.0 / 4.0; case 5: return 1.0 / 5.0; default: return 1.0 / 6.0;
+        case 4: return 1.0 / 4.0; case 5: return 1.0 / 5.0; case 6: case 0: return 1.0 / 6.0;
+        default: return f64_div(1.0, (double)c);
     }
 }
 template <class C> EWN_HD double evaluate(const Game<C>& g, const Geo& geo, int heuristic) {
     if (tl_won<C>(g, geo)) return 10.0;                                   // minimax_ewn.py:42-44
-    if (match<C>(g.br, (typename C::W)0) != 0 || g.tl == C::ALL) return -10.0;   // :45-47
+    if (any_at<C>(g.br, 0) || all_dead<C>(g.tl)) return -10.0;            // :45-47
     SideStats p = side_stats<C>(g.tl), n = side_stats<C>(g.br);
     // Both colours measure max(N-1-x, N-1-y), the distance to the BOTTOM-RIGHT corner (minimax_ewn.py:67-76),
     // so N - min_dist = 1 + max over cubes of min(x, y).

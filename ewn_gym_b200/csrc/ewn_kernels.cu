@@ -45,7 +45,8 @@ inline int cuda_fail(cudaError_t e, const char* what) {
         if (e__ != cudaSuccess) return cuda_fail(e__, name); \
     } while (0)
 
-inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L <= 3 && L < N - 1; }
+// envs/ewn.py:47: any cube_layer < board_size - 1 (up to 28 cubes per side on 9x9)
+inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L < N - 1; }
 inline unsigned blocks_for(int64_t n) { return (unsigned)((n + TPB - 1) / TPB); }
 
 // ------------------------------------------------------------------------------------------------
@@ -71,11 +72,13 @@ template <class C, int NT> __device__ __forceinline__ void stage_rows(const Game
     __syncwarp();
     if (mine) {
         int16_t* row = sm + lane * NN;
+        const int nc = C::ncubes(geo);
 #pragma unroll
-        for (int k = 0; k < 6; k++) {
-            int c = (int)((g.tl >> (C::FB * k)) & C::FM);
+        for (int k = 0; k < C::MAXC; k++) {
+            if (k >= nc) break;
+            int c = C::get(g.tl, k);
             if (c != (int)C::FM) row[lin_cell<C, NT>(geo, c)] = (int16_t)(k + 1);
-            int d = (int)((g.br >> (C::FB * k)) & C::FM);
+            int d = C::get(g.br, k);
             if (d != (int)C::FM) row[lin_cell<C, NT>(geo, d)] = (int16_t)(-(k + 1));
         }
     }
@@ -124,30 +127,29 @@ template <class C> __global__ void __launch_bounds__(TPB) k_reset(u64* state, co
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
     int dice;
-    if (dice_in) dice = dice_in[i];
+    if (dice_in) { dice = dice_in[i]; dice = dice < 1 ? 1 : (dice > geo.cube_num ? geo.cube_num : dice); }   // a die outside 1..cube_num would spill into the flag bits
     else { u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_RESET, blk); dice = 1 + (int)bounded(blk[0], (u32)geo.cube_num); }
     Game<C> g; setup<C>(g, geo, dice);
-    pack(g, state, i);
+    pack(g, state, i, geo);
 }
 
 template <class C> __global__ void __launch_bounds__(TPB) k_encode(const int16_t* board, const int32_t* dice, const int32_t* player,
                                                                    u64* state, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    typedef typename C::W W;
-    const int N = geo.N, NN = N * N;
-    Game<C> g; g.tl = C::ALL; g.br = C::ALL;
+    const int N = geo.N, NN = N * N, nc = geo.cube_num;
+    Game<C> g; g.tl = C::all(); g.br = C::all();
     const int16_t* b = board + i * NN;
     for (int x = 0; x < N; x++)
         for (int y = 0; y < N; y++) {
             int v = b[x * N + y];
-            if (v > 0 && v <= 6) { int sh = C::FB * (v - 1); g.tl = (g.tl & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
-            else if (v < 0 && v >= -6) { int sh = C::FB * (-v - 1); g.br = (g.br & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+            if (v > 0 && v <= nc) C::set(g.tl, v - 1, C::cell(x, y));
+            else if (v < 0 && v >= -nc) C::set(g.br, -v - 1, C::cell(x, y));
         }
     int d = dice ? dice[i] : 1;
-    g.dice = d < 1 ? 1 : (d > 6 ? 6 : d);
+    g.dice = d < 1 ? 1 : (d > nc ? nc : d);
     g.player = (player && player[i] == EWN_BOTTOM_RIGHT) ? SIDE_BR : SIDE_TL;
-    pack(g, state, i);
+    pack(g, state, i, geo);
 }
 
 template <class C> __global__ void __launch_bounds__(TPB) k_decode(const u64* state, int16_t* board, int64_t* dice, int32_t* player,
@@ -156,9 +158,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_decode(const u64* st
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool mine = i < n;
-    Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0;
+    Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
     if (mine) {
-        unpack(g, state, i);
+        unpack(g, state, i, geo);
         if (dice) dice[i] = g.dice;
         if (player) player[i] = g.player == SIDE_BR ? EWN_BOTTOM_RIGHT : EWN_TOP_LEFT;
     }
@@ -180,7 +182,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_legal(const u64* sta
                                                                   int32_t* count, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
     Legal l;
     if (side == SIDE_BR) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
@@ -201,7 +203,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_legal(const u64* sta
 template <class C> __global__ void __launch_bounds__(TPB) k_check_win(const u64* state, uint8_t* win, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     win[i] = full_win<C>(g, geo) ? 1 : 0;
 }
 
@@ -209,26 +211,26 @@ template <class C> __global__ void __launch_bounds__(TPB) k_ply(u64* state, int 
                                                                 uint8_t* win, int32_t* moved, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
     int t = 0, sh = -1;
     bool ok;
     if (side == SIDE_BR) ok = ply_action<C, SIDE_BR>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
     else                 ok = ply_action<C, SIDE_TL>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
     if (ok) g.player = side ^ 1;
-    pack(g, state, i);
+    pack(g, state, i, geo);
     if (valid) valid[i] = ok ? 1 : 0;
     if (win) win[i] = full_win<C>(g, geo) ? 1 : 0;
     if (moved) moved[i] = sh < 0 ? 0 : sh / C::FB + 1;
 }
 
-template <class C> __global__ void __launch_bounds__(TPB) k_set_dice(u64* state, const int32_t* dice, const int32_t* player, int64_t n) {
+template <class C> __global__ void __launch_bounds__(TPB) k_set_dice(u64* state, const int32_t* dice, const int32_t* player, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
-    if (dice) { int d = dice[i]; g.dice = d < 1 ? 1 : (d > 6 ? 6 : d); }
+    Game<C> g; unpack(g, state, i, geo);
+    if (dice) { int d = dice[i]; g.dice = d < 1 ? 1 : (d > geo.cube_num ? geo.cube_num : d); }
     if (player) g.player = player[i] == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL;
-    pack(g, state, i);
+    pack(g, state, i, geo);
 }
 
 // NN-facing observation (classical_policies/alpha_zero/alpha_zero.py:39-58 ewn_obs_one_hot): board[x][y][k] = +1 where TOP_LEFT's
@@ -254,12 +256,12 @@ template <class C> __global__ void __launch_bounds__(TPB) k_decode_onehot(const 
     }
     __syncthreads();
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     float* b = board + i * row;
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
+    for (int k = 0; k < C::MAXC; k++) {
         if (k >= cn) break;
-        const int c = (int)((g.tl >> (C::FB * k)) & C::FM), d = (int)((g.br >> (C::FB * k)) & C::FM);
+        const int c = C::get(g.tl, k), d = C::get(g.br, k);
         if (c != (int)C::FM) b[(C::x_of(c) * geo.N + C::y_of(c)) * cn + k] = 1.f;
         if (d != (int)C::FM) b[(C::x_of(d) * geo.N + C::y_of(d)) * cn + k] = -1.f;
     }
@@ -277,7 +279,7 @@ template <class C> __global__ void __launch_bounds__(128) k_numpy_random_games(c
     const int r = numpy_random_game<C>(g, geo, seeds[i], rng, steps, h);
     if (result) result[i] = (int8_t)r;
     if (agent_steps) agent_steps[i] = steps;
-    if (final_state) pack(g, final_state, i);
+    if (final_state) pack(g, final_state, i, geo);
     if (trace) trace[i] = h;
 }
 
@@ -292,9 +294,9 @@ template <class C> __global__ void __launch_bounds__(TPB) k_numpy_draw(u64* stat
                                                                        int roll, int pick_player, int32_t* action) {
     const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     RawStream rs; rs.raw = raw + i * K; rs.K = K; rs.cur = cursor[i];
-    if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
+    if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i, geo); }
     if (pick_player) {
         Legal l;
         if (pick_player == EWN_BOTTOM_RIGHT) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
@@ -310,16 +312,16 @@ template <class C> __global__ void __launch_bounds__(TPB) k_numpy_draw(u64* stat
 template <class C> __global__ void __launch_bounds__(TPB) k_flip(const u64* in, u64* out, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, in, i);
+    Game<C> g; unpack(g, in, i, geo);
     flip_game<C>(g, geo);
-    pack(g, out, i);
+    pack(g, out, i, geo);
 }
 
 template <class C> __global__ void __launch_bounds__(TPB) k_random_action(const u64* state, int64_t* action, int64_t n, Geo geo,
                                                                           u64 seed, u64 step, u64 env_id0) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_STEP, blk);
     Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
     int c = legal_count(l);
@@ -350,8 +352,9 @@ template <class C, int NT, bool REPLAY, bool SHAPED, bool VEC> __global__ void _
 k_step(const __grid_constant__ StepKArgs ka) {
     extern __shared__ uint4 smem_raw[];
     __shared__ unsigned s_tot, s_row0;                          // s_tot = finished | won << 10 | lost << 20 of this block
-    __shared__ __align__(16) u64 s_term[STPB * C::WORDS];       // packed terminal states of the finished games
+    __shared__ __align__(16) u64 s_term[STPB * C::WORDS];       // packed terminal states of the finished games (PG: geo.sw <= 9 words each)
     __shared__ unsigned char s_who[STPB];                       // ... and the thread that owns each of them
+    __shared__ unsigned char s_code[STPB];                      // ... and how each of them ended (EWN_CODE_*)
     const ewn_step_args& a = ka.a;
     const int64_t n = a.n;
     const unsigned tid = threadIdx.x;
@@ -365,14 +368,14 @@ k_step(const __grid_constant__ StepKArgs ka) {
     }
 
     Game<C> g, term;
-    g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
+    g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0; term = g;
     StepOut out; out.term = 0; out.code = CODE_ONGOING;
     if (mine) {
         StepParams p = ka.p;
         p.replay = REPLAY; p.shaped = SHAPED;
         if (NT) { p.geo.N = NT; p.geo.corner = C::cell(NT - 1, NT - 1); }
         if (VEC) p.agent_random = 0;
-        unpack(g, a.state, i);
+        unpack(g, a.state, i, ka.p.geo);
         int al = 0, ad = 0;
         if (!p.agent_random) {
             if (VEC || a.action_i64) { longlong2 v = __ldcs(reinterpret_cast<const longlong2*>(a.action_i64) + i); al = (int)v.x; ad = (v.y < 0 || v.y > 2) ? 3 : (int)v.y; }
@@ -389,7 +392,7 @@ k_step(const __grid_constant__ StepKArgs ka) {
         if (a.step_dev) p.step += __ldg(a.step_dev);
         step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
         if (SHAPED) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
-        pack(g, a.state, i);
+        pack(g, a.state, i, ka.p.geo);
         if (VEC) {
             __stcs(a.reward_f32 + i, (float)out.reward);
             __stcs(a.terminated + i, (uint8_t)out.term);
@@ -416,10 +419,11 @@ k_step(const __grid_constant__ StepKArgs ka) {
         stage_rows<C, NT>(g, mine, geo, sm, lane);
         write_rows_dense<C, NT>(a.obs_board, warp_env0, n, geo, sm, lane);
     }
-    if (!compact && (a.term_board || a.term_dice)) {             // dense terminal rows (row = env index), warp-level
+    if (!compact && (a.term_board || a.term_dice || a.term_code)) {   // dense terminal rows (row = env index), warp-level
         const unsigned done = __ballot_sync(0xffffffffu, fin);
         if (done) {
             if (fin && a.term_dice) a.term_dice[i] = term.dice;
+            if (fin && a.term_code) a.term_code[i] = (uint8_t)out.code;
             if (a.term_board) {
                 int16_t* sm = smb + warp * 32 * NN;
                 stage_rows<C, NT>(term, fin, geo, sm, lane);
@@ -441,8 +445,9 @@ k_step(const __grid_constant__ StepKArgs ka) {
                 base = __shfl_sync(0xffffffffu, base, 0) & 1023u;
                 if (fin) {
                     const unsigned k = base + (unsigned)__popc(done & ((1u << lane) - 1u));
-                    pack(term, s_term, (long)k);
+                    pack(term, s_term, (long)k, geo);
                     s_who[k] = (unsigned char)tid;
+                    s_code[k] = (unsigned char)out.code;
                 }
             }
         }
@@ -466,20 +471,31 @@ k_step(const __grid_constant__ StepKArgs ka) {
     }
     __syncthreads();
     const int64_t row0 = (int64_t)s_row0;
+    const int head = (int)(((unsigned)row0 * (unsigned)NN) & 7u);
     if ((int)tid < F) {
-        Game<C> t; unpack(t, s_term, (long)tid);
+        Game<C> t; unpack(t, s_term, (long)tid, geo);
         if (a.term_dice) __stcs(reinterpret_cast<long long*>(a.term_dice) + row0 + tid, (long long)t.dice);
         __stcs(a.term_index + row0 + tid, (int32_t)(a.term_index_base + (int64_t)blockIdx.x * STPB + s_who[tid]));
+        if (a.term_code) a.term_code[row0 + tid] = s_code[tid];
+        if constexpr (C::GENERIC) {                               // generic codec: one finished game per thread, all its cubes
+            if (boards)
+                for (int k = 0; k < geo.cube_num; k++) {
+                    const int c = C::get(t.tl, k), d = C::get(t.br, k);
+                    if (c != (int)C::FM) smb[head + tid * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(k + 1);
+                    if (d != (int)C::FM) smb[head + tid * NN + lin_cell<C, NT>(geo, d)] = (int16_t)(-(k + 1));
+                }
+        }
     }
     if (!boards) return;
-    const int head = (int)(((unsigned)row0 * (unsigned)NN) & 7u);
-    for (int p = tid; p < F * 12; p += STPB) {                    // one (finished game, cube) pair per thread
-        const int r = (int)__umulhi((unsigned)p, 0x15555556u);    // p / 12
-        const int k = p - 12 * r;
-        const int br = k >= 6, kk = br ? k - 6 : k;
-        const typename C::W side = (typename C::W)(C::WORDS == 1 ? (br ? s_term[r] >> 32 : s_term[r]) : s_term[2 * r + br]);
-        const int c = (int)((side >> (C::FB * kk)) & C::FM);
-        if (c != (int)C::FM) smb[head + r * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(br ? -(kk + 1) : kk + 1);
+    if constexpr (!C::GENERIC) {
+        for (int p = tid; p < F * 12; p += STPB) {                // one (finished game, cube) pair per thread
+            const int r = (int)__umulhi((unsigned)p, 0x15555556u);    // p / 12
+            const int k = p - 12 * r;
+            const int br = k >= 6, kk = br ? k - 6 : k;
+            const typename C::W side = (typename C::W)(C::WORDS == 1 ? (br ? s_term[r] >> 32 : s_term[r]) : s_term[2 * r + br]);
+            const int c = (int)((side >> (C::FB * kk)) & C::FM);
+            if (c != (int)C::FM) smb[head + r * NN + lin_cell<C, NT>(geo, c)] = (int16_t)(br ? -(kk + 1) : kk + 1);
+        }
     }
     __syncthreads();
     int16_t* const dst = a.term_board + row0 * NN - head;         // element `e` of the staging area goes to dst[e]
@@ -561,7 +577,7 @@ template <class C, int NT> __device__ __forceinline__ void scatter_row(const Gam
 // Terminal rows of one block, after its loop: thread r owns finished game r of the pass (its dice, its env index and the
 // scatter of its twelve cubes into the staging tile), then the tile leaves as 16-byte vectors.  Kept out of line so that its
 // registers and schedule do not disturb the step loop.
-template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* term_board, int64_t* term_dice, int32_t* term_index, int64_t index_base,
+template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* term_board, int64_t* term_dice, int32_t* term_index, uint8_t* term_code, int64_t index_base,
                                                                     Geo geo, int16_t* smb, const u64* s_term, const u32* s_who,
                                                                     const unsigned* s_wcnt, unsigned seg, int F, int64_t row0) {
     const int tid = (int)threadIdx.x;
@@ -591,7 +607,8 @@ template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* ter
             const int e = src(r0 + tid);
             Game<C> t; unpack(t, s_term, (long)e);
             if (term_dice) __stcs(reinterpret_cast<long long*>(term_dice) + rowc + tid, (long long)t.dice);
-            __stcs(term_index + rowc + tid, (int32_t)(index_base + (int64_t)s_who[e]));
+            __stcs(term_index + rowc + tid, (int32_t)(index_base + (int64_t)(s_who[e] & 0x3FFFFFFFu)));
+            if (term_code) term_code[rowc + tid] = (uint8_t)(1u + (s_who[e] >> 30));        // EWN_CODE_* 1..4
             if (term_board) scatter_row<C, NT>(t, geo, smb + head, tid);
         }
         if (!term_board) continue;
@@ -709,7 +726,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
                 if (compact && fin) {
                     const unsigned k = (unsigned)warp * seg + wcnt + (unsigned)__popc(done & ((1u << lane) - 1u));
                     pack(term, s_term, (long)k);
-                    s_who[k] = (u32)i;
+                    s_who[k] = (u32)i | ((u32)(out.code - 1) << 30);        // i < 2^30; the result code (1..4) rides in the top bits
                 }
                 wcnt += (unsigned)__popc(done);
                 if (fin) tally_c += (out.code == CODE_AGENT_WON ? 1u : 0u) + (out.code == CODE_AGENT_LOST ? 0x10000u : 0u);
@@ -764,7 +781,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
 #if EWN_VFLUSH
     __syncthreads();
-    vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, F, (int64_t)s_row0);
+    vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_code, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, F, (int64_t)s_row0);
 }
 #else
     // row r of this block's output <-> entry src(r) of the segmented list
@@ -783,7 +800,8 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
         const int e = src(r);
         Game<C> t; unpack(t, s_term, (long)e);
         if (a.term_dice) __stcs(reinterpret_cast<long long*>(a.term_dice) + row0 + r, (long long)t.dice);
-        __stcs(a.term_index + row0 + r, (int32_t)(a.term_index_base + (int64_t)s_who[e]));
+        __stcs(a.term_index + row0 + r, (int32_t)(a.term_index_base + (int64_t)(s_who[e] & 0x3FFFFFFFu)));
+        if (a.term_code) a.term_code[row0 + r] = (uint8_t)(1u + (s_who[e] >> 30));
     }
     if (!a.term_board) return;
     for (int r0 = 0; r0 < F; r0 += VTPB) {                         // VTPB rows per pass through the staging tile
@@ -828,7 +846,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
 template <class C> __global__ void __launch_bounds__(TPB) k_evaluate(const u64* state, double* value, int64_t n, Geo geo, int heuristic) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     value[i] = evaluate<C>(g, geo, heuristic);
 }
 
@@ -998,7 +1016,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64*
                                                                       PairBuf pb, int32_t* n_children, u32 count, u32* wins) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     g.player = SIDE_TL;
     int cnt = 0;
     if (!full_win<C>(g, geo)) {
@@ -1120,7 +1138,7 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_best(const u64* state, const u32* wins, int8_t* action, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     int la = -1, di = -1;
     if (!full_win<C>(g, geo)) {
         Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
@@ -1150,17 +1168,22 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
     // publish: the playout kernel that filled my counters precedes this kernel on the stream, so they are complete
     if (blockIdx.x == 0 && threadIdx.x < world) { __threadfence_system(); st_release_sys(theirs + rank, epoch); }
     // wait for the same epoch of every rank; the flag words live in MY memory, the spin never crosses NVLink
+    int timed_out = 0;
     if (threadIdx.x < world) {
         const u32* f = mine + threadIdx.x;
         unsigned long long t0 = global_ns();
         while ((int)(ld_acquire_sys(f) - epoch) < 0) {
-            if (global_ns() - t0 > timeout_ns) { atomicExch(mine + EWN_PEER_ERR_WORD, epoch); break; }
+            if (global_ns() - t0 > timeout_ns) { atomicExch(mine + EWN_PEER_ERR_WORD, epoch); timed_out = 1; break; }
             __nanosleep(64);
         }
     }
-    __syncthreads();
+    const int dead = __syncthreads_or(timed_out);
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
+    if (dead) {                                                  // a peer never published this epoch: no move, and the caller can see it
+        action[2 * i] = (int8_t)-1; action[2 * i + 1] = (int8_t)-1;
+        return;
+    }
     uint2 w[EWN_MAX_PEERS][3];                                   // 24-byte rows: three 8-byte peer loads per rank, all in flight together
 #pragma unroll
     for (int r = 0; r < EWN_MAX_PEERS; r++)
@@ -1181,7 +1204,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 #pragma unroll
         for (int k = 0; k < 3; k++) dst[k] = make_uint2(sum[2 * k], sum[2 * k + 1]);
     }
-    Game<C> g; unpack(g, state, i);
+    Game<C> g; unpack(g, state, i, geo);
     int la = -1, di = -1;
     if (!full_win<C>(g, geo)) {
         Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
@@ -1197,20 +1220,31 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 // ------------------------------------------------------------------------------------------------
 // library-owned scratch (one per device), grown on demand; used when the caller passes no workspace
 // ------------------------------------------------------------------------------------------------
-struct Scratch { void* p = nullptr; size_t bytes = 0; };
-Scratch g_scratch[64];
+// One allocation per (device, stream): calls on different streams never share scratch, so ewn_expectiminimax / ewn_mc_root_wins
+// without a caller workspace are safe from several host threads as long as each thread uses its own stream (calls on ONE stream
+// are ordered by the stream).  The table itself is guarded by a mutex; growing an entry waits for that stream only.
+struct Scratch { int dev = -1; cudaStream_t st = nullptr; void* p = nullptr; size_t bytes = 0; };
+constexpr int MAX_SCRATCH = 256;
+Scratch g_scratch[MAX_SCRATCH];
+int g_scratch_n = 0;
+std::mutex g_scratch_mutex;
 
-int scratch_get(size_t bytes, void** out) {
+int scratch_get(size_t bytes, void** out, cudaStream_t st) {
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64) return EWN_EARG;
-    Scratch& s = g_scratch[dev];
-    if (s.bytes < bytes) {
-        if (s.p) { CU(cudaDeviceSynchronize()); CU(cudaFree(s.p)); s.p = nullptr; s.bytes = 0; }
-        CU(cudaMalloc(&s.p, bytes));
-        s.bytes = bytes;
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    Scratch* s = nullptr;
+    for (int i = 0; i < g_scratch_n; i++) if (g_scratch[i].dev == dev && g_scratch[i].st == st) { s = &g_scratch[i]; break; }
+    if (!s) {
+        if (g_scratch_n == MAX_SCRATCH) return EWN_ESPACE;            // pass a workspace instead
+        s = &g_scratch[g_scratch_n++]; s->dev = dev; s->st = st;
     }
-    *out = s.p;
+    if (s->bytes < bytes) {
+        if (s->p) { CU(cudaStreamSynchronize(st)); CU(cudaFree(s->p)); s->p = nullptr; s->bytes = 0; }
+        CU(cudaMalloc(&s->p, bytes));
+        s->bytes = bytes;
+    }
+    *out = s->p;
     return EWN_OK;
 }
 
@@ -1261,8 +1295,15 @@ static int launch_playouts(const void* pairs, const uint32_t* root_ids, const in
     return EWN_OK;
 }
 
-#define DISPATCH(N, expr_p5, expr_p8) \
-    do { if (use_p5(N)) { typedef P5 C; expr_p5; } else { typedef P8 C; expr_p8; } } while (0)
+// run `...` with C = the codec of (N, L): P5 / P8 for the six-cube configurations, PG for cube_layer >= 4
+#define FOR_CODEC(N, L, ...)                                             \
+    do {                                                                 \
+        switch (codec_of(N, L)) {                                        \
+            case 0: { typedef P5 C; __VA_ARGS__; } break;                \
+            case 1: { typedef P8 C; __VA_ARGS__; } break;                \
+            default: { typedef PG C; __VA_ARGS__; } break;               \
+        }                                                                \
+    } while (0)
 
 }  // namespace
 
@@ -1297,6 +1338,7 @@ int ewn_device_pci_bus_id(int device, char* out, int len) {
     return EWN_OK;
 }
 int ewn_state_words(int N) { return (N >= 3 && N <= EWN_MAX_BOARD) ? (use_p5(N) ? 1 : 2) : EWN_EARG; }
+int ewn_state_words_cfg(int N, int L) { return config_ok(N, L) ? make_geo(N, L).sw : EWN_EARG; }
 int64_t ewn_launch_count(void) { return g_launches.load(); }
 
 int ewn_reset(uint64_t* state, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void* stream) {
@@ -1304,8 +1346,7 @@ int ewn_reset(uint64_t* state, int64_t n, int N, int L, uint64_t seed, uint64_t 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_reset<P5><<<blocks_for(n), TPB, 0, st>>>(state, nullptr, n, geo, seed, step, env_id0);
-    else           k_reset<P8><<<blocks_for(n), TPB, 0, st>>>(state, nullptr, n, geo, seed, step, env_id0);
+    FOR_CODEC(N, L, k_reset<C><<<blocks_for(n), TPB, 0, st>>>(state, nullptr, n, geo, seed, step, env_id0));
     LAUNCHED("k_reset");
     return EWN_OK;
 }
@@ -1315,8 +1356,7 @@ int ewn_reset_dice(uint64_t* state, const int32_t* dice, int64_t n, int N, int L
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_reset<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, n, geo, 0, 0, 0);
-    else           k_reset<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, n, geo, 0, 0, 0);
+    FOR_CODEC(N, L, k_reset<C><<<blocks_for(n), TPB, 0, st>>>(state, dice, n, geo, 0, 0, 0));
     LAUNCHED("k_reset");
     return EWN_OK;
 }
@@ -1326,8 +1366,7 @@ int ewn_encode(const int16_t* board, const int32_t* dice, const int32_t* player,
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_encode<P5><<<blocks_for(n), TPB, 0, st>>>(board, dice, player, state, n, geo);
-    else           k_encode<P8><<<blocks_for(n), TPB, 0, st>>>(board, dice, player, state, n, geo);
+    FOR_CODEC(N, L, k_encode<C><<<blocks_for(n), TPB, 0, st>>>(board, dice, player, state, n, geo));
     LAUNCHED("k_encode");
     return EWN_OK;
 }
@@ -1337,8 +1376,7 @@ int ewn_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* pl
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_decode<P5><<<blocks_for(n), TPB, obs_smem<P5>(geo), st>>>(state, board, dice, player, n, geo);
-    else           k_decode<P8><<<blocks_for(n), TPB, obs_smem<P8>(geo), st>>>(state, board, dice, player, n, geo);
+    FOR_CODEC(N, L, k_decode<C><<<blocks_for(n), TPB, obs_smem<C>(geo), st>>>(state, board, dice, player, n, geo));
     LAUNCHED("k_decode");
     return EWN_OK;
 }
@@ -1348,8 +1386,7 @@ int ewn_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, in
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_legal<P5><<<blocks_for(n), TPB, 0, st>>>(state, player, mask, list, count, n, geo);
-    else           k_legal<P8><<<blocks_for(n), TPB, 0, st>>>(state, player, mask, list, count, n, geo);
+    FOR_CODEC(N, L, k_legal<C><<<blocks_for(n), TPB, 0, st>>>(state, player, mask, list, count, n, geo));
     LAUNCHED("k_legal");
     return EWN_OK;
 }
@@ -1359,8 +1396,7 @@ int ewn_check_win(const uint64_t* state, uint8_t* win, int64_t n, int N, int L, 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_check_win<P5><<<blocks_for(n), TPB, 0, st>>>(state, win, n, geo);
-    else           k_check_win<P8><<<blocks_for(n), TPB, 0, st>>>(state, win, n, geo);
+    FOR_CODEC(N, L, k_check_win<C><<<blocks_for(n), TPB, 0, st>>>(state, win, n, geo));
     LAUNCHED("k_check_win");
     return EWN_OK;
 }
@@ -1371,8 +1407,7 @@ int ewn_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_ply<P5><<<blocks_for(n), TPB, 0, st>>>(state, player, action, valid, win, moved_cube, n, geo);
-    else           k_ply<P8><<<blocks_for(n), TPB, 0, st>>>(state, player, action, valid, win, moved_cube, n, geo);
+    FOR_CODEC(N, L, k_ply<C><<<blocks_for(n), TPB, 0, st>>>(state, player, action, valid, win, moved_cube, n, geo));
     LAUNCHED("k_ply");
     return EWN_OK;
 }
@@ -1380,9 +1415,9 @@ int ewn_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, 
 int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, int64_t n, int N, int L, void* stream) {
     if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
     if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_set_dice<P5><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
-    else           k_set_dice<P8><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n);
+    FOR_CODEC(N, L, k_set_dice<C><<<blocks_for(n), TPB, 0, st>>>(state, dice, player, n, geo));
     LAUNCHED("k_set_dice");
     return EWN_OK;
 }
@@ -1392,8 +1427,7 @@ int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_decode_onehot<P5><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
-    else           k_decode_onehot<P8><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo);
+    FOR_CODEC(N, L, k_decode_onehot<C><<<blocks_for(n), TPB, 0, st>>>(state, board, dice, n, geo));
     LAUNCHED("k_decode_onehot");
     return EWN_OK;
 }
@@ -1405,8 +1439,7 @@ int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
     const unsigned grid = (unsigned)((n + 127) / 128);
-    if (use_p5(N)) k_numpy_random_games<P5><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
-    else           k_numpy_random_games<P8><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace);
+    FOR_CODEC(N, L, k_numpy_random_games<C><<<grid, 128, 0, st>>>(seeds, n, geo, result, agent_steps, final_state, trace));
     LAUNCHED("k_numpy_random_games");
     return EWN_OK;
 }
@@ -1425,8 +1458,7 @@ int ewn_numpy_draw(uint64_t* state, const uint32_t* raw, int32_t* cursor, int K,
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_numpy_draw<P5><<<blocks_for(n), TPB, 0, st>>>(state, raw, cursor, K, n, geo, roll_dice, pick_player, action);
-    else           k_numpy_draw<P8><<<blocks_for(n), TPB, 0, st>>>(state, raw, cursor, K, n, geo, roll_dice, pick_player, action);
+    FOR_CODEC(N, L, k_numpy_draw<C><<<blocks_for(n), TPB, 0, st>>>(state, raw, cursor, K, n, geo, roll_dice, pick_player, action));
     LAUNCHED("k_numpy_draw");
     return EWN_OK;
 }
@@ -1436,8 +1468,7 @@ int ewn_flip(const uint64_t* state, uint64_t* out, int64_t n, int N, int L, void
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_flip<P5><<<blocks_for(n), TPB, 0, st>>>(state, out, n, geo);
-    else           k_flip<P8><<<blocks_for(n), TPB, 0, st>>>(state, out, n, geo);
+    FOR_CODEC(N, L, k_flip<C><<<blocks_for(n), TPB, 0, st>>>(state, out, n, geo));
     LAUNCHED("k_flip");
     return EWN_OK;
 }
@@ -1448,8 +1479,7 @@ int ewn_random_action(const uint64_t* state, int64_t* action, int64_t n, int N, 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_random_action<P5><<<blocks_for(n), TPB, 0, st>>>(state, action, n, geo, seed, step, env_id0);
-    else           k_random_action<P8><<<blocks_for(n), TPB, 0, st>>>(state, action, n, geo, seed, step, env_id0);
+    FOR_CODEC(N, L, k_random_action<C><<<blocks_for(n), TPB, 0, st>>>(state, action, n, geo, seed, step, env_id0));
     LAUNCHED("k_random_action");
     return EWN_OK;
 }
@@ -1483,7 +1513,8 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     } while (0)
     const int N = a->board_size;
     // the VecEnv surface with compacted (or no) terminal observations runs on the persistent kernel
-    if (vec && !(a->flags & EWN_STEP_BLOCK_KERNEL) && (a->term_count || (!a->term_board && !a->term_dice)) && a->n < ((int64_t)1 << 30)) {
+    const int codec = codec_of(N, a->cube_layer);
+    if (codec != 2 && vec && !(a->flags & EWN_STEP_BLOCK_KERNEL) && (a->term_count || (!a->term_board && !a->term_dice && !a->term_code)) && a->n < ((int64_t)1 << 30)) {
         const int64_t n_units = (a->n + VTPB - 1) / VTPB;
         int64_t blocks = (int64_t)sm_count() * VMINB;
         if (blocks > n_units) blocks = n_units;
@@ -1508,13 +1539,34 @@ int ewn_step(const ewn_step_args* a, void* stream) {
         LAUNCHED("k_vstep");
         return EWN_OK;
     }
-    if (N == 5) LAUNCH_STEP(P5, 5); else if (use_p5(N)) LAUNCH_STEP(P5, 0); else if (N == 7) LAUNCH_STEP(P8, 7); else LAUNCH_STEP(P8, 0);
+    if (codec == 2) LAUNCH_STEP(PG, 0);          // cube_layer >= 4: generic codec on the block kernel
+    else if (N == 5) LAUNCH_STEP(P5, 5); else if (use_p5(N)) LAUNCH_STEP(P5, 0); else if (N == 7) LAUNCH_STEP(P8, 7); else LAUNCH_STEP(P8, 0);
 #undef LAUNCH_STEP
     LAUNCHED("k_step");
     return EWN_OK;
 }
 
+// the two dice a step draws (STEP block words 0 and 2), for callers that run the opponent's policy themselves between the two plies
+__global__ void __launch_bounds__(TPB) k_step_dice(int32_t* dice_opp, int32_t* dice_next, int64_t n, int cube_num, u64 seed, u64 step, u64 env_id0,
+                                                   const unsigned long long* step_dev) {
+    int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    u32 blk[4]; env_block(seed, env_id0 + (u64)i, step + (step_dev ? *step_dev : 0ull), TAG_STEP, blk);
+    if (dice_opp) dice_opp[i] = 1 + (int)bounded(blk[0], (u32)cube_num);
+    if (dice_next) dice_next[i] = 1 + (int)bounded(blk[2], (u32)cube_num);
+}
+
 __global__ void k_counter_add(unsigned long long* c, unsigned long long k) { if (threadIdx.x == 0 && blockIdx.x == 0) *c += k; }
+
+int ewn_step_dice(int32_t* dice_opp, int32_t* dice_next, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0,
+                  const uint64_t* step_dev, void* stream) {
+    if ((!dice_opp && !dice_next) || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    k_step_dice<<<blocks_for(n), TPB, 0, (cudaStream_t)stream>>>(dice_opp, dice_next, n, L * (L + 1) / 2, seed, step, env_id0,
+                                                                 reinterpret_cast<const unsigned long long*>(step_dev));
+    LAUNCHED("k_step_dice");
+    return EWN_OK;
+}
 
 int ewn_counter_add(uint64_t* counter, uint64_t k, void* stream) {
     if (!counter) return EWN_EARG;
@@ -1528,8 +1580,7 @@ int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, 
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
-    if (use_p5(N)) k_evaluate<P5><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo, heuristic);
-    else           k_evaluate<P8><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo, heuristic);
+    FOR_CODEC(N, L, k_evaluate<C><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo, heuristic));
     LAUNCHED("k_evaluate");
     return EWN_OK;
 }
@@ -1598,7 +1649,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
         size_t want = per_root * (size_t)n;
         const size_t cap = (size_t)1 << 30;
         if (want > cap) want = cap > per_root ? cap : per_root;
-        int rc = scratch_get(want, &workspace);
+        int rc = scratch_get(want, &workspace, st);
         if (rc) return rc;
         workspace_bytes = want;
     }
@@ -1655,7 +1706,7 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     if (n > ((int64_t)1 << 28)) return EWN_ENOSUP;        // slot * 8 + child is a 32-bit word
     const size_t need = ewn_mc_workspace(n);
     if (!workspace || workspace_bytes == 0) {
-        int rc = scratch_get(need, &workspace);
+        int rc = scratch_get(need, &workspace, (cudaStream_t)stream);
         if (rc) return rc;
     } else if (workspace_bytes < need) return EWN_ESPACE;
     Geo geo = make_geo(N, L);
@@ -1675,6 +1726,7 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
 
 int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void* stream) {
     if (!state || !wins || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
     if (n == 0) return EWN_OK;
     Geo geo = make_geo(N, L);
     cudaStream_t st = (cudaStream_t)stream;
@@ -1723,6 +1775,7 @@ int ewn_mc_best_action_peers(const uint64_t* state, const uint32_t* const* wins_
                              uint32_t epoch, uint32_t timeout_ms, uint32_t* wins_total, int8_t* action, int64_t n, int N, int L, void* stream) {
     if (!state || !wins_peers || !flag_peers || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
     if (world < 1 || world > EWN_MAX_PEERS || rank < 0 || rank >= world || epoch == 0) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
     PeerSet ps;
     for (int r = 0; r < EWN_MAX_PEERS; r++) {
         ps.wins[r] = r < world ? wins_peers[r] : nullptr;
@@ -1753,7 +1806,7 @@ struct ewn_vec {
     uint64_t* state;
     int64_t* action;
     int16_t* obs_board; int64_t* obs_dice; float* reward; uint8_t* done; uint8_t* trunc;
-    int16_t* term_board; int64_t* term_dice; int32_t* term_index; uint32_t* term_count;
+    int16_t* term_board; int64_t* term_dice; int32_t* term_index; uint32_t* term_count; uint8_t* term_code;
     uint32_t* count_host;          // page-locked landing slot for *term_count
     int32_t* tolerance; double* prev_score;
 };
@@ -1765,7 +1818,7 @@ static void vec_free(ewn_vec* v) {
     if (v->h2d) cudaStreamDestroy(v->h2d);
     for (int i = 0; i < 64; i++) if (v->ev[i]) cudaEventDestroy(v->ev[i]);
     cudaFree(v->state); cudaFree(v->action); cudaFree(v->obs_board); cudaFree(v->obs_dice); cudaFree(v->reward);
-    cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->term_index); cudaFree(v->term_count);
+    cudaFree(v->done); cudaFree(v->trunc); cudaFree(v->term_board); cudaFree(v->term_dice); cudaFree(v->term_index); cudaFree(v->term_count); cudaFree(v->term_code);
     if (v->count_host) cudaFreeHost(v->count_host);
     cudaFree(v->tolerance); cudaFree(v->prev_score);
     delete v;
@@ -1779,7 +1832,7 @@ int ewn_vec_create(const ewn_vec_config* cfg, ewn_vec** out) {
     v->cfg = *cfg;
     if (v->cfg.chunks <= 0) v->cfg.chunks = 8;
     if (v->cfg.chunks > 64) v->cfg.chunks = 64;
-    v->words = use_p5(cfg->board_size) ? 1 : 2;
+    v->words = make_geo(cfg->board_size, cfg->cube_layer).sw;
     v->n_streams = 3;
     const int64_t n = cfg->n;
     const int NN = cfg->board_size * cfg->board_size;
@@ -1799,6 +1852,7 @@ int ewn_vec_create(const ewn_vec_config* cfg, ewn_vec** out) {
     VEC_TRY(cudaMalloc(&v->term_board, (size_t)n * NN * 2));
     VEC_TRY(cudaMalloc(&v->term_dice, (size_t)n * 8));
     VEC_TRY(cudaMalloc(&v->term_index, (size_t)n * 4));
+    VEC_TRY(cudaMalloc(&v->term_code, (size_t)n));
     VEC_TRY(cudaMalloc(&v->term_count, 256));
     VEC_TRY(cudaMemset(v->term_count, 0, 256));
     VEC_TRY(cudaHostAlloc((void**)&v->count_host, 64, cudaHostAllocDefault));
@@ -1854,8 +1908,19 @@ static void* pinned_alias(const void* p) {
     return at.type == cudaMemoryTypeHost ? at.devicePointer : nullptr;
 }
 
+int ewn_vec_set_seed(ewn_vec* v, uint64_t seed) {
+    if (!v) return EWN_EARG;
+    v->cfg.seed = seed;
+    return EWN_OK;
+}
+
 int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t* obs_dice, float* reward, uint8_t* done, uint8_t* truncated,
                  int16_t* term_board, int64_t* term_dice, int32_t* term_index, uint32_t* term_count) {
+    return ewn_vec_step2(v, action, obs_board, obs_dice, reward, done, truncated, term_board, term_dice, term_index, nullptr, term_count);
+}
+
+int ewn_vec_step2(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t* obs_dice, float* reward, uint8_t* done, uint8_t* truncated,
+                  int16_t* term_board, int64_t* term_dice, int32_t* term_index, uint8_t* term_code, uint32_t* term_count) {
     if (!v || !action) return EWN_EARG;
     if (term_count && !term_index) return EWN_EARG;
     CU(cudaSetDevice(v->cfg.device));
@@ -1867,8 +1932,9 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
     int16_t* d_board = (int16_t*)pinned_alias(obs_board); int64_t* d_dice = (int64_t*)pinned_alias(obs_dice);
     float* d_rew = (float*)pinned_alias(reward); uint8_t* d_done = (uint8_t*)pinned_alias(done); uint8_t* d_trunc = (uint8_t*)pinned_alias(truncated);
     int16_t* d_tb = (int16_t*)pinned_alias(term_board); int64_t* d_td = (int64_t*)pinned_alias(term_dice); int32_t* d_ti = (int32_t*)pinned_alias(term_index);
+    uint8_t* d_tc = (uint8_t*)pinned_alias(term_code);
     const bool direct = !c.shaped && !(c.flags & EWN_VEC_STAGED) && d_board && d_dice && d_rew && d_done && d_trunc &&
-                        (!term_count || ((!term_board || d_tb) && (!term_dice || d_td) && d_ti));
+                        (!term_count || ((!term_board || d_tb) && (!term_dice || d_td) && d_ti && (!term_code || d_tc)));
     // chunk boundaries are multiples of 1024 games so that every chunk starts 16-byte aligned in every array
     int64_t per = (c.n + c.chunks - 1) / c.chunks;
     per = (per + 1023) & ~(int64_t)1023;
@@ -1895,11 +1961,14 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
             a.obs_board = v->obs_board + lo * NN; a.obs_dice = v->obs_dice + lo;
         }
         if (term_count) {               // compacted terminal observations, one list for all chunks
-            if (direct) { a.term_board = d_tb; a.term_dice = d_td; a.term_index = d_ti; }
-            else { a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr; a.term_index = v->term_index; }
+            if (direct) { a.term_board = d_tb; a.term_dice = d_td; a.term_index = d_ti; a.term_code = d_tc; }
+            else { a.term_board = term_board ? v->term_board : nullptr; a.term_dice = term_dice ? v->term_dice : nullptr; a.term_index = v->term_index;
+                   a.term_code = term_code ? v->term_code : nullptr; }
             a.term_count = v->term_count + (v->step & 1); a.term_index_base = lo;
-            if (lo == 0) a.term_count_clear = v->term_count + ((v->step + 1) & 1);
         }
+        // every step clears the counter the NEXT one appends to, whether or not this call asked for terminal observations: a caller
+        // that skips them for one step must not find the count of two steps ago (rows would be appended past it)
+        if (lo == 0) a.term_count_clear = v->term_count + ((v->step + 1) & 1);
         if (c.shaped) { a.tolerance = v->tolerance + lo; a.prev_score = v->prev_score + lo; a.shaped = 1; }
         a.reward = c.reward; a.illegal_move_reward = c.illegal_move_reward;
         a.seed = c.seed; a.step = v->step; a.env_id0 = c.env_id0 + (uint64_t)lo;
@@ -1926,6 +1995,7 @@ int ewn_vec_step(ewn_vec* v, const int64_t* action, int16_t* obs_board, int64_t*
             if (term_board) CU(cudaMemcpyAsync(term_board, v->term_board, (size_t)cnt * NN * 2, cudaMemcpyDeviceToHost, s0));
             if (term_dice) CU(cudaMemcpyAsync(term_dice, v->term_dice, (size_t)cnt * 8, cudaMemcpyDeviceToHost, s0));
             CU(cudaMemcpyAsync(term_index, v->term_index, (size_t)cnt * 4, cudaMemcpyDeviceToHost, s0));
+            if (term_code) CU(cudaMemcpyAsync(term_code, v->term_code, (size_t)cnt, cudaMemcpyDeviceToHost, s0));
         }
     }
     CU(cudaStreamSynchronize(s0));

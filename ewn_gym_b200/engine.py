@@ -71,7 +71,7 @@ class Engine:
         self.cube_num = self.L * (self.L + 1) // 2
         self.lib = library if library is not None else _lib.lib()
         self.xp = arrays if arrays is not None else TorchCuda(device)
-        self.words = self.lib.ewn_state_words(self.N)
+        self.words = self.lib.ewn_state_words_cfg(self.N, self.L)
         if self.words < 1:
             raise ValueError(f"board_size {board_size} not supported (3..9)")
 
@@ -80,7 +80,7 @@ class Engine:
         _lib.check(rc, what, self.lib)
 
     def _state_shape(self, n):
-        return (n,) if self.words == 1 else (n, 2)
+        return (n,) if self.words == 1 else (n, self.words)
 
     def new_state(self, n):
         return self.xp.empty(self._state_shape(n), "u64")
@@ -229,7 +229,7 @@ class Engine:
         res = dict(out or {})
         shapes = {"reward_f32": ((n,), "f32"), "reward_f64": ((n,), "f64"), "terminated": ((n,), "u8"), "truncated": ((n,), "u8"),
                   "code": ((n,), "i32"), "action_out": ((n,), "u8"), "obs_board": ((n, self.N, self.N), "i16"), "obs_dice": ((n,), "i64"),
-                  "term_board": ((n, self.N, self.N), "i16"), "term_dice": ((n,), "i64")}
+                  "term_board": ((n, self.N, self.N), "i16"), "term_dice": ((n,), "i64"), "term_code": ((n,), "u8")}
         for name in want:
             if name not in res:
                 res[name] = xp.empty(*shapes[name])
@@ -239,16 +239,10 @@ class Engine:
         if action is not None:
             import numpy as np
             dtn = str(action.dtype).replace("torch.", "")
-            if dtn == "int64":
-                a.action_i64 = xp.ptr(action)
-            elif dtn == "int32":
-                a.action_i32 = xp.ptr(action)
-            elif dtn == "uint8":
-                a.action_u8 = xp.ptr(action)
-            else:
-                act = xp.asarray(action, "i64")
-                keep.append(act)
-                a.action_i64 = xp.ptr(act)
+            kind = {"int64": "i64", "int32": "i32", "uint8": "u8"}.get(dtn, "i64")
+            act = xp.asarray(action, kind)          # on the engine's device and contiguous (a no-op for tensors that already are)
+            keep.append(act)
+            setattr(a, "action_" + kind, xp.ptr(act))
         for name in shapes:
             if name in res and res[name] is not None:
                 setattr(a, name, xp.ptr(res[name]))
@@ -270,8 +264,16 @@ class Engine:
         a.flags = (1 if block_kernel else 0) | (2 if no_pdl else 0)
         if step_dev is not None:                   # int64[1] device counter added to `step` at run time (CUDA-graph replays)
             a.step_dev = xp.ptr(step_dev)
+        self._last_keep = keep                     # StepPlan holds on to these: its launches reuse the pointers
         self._chk(self.lib.ewn_step(C.byref(a), xp.stream()), "ewn_step")
         return res
+
+    def step_dice(self, n: int, seed: int, step: int, env_id0: int = 0, step_dev=None):
+        """-> (dice_opp i32[n], dice_next i32[n]): the dice step `step` draws (envs/ewn.py:458 and :483), for external opponents"""
+        d0, d1 = self.xp.empty((n,), "i32"), self.xp.empty((n,), "i32")
+        self._chk(self.lib.ewn_step_dice(self.xp.ptr(d0), self.xp.ptr(d1), n, self.N, self.L, seed, step, env_id0, self.xp.ptr(step_dev),
+                                         self.xp.stream()), "ewn_step_dice")
+        return d0, d1
 
     def counter_add(self, counter, k: int):
         """*counter += k on the current stream (see ewn_step_args.step_dev)"""
@@ -349,7 +351,7 @@ class StepPlan:
         finally:
             engine.lib = lib
         self.args, self.stream = captured["args"], captured["stream"]
-        self._keep = (state, action, kw)
+        self._keep = (state, action, kw, list(getattr(engine, "_last_keep", ())))    # every tensor whose pointer the argument block holds
         self._fn, self._ref = real, C.byref(self.args)
 
     def launch(self, step: int):

@@ -68,14 +68,18 @@ def mc_predict_sharded(engine, state, seed: int, playouts_per_action: int, root_
     return engine.mc_best_action(state, wins), wins
 
 
-def mc_predict_peers(engine, exchange, state, seed: int, playouts_per_action: int, root_ids=None, first: int = 0):
+def mc_predict_peers(engine, exchange, state, seed: int, playouts_per_action: int, root_ids=None, first: int = 0, check: bool = False):
     """mc_predict_sharded without the collective library: the win counters are written straight into this rank's NVLink-visible
     buffer and ONE kernel per rank merges all ranks' counters with peer loads and takes the arg-max (ewn_gym_b200/peer.py).
-    -> (action int8[n][2], wins u32[n][6]); identical on every rank and identical to mc_predict_sharded."""
+    -> (action int8[n][2], wins u32[n][6]); identical on every rank and identical to mc_predict_sharded.
+    check=True raises if the wait for the peers timed out (that costs a device synchronisation; arena.play_matches checks at its own)."""
     lo, hi = split_range(playouts_per_action, exchange.rank, exchange.world)
     w = exchange.wins_buffer()
     engine.mc_root_wins(state, seed, first + lo, hi - lo, root_ids=root_ids, wins=w)
-    return exchange.best_action(state)
+    out = exchange.best_action(state)
+    if check:                                    # synchronises; a timed-out wait also shows as action (-1, -1) on every root
+        exchange.check()
+    return out
 
 
 class ShardedRollout:

@@ -9,8 +9,12 @@
  *   - plain C, no torch types: device pointers + sizes + an explicit cudaStream_t (passed as void*; NULL = the
  *     legacy default stream).  Entry points only enqueue work on `stream`; they never synchronise, except the
  *     ewn_vec_* host-buffer calls, which return after the outputs are in the caller's host buffers.
- *   - every function returns 0 on success or a negative EWN_E* code; nothing throws; no hidden global state.
- *   - `state` is the packed game array: ewn_state_words(N) u64 per game (1 for N<=5, 2 for N<=9), game-major.
+ *   - every function returns 0 on success or a negative EWN_E* code; nothing throws.  The library keeps two process-wide caches,
+ *     both mutex-guarded: the 'hybrid' value tables of ewn_expectiminimax (one per device and board size, read-only once built)
+ *     and the scratch used when a search call passes no workspace (one per device and stream -- calls on one stream are ordered
+ *     by the stream, calls on different streams never share scratch).
+ *   - `state` is the packed game array: ewn_state_words_cfg(N, L) u64 per game (1 for N<=5, 2 for N<=9 with cube_layer <= 3;
+ *     2*ceil(cube_num/8)+1 for cube_layer >= 4), game-major.
  *     Layout is documented in DESIGN.md "Packed state" and ewn_gym_b200/csrc/ewn_core.cuh.
  *   - boards are int16 [n][N][N] exactly as the reference's observation (envs/ewn.py:63-69): +k TOP_LEFT cube k,
  *     -k BOTTOM_RIGHT cube k, 0 empty.  Players: 1 = TOP_LEFT, 2 = BOTTOM_RIGHT (constants/player.py:5-6).
@@ -67,8 +71,11 @@ EWN_API int ewn_device_count(void);
 /* "dddd:bb:dd.f" of a CUDA device (len >= 13): lets the host layer find the NUMA node the GPU hangs off
  * (/sys/bus/pci/devices/<id>/numa_node) and keep its page-locked buffers and stepping thread there (vec_env.py) */
 EWN_API int ewn_device_pci_bus_id(int device, char *out, int len);
-/* u64 words per game for this board size (1 or 2), or EWN_EARG */
+/* u64 words per game for this board size with cube_layer <= 3 (1 or 2), or EWN_EARG */
 EWN_API int ewn_state_words(int board_size);
+/* u64 words per game for (board_size, cube_layer): 1 / 2 for the six-cube layouts, 2 * ceil(cube_num / 8) + 1 for cube_layer >= 4
+ * (envs/ewn.py:47,51: any cube_layer < board_size - 1, cube_num = L (L + 1) / 2), or EWN_EARG */
+EWN_API int ewn_state_words_cfg(int board_size, int cube_layer);
 /* total kernels launched by this library in this process (bench.py reports it as gpu_launches) */
 EWN_API int64_t ewn_launch_count(void);
 
@@ -166,6 +173,9 @@ typedef struct ewn_step_args {
     const uint64_t *step_dev;     /* optional device counter added to `step` when the kernel runs: a CUDA graph of K   */
                                   /* captured steps (step = 1..K baked in) is replayed with fresh Philox counters by   */
                                   /* ewn_counter_add(step_dev, K) at the end of the graph                              */
+    uint8_t *term_code;           /* optional, rows as term_dice (compacted with term_count, else dense): EWN_CODE_* of the   */
+                                  /* finished game -- info["message"] of envs/ewn.py:448,454,473,478 without guessing it     */
+                                  /* from the reward's sign                                                                  */
 } ewn_step_args;
 
 /* flags: run the VecEnv surface on the one-block-per-128-games kernel instead of the persistent one (A/B measurements) */
@@ -174,6 +184,14 @@ typedef struct ewn_step_args {
 #define EWN_STEP_NO_PDL 2
 
 EWN_API int ewn_step(const ewn_step_args *args, void *stream);
+/* The two dice a step draws for games i = 0..n-1 (Philox STEP block of (env_id0+i, step [+ *step_dev]): word 0 = the die rolled for
+ * the opponent's ply at envs/ewn.py:458, word 2 = the die at :483 / the first die after an auto-reset), as int32[n] arrays (either
+ * may be NULL).  For opponents that are not the in-kernel random player (envs/ewn.py:265-296 opponent_policy): the caller plays the
+ * agent's ply on a copy (ewn_ply), sets dice_opp, flips (ewn_flip), asks its policy, and then runs the real step in replay mode with
+ * inject_dice_opp = dice_opp, inject_opp_action = the policy's answers, inject_dice_next = dice_next -- the same dice the fused
+ * random-opponent step would have drawn. */
+EWN_API int ewn_step_dice(int32_t *dice_opp, int32_t *dice_next, int64_t n, int board_size, int cube_layer, uint64_t seed, uint64_t step,
+                  uint64_t env_id0, const uint64_t *step_dev, void *stream);
 /* *counter += k on `stream` (one tiny kernel; capturable).  See ewn_step_args.step_dev. */
 EWN_API int ewn_counter_add(uint64_t *counter, uint64_t k, void *stream);
 
@@ -285,6 +303,13 @@ EWN_API int ewn_vec_reset(ewn_vec *v, int16_t *obs_board, int64_t *obs_dice);
  * sized for n rows; pass term_count == NULL to skip terminal observations altogether). */
 EWN_API int ewn_vec_step(ewn_vec *v, const int64_t *action, int16_t *obs_board, int64_t *obs_dice, float *reward, uint8_t *done,
                  uint8_t *truncated, int16_t *term_board, int64_t *term_dice, int32_t *term_index, uint32_t *term_count);
+/* the same with the result code (EWN_CODE_*) of every finished game, term_code u8[n] compacted like term_dice (or NULL) */
+EWN_API int ewn_vec_step2(ewn_vec *v, const int64_t *action, int16_t *obs_board, int64_t *obs_dice, float *reward, uint8_t *done,
+                  uint8_t *truncated, int16_t *term_board, int64_t *term_dice, int32_t *term_index, uint8_t *term_code,
+                  uint32_t *term_count);
+/* VecEnv.seed(seed) (train.py:135): the Philox key the NEXT ewn_vec_reset and every step after it use; game i keeps its own
+ * stream (key = seed, counter = env_id0 + i), which is what SubprocVecEnv's seed + i per worker amounts to */
+EWN_API int ewn_vec_set_seed(ewn_vec *v, uint64_t seed);
 /* pinned host memory helpers so that callers can hand in page-locked numpy buffers */
 EWN_API int ewn_host_alloc(void **ptr, size_t bytes);
 EWN_API int ewn_host_free(void *ptr);

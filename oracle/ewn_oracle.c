@@ -27,7 +27,7 @@
 #include <stdlib.h>
 
 #define ORC_MAXN 9
-#define ORC_MAXC 6 /* cube_num = L(L+1)/2 <= 6, i.e. cube_layer <= 3 */
+#define ORC_MAXC 28 /* cube_num = L(L+1)/2, cube_layer < board_size - 1 <= 8 (envs/ewn.py:47,51): up to 28 cubes per side on 9x9 */
 
 #define TOP_LEFT 1     /* constants/player.py:5 */
 #define BOTTOM_RIGHT 2 /* constants/player.py:6 */

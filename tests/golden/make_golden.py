@@ -210,7 +210,7 @@ def gen_rules(name, N, L, n_states):
         if win or si >= 1500:
             continue
         for player in (R.Player.TOP_LEFT, R.Player.BOTTOM_RIGHT):
-            for d in range(1, 7):
+            for d in range(1, menv.cube_num + 1):            # envs/ewn.py:91: the die has cube_num faces
                 ag.restore_env_with_obs({"board": b.astype(np.int16), "dice_roll": d})
                 has_cube = (menv.board > 0).any() if player == R.Player.TOP_LEFT else (menv.board < 0).any()
                 if not has_cube:
@@ -386,6 +386,12 @@ TARGETS = {
     "games5": lambda: gen_games("random_games_5x5.npz", 5, 3, 10000),
     "games7": lambda: gen_games("random_games_7x7.npz", 7, 3, 1000),
     "games4": lambda: gen_games("random_games_4x4_L2.npz", 4, 2, 500),
+    # cube_layer >= 4 (envs/ewn.py:47,51: 10 / 15 / 28 cubes per side, die with as many faces): the generic state codec
+    "games7L4": lambda: gen_games("random_games_7x7_L4.npz", 7, 4, 400),
+    "games9L7": lambda: gen_games("random_games_9x9_L7.npz", 9, 7, 60),
+    "rules6L4": lambda: gen_rules("rules_6x6_L4.npz", 6, 4, 300),
+    "rules7L5": lambda: gen_rules("rules_7x7_L5.npz", 7, 5, 150),
+    "shaped7L4": lambda: gen_shaped("shaped_7x7_L4.npz", 7, 4, 16, 96, 10),
     "mm5": lambda: gen_minimax("minimax_5x5.npz", 5, 3, 2000, {1: 2000, 2: 2000, 3: 2000, 4: 2000, 5: 320}),
     "mm7": lambda: gen_minimax("minimax_7x7.npz", 7, 3, 600, {1: 600, 2: 600, 3: 600, 4: 600, 5: 96}, heur_count=100),
     "rules5": lambda: gen_rules("rules_5x5.npz", 5, 3, 4000),

@@ -14,15 +14,20 @@
 using namespace ewn;
 
 namespace {
-inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L <= 3 && L < N - 1; }
+inline bool config_ok(int N, int L) { return N >= 3 && N <= EWN_MAX_BOARD && L >= 1 && L < N - 1; }
+// f(codec tag) with the codec of (N, L): P5 / P8 for the six-cube layouts, PG for cube_layer >= 4
+template <class F> auto with_codec(int N, int L, F&& f) {
+    switch (codec_of(N, L)) { case 0: return f(P5{}); case 1: return f(P8{}); default: return f(PG{}); }
+}
+#define WITH_CODEC(N, L, expr) with_codec(N, L, [&](auto c_) { typedef decltype(c_) C; return (expr); })
 
 template <class C> void decode_one(const Game<C>& g, const Geo& geo, int16_t* row) {
     const int N = geo.N;
     memset(row, 0, sizeof(int16_t) * N * N);
-    for (int k = 0; k < 6; k++) {
-        int c = (int)((g.tl >> (C::FB * k)) & C::FM);
+    for (int k = 0; k < C::ncubes(geo); k++) {
+        int c = C::get(g.tl, k);
         if (c != (int)C::FM) row[C::x_of(c) * N + C::y_of(c)] = (int16_t)(k + 1);
-        int d = (int)((g.br >> (C::FB * k)) & C::FM);
+        int d = C::get(g.br, k);
         if (d != (int)C::FM) row[C::x_of(d) * N + C::y_of(d)] = (int16_t)(-(k + 1));
     }
 }
@@ -30,30 +35,29 @@ template <class C> void decode_one(const Game<C>& g, const Geo& geo, int16_t* ro
 template <class C> int t_reset(uint64_t* state, const int32_t* dice_in, int64_t n, const Geo& geo, u64 seed, u64 step, u64 env_id0) {
     for (int64_t i = 0; i < n; i++) {
         int dice;
-        if (dice_in) dice = dice_in[i];
+        if (dice_in) { dice = dice_in[i]; dice = dice < 1 ? 1 : (dice > geo.cube_num ? geo.cube_num : dice); }
         else { u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_RESET, blk); dice = 1 + (int)bounded(blk[0], (u32)geo.cube_num); }
         Game<C> g; setup<C>(g, geo, dice);
-        pack(g, state, i);
+        pack(g, state, i, geo);
     }
     return EWN_OK;
 }
 
 template <class C> int t_encode(const int16_t* board, const int32_t* dice, const int32_t* player, uint64_t* state, int64_t n, const Geo& geo) {
-    typedef typename C::W W;
-    const int N = geo.N, NN = N * N;
+    const int N = geo.N, NN = N * N, nc = geo.cube_num;
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; g.tl = C::ALL; g.br = C::ALL;
+        Game<C> g; g.tl = C::all(); g.br = C::all();
         const int16_t* b = board + i * NN;
         for (int x = 0; x < N; x++)
             for (int y = 0; y < N; y++) {
                 int v = b[x * N + y];
-                if (v > 0 && v <= 6) { int sh = C::FB * (v - 1); g.tl = (g.tl & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
-                else if (v < 0 && v >= -6) { int sh = C::FB * (-v - 1); g.br = (g.br & ~(C::FM << sh)) | ((W)C::cell(x, y) << sh); }
+                if (v > 0 && v <= nc) C::set(g.tl, v - 1, C::cell(x, y));
+                else if (v < 0 && v >= -nc) C::set(g.br, -v - 1, C::cell(x, y));
             }
         int d = dice ? dice[i] : 1;
-        g.dice = d < 1 ? 1 : (d > 6 ? 6 : d);
+        g.dice = d < 1 ? 1 : (d > nc ? nc : d);
         g.player = (player && player[i] == EWN_BOTTOM_RIGHT) ? SIDE_BR : SIDE_TL;
-        pack(g, state, i);
+        pack(g, state, i, geo);
     }
     return EWN_OK;
 }
@@ -61,7 +65,7 @@ template <class C> int t_encode(const int16_t* board, const int32_t* dice, const
 template <class C> int t_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* player, int64_t n, const Geo& geo) {
     const int NN = geo.N * geo.N;
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i);
+        Game<C> g; unpack(g, state, i, geo);
         if (dice) dice[i] = g.dice;
         if (player) player[i] = g.player == SIDE_BR ? EWN_BOTTOM_RIGHT : EWN_TOP_LEFT;
         if (board) decode_one<C>(g, geo, board + i * NN);
@@ -71,7 +75,7 @@ template <class C> int t_decode(const uint64_t* state, int16_t* board, int64_t* 
 
 template <class C> int t_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, int32_t* count, int64_t n, const Geo& geo) {
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i);
+        Game<C> g; unpack(g, state, i, geo);
         int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
         Legal l;
         if (side == SIDE_BR) l = legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice));
@@ -94,13 +98,13 @@ template <class C> int t_legal(const uint64_t* state, int player, uint8_t* mask,
 template <class C> int t_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, uint8_t* win, int32_t* moved, int64_t n,
                              const Geo& geo) {
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i);
+        Game<C> g; unpack(g, state, i, geo);
         int side = player == 0 ? g.player : (player == EWN_BOTTOM_RIGHT ? SIDE_BR : SIDE_TL);
         int t = 0, sh = -1; bool ok;
         if (side == SIDE_BR) ok = ply_action<C, SIDE_BR>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
         else                 ok = ply_action<C, SIDE_TL>(g, geo, action[2 * i], action[2 * i + 1], t, sh);
         if (ok) g.player = side ^ 1;
-        pack(g, state, i);
+        pack(g, state, i, geo);
         if (valid) valid[i] = ok ? 1 : 0;
         if (win) win[i] = full_win<C>(g, geo) ? 1 : 0;
         if (moved) moved[i] = sh < 0 ? 0 : sh / C::FB + 1;
@@ -117,7 +121,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
     p.agent_random = a.agent_random != 0; p.autoreset = a.autoreset != 0; p.shaped = a.shaped != 0; p.replay = replay;
     if (a.term_count_clear) *a.term_count_clear = 0u;
     for (int64_t i = 0; i < a.n; i++) {
-        Game<C> g, term; unpack(g, a.state, i); term = g;
+        Game<C> g, term; unpack(g, a.state, i, geo); term = g;
         int al = 0, ad = 0;
         if (!p.agent_random) {
             if (a.action_i64) { al = (int)a.action_i64[2 * i]; int64_t y = a.action_i64[2 * i + 1]; ad = (y < 0 || y > 2) ? 3 : (int)y; }
@@ -131,7 +135,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
         StepOut out;
         step_one<C>(g, term, p, i, al, ad, inj, &tol, &prev, out);
         if (p.shaped) { a.tolerance[i] = tol; a.prev_score[i] = prev; }
-        pack(g, a.state, i);
+        pack(g, a.state, i, geo);
         if (a.reward_f32) a.reward_f32[i] = (float)out.reward;
         if (a.reward_f64) a.reward_f64[i] = out.reward;
         if (a.terminated) a.terminated[i] = (uint8_t)out.term;
@@ -148,6 +152,7 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
             int64_t row = i;
             if (a.term_count) { row = (*a.term_count)++; a.term_index[row] = (int32_t)(a.term_index_base + i); }
             if (a.term_dice) a.term_dice[row] = term.dice;
+            if (a.term_code) a.term_code[row] = (uint8_t)out.code;
             if (a.term_board) decode_one<C>(term, geo, a.term_board + row * NN);
         }
     }
@@ -214,7 +219,7 @@ template <class C> int t_emm(const uint64_t* state, int64_t n, const Geo& geo, i
 template <class C> int t_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, const Geo& geo, u64 seed, u32 first, u32 count,
                                   uint32_t* wins, unsigned long long* plies) {
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i);
+        Game<C> g; unpack(g, state, i, geo);
         for (u32 p = first; p < first + count; p++) {
             int pl = 0;
             wins[i] += (u32)playout<C>(g, geo, seed, root_ids ? root_ids[i] : (u32)i, 7u, p, &pl);
@@ -227,7 +232,7 @@ template <class C> int t_playouts(const uint64_t* state, const uint32_t* root_id
 template <class C> int t_mc(const uint64_t* state, const uint32_t* root_ids, int64_t n, const Geo& geo, u64 seed, u32 first, u32 count,
                             uint32_t* wins, int32_t* n_children, unsigned long long* plies) {
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i); g.player = SIDE_TL;
+        Game<C> g; unpack(g, state, i, geo); g.player = SIDE_TL;
         int cnt = 0;
         if (!full_win<C>(g, geo)) {
             Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
@@ -249,7 +254,7 @@ template <class C> int t_mc(const uint64_t* state, const uint32_t* root_ids, int
 
 template <class C> int t_mc_best(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, const Geo& geo) {
     for (int64_t i = 0; i < n; i++) {
-        Game<C> g; unpack(g, state, i);
+        Game<C> g; unpack(g, state, i, geo);
         int la = -1, di = -1;
         if (!full_win<C>(g, geo)) {
             Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
@@ -264,7 +269,7 @@ template <class C> int t_mc_best(const uint64_t* state, const uint32_t* wins, in
 }  // namespace
 
 template <class C> static int t_flip(const uint64_t* in, uint64_t* out, int64_t n, const Geo& geo) {
-    for (int64_t i = 0; i < n; i++) { Game<C> g; unpack(g, in, i); flip_game<C>(g, geo); pack(g, out, i); }
+    for (int64_t i = 0; i < n; i++) { Game<C> g; unpack(g, in, i, geo); flip_game<C>(g, geo); pack(g, out, i, geo); }
     return EWN_OK;
 }
 #define BY_CODEC(N, call_p5, call_p8) (use_p5(N) ? (call_p5) : (call_p8))
@@ -275,63 +280,62 @@ const char* ewn_strerror(int) { return "hostsim"; }
 const char* ewn_last_cuda_error(void) { return ""; }
 int ewn_device_count(void) { return 0; }
 int ewn_state_words(int N) { return (N >= 3 && N <= EWN_MAX_BOARD) ? (use_p5(N) ? 1 : 2) : EWN_EARG; }
+int ewn_state_words_cfg(int N, int L) { return config_ok(N, L) ? make_geo(N, L).sw : EWN_EARG; }
 int64_t ewn_launch_count(void) { return 0; }
 
 int ewn_reset(uint64_t* state, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void*) {
     if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_reset<P5>(state, nullptr, n, geo, seed, step, env_id0), t_reset<P8>(state, nullptr, n, geo, seed, step, env_id0));
+    return WITH_CODEC(N, L, t_reset<C>(state, nullptr, n, geo, seed, step, env_id0));
 }
 int ewn_reset_dice(uint64_t* state, const int32_t* dice, int64_t n, int N, int L, void*) {
     if (!state || !dice || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_reset<P5>(state, dice, n, geo, 0, 0, 0), t_reset<P8>(state, dice, n, geo, 0, 0, 0));
+    return WITH_CODEC(N, L, t_reset<C>(state, dice, n, geo, 0, 0, 0));
 }
 int ewn_encode(const int16_t* board, const int32_t* dice, const int32_t* player, uint64_t* state, int64_t n, int N, int L, void*) {
     if (!board || !state || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_encode<P5>(board, dice, player, state, n, geo), t_encode<P8>(board, dice, player, state, n, geo));
+    return WITH_CODEC(N, L, t_encode<C>(board, dice, player, state, n, geo));
 }
 int ewn_decode(const uint64_t* state, int16_t* board, int64_t* dice, int32_t* player, int64_t n, int N, int L, void*) {
     if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_decode<P5>(state, board, dice, player, n, geo), t_decode<P8>(state, board, dice, player, n, geo));
+    return WITH_CODEC(N, L, t_decode<C>(state, board, dice, player, n, geo));
 }
 int ewn_legal(const uint64_t* state, int player, uint8_t* mask, int8_t* list, int32_t* count, int64_t n, int N, int L, void*) {
     if (!state || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_legal<P5>(state, player, mask, list, count, n, geo), t_legal<P8>(state, player, mask, list, count, n, geo));
+    return WITH_CODEC(N, L, t_legal<C>(state, player, mask, list, count, n, geo));
 }
 int ewn_check_win(const uint64_t* state, uint8_t* win, int64_t n, int N, int L, void*) {
     if (!state || !win || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    for (int64_t i = 0; i < n; i++) {
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); win[i] = full_win<P5>(g, geo); }
-        else { Game<P8> g; unpack(g, state, i); win[i] = full_win<P8>(g, geo); }
-    }
-    return EWN_OK;
+    return WITH_CODEC(N, L, ([&] { for (int64_t i = 0; i < n; i++) { Game<C> g; unpack(g, state, i, geo); win[i] = full_win<C>(g, geo); } return (int)EWN_OK; })());
 }
 int ewn_ply(uint64_t* state, int player, const int32_t* action, uint8_t* valid, uint8_t* win, int32_t* moved, int64_t n, int N, int L, void*) {
     if (!state || !action || n < 0 || !config_ok(N, L) || player < 0 || player > 2) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_ply<P5>(state, player, action, valid, win, moved, n, geo), t_ply<P8>(state, player, action, valid, win, moved, n, geo));
+    return WITH_CODEC(N, L, t_ply<C>(state, player, action, valid, win, moved, n, geo));
 }
 int ewn_set_dice(uint64_t* state, const int32_t* dice, const int32_t* player, int64_t n, int N, int L, void*) {
     if (!state || n < 0 || !config_ok(N, L)) return EWN_EARG;
-    for (int64_t i = 0; i < n; i++) {
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); if (dice) g.dice = dice[i]; if (player) g.player = player[i] == EWN_BOTTOM_RIGHT; pack(g, state, i); }
-        else { Game<P8> g; unpack(g, state, i); if (dice) g.dice = dice[i]; if (player) g.player = player[i] == EWN_BOTTOM_RIGHT; pack(g, state, i); }
-    }
-    return EWN_OK;
+    Geo geo = make_geo(N, L);
+    return WITH_CODEC(N, L, ([&] {
+        for (int64_t i = 0; i < n; i++) {
+            Game<C> g; unpack(g, state, i, geo);
+            if (dice) { int d = dice[i]; g.dice = d < 1 ? 1 : (d > geo.cube_num ? geo.cube_num : d); }
+            if (player) g.player = player[i] == EWN_BOTTOM_RIGHT;
+            pack(g, state, i, geo);
+        }
+        return (int)EWN_OK; })());
 }
 int ewn_random_action(const uint64_t* state, int64_t* action, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0, void*) {
     if (!state || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
     for (int64_t i = 0; i < n; i++) {
         u32 blk[4]; env_block(seed, env_id0 + (u64)i, step, TAG_STEP, blk);
-        Legal l;
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); l = legal<P5, SIDE_TL>(g, geo, movers<P5>(g.tl, g.dice)); }
-        else { Game<P8> g; unpack(g, state, i); l = legal<P8, SIDE_TL>(g, geo, movers<P8>(g.tl, g.dice)); }
+        Legal l = WITH_CODEC(N, L, ([&] { Game<C> g; unpack(g, state, i, geo); return legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice)); })());
         int c = legal_count(l), la = 0, di = 0, sh;
         if (c > 0) legal_pick(l, (int)bounded(blk[3], (u32)c), la, di, sh);
         action[2 * i] = la; action[2 * i + 1] = di;
@@ -345,7 +349,18 @@ int ewn_step(const ewn_step_args* a, void*) {
     if (replay && !(a->inject_dice_opp && a->inject_opp_action && a->inject_dice_next)) return EWN_EARG;
     if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
     Geo geo = make_geo(a->board_size, a->cube_layer);
-    return BY_CODEC(a->board_size, t_step<P5>(*a, geo), t_step<P8>(*a, geo));
+    return WITH_CODEC(a->board_size, a->cube_layer, t_step<C>(*a, geo));
+}
+int ewn_step_dice(int32_t* dice_opp, int32_t* dice_next, int64_t n, int N, int L, uint64_t seed, uint64_t step, uint64_t env_id0,
+                  const uint64_t* step_dev, void*) {
+    if ((!dice_opp && !dice_next) || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    const int cn = L * (L + 1) / 2;
+    for (int64_t i = 0; i < n; i++) {
+        u32 blk[4]; env_block(seed, env_id0 + (u64)i, step + (step_dev ? *step_dev : 0), TAG_STEP, blk);
+        if (dice_opp) dice_opp[i] = 1 + (int)bounded(blk[0], (u32)cn);
+        if (dice_next) dice_next[i] = 1 + (int)bounded(blk[2], (u32)cn);
+    }
+    return EWN_OK;
 }
 int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_t* result, int32_t* agent_steps, uint64_t* final_state,
                            uint64_t* trace, void*) {
@@ -354,8 +369,7 @@ int ewn_numpy_random_games(const uint32_t* seeds, int64_t n, int N, int L, int8_
     MT19937 rng;
     for (int64_t i = 0; i < n; i++) {
         int steps; u64 h; int r;
-        if (use_p5(N)) { Game<P5> g; r = numpy_random_game<P5>(g, geo, seeds[i], rng, steps, h); if (final_state) pack(g, final_state, i); }
-        else           { Game<P8> g; r = numpy_random_game<P8>(g, geo, seeds[i], rng, steps, h); if (final_state) pack(g, final_state, i); }
+        r = WITH_CODEC(N, L, ([&] { Game<C> g; int q = numpy_random_game<C>(g, geo, seeds[i], rng, steps, h); if (final_state) pack(g, final_state, i, geo); return q; })());
         if (result) result[i] = (int8_t)r;
         if (agent_steps) agent_steps[i] = steps;
         if (trace) trace[i] = h;
@@ -375,12 +389,9 @@ int ewn_numpy_draw(uint64_t* state, const uint32_t* raw, int32_t* cursor, int K,
     for (int64_t i = 0; i < n; i++) {
         RawStream rs; rs.raw = raw + i * K; rs.K = K; rs.cur = cursor[i];
         int la = 0, di = 0, sh;
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
-            if (pick_player) { Legal l = pick_player == EWN_BOTTOM_RIGHT ? legal<P5, SIDE_BR>(g, geo, movers<P5>(g.br, g.dice)) : legal<P5, SIDE_TL>(g, geo, movers<P5>(g.tl, g.dice));
-                int cnt = legal_count(l); if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh); } }
-        else { Game<P8> g; unpack(g, state, i); if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i); }
-            if (pick_player) { Legal l = pick_player == EWN_BOTTOM_RIGHT ? legal<P8, SIDE_BR>(g, geo, movers<P8>(g.br, g.dice)) : legal<P8, SIDE_TL>(g, geo, movers<P8>(g.tl, g.dice));
-                int cnt = legal_count(l); if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh); } }
+        WITH_CODEC(N, L, ([&] { Game<C> g; unpack(g, state, i, geo); if (roll) { g.dice = rs.randint(1, geo.cube_num + 1); pack(g, state, i, geo); }
+            if (pick_player) { Legal l = pick_player == EWN_BOTTOM_RIGHT ? legal<C, SIDE_BR>(g, geo, movers<C>(g.br, g.dice)) : legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+                int cnt = legal_count(l); if (cnt > 0) legal_pick(l, rs.randint(0, cnt), la, di, sh); } return 0; })());
         if (pick_player) { action[2 * i] = la; action[2 * i + 1] = di; }
         cursor[i] = rs.cur;
     }
@@ -393,14 +404,10 @@ int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t 
     for (int64_t i = 0; i < n; i++) {
         float* b = board + i * row;
         for (int k = 0; k < row; k++) b[k] = 0.f;
-        int64_t tl, br; int dice_v;
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); dice_v = g.dice;
-            for (int k = 0; k < cn; k++) { int c = (g.tl >> (5 * k)) & 31, d = (g.br >> (5 * k)) & 31;
-                if (c != 31) b[(P5::x_of(c) * N + P5::y_of(c)) * cn + k] = 1.f; if (d != 31) b[(P5::x_of(d) * N + P5::y_of(d)) * cn + k] = -1.f; } }
-        else { Game<P8> g; unpack(g, state, i); dice_v = g.dice;
-            for (int k = 0; k < cn; k++) { int c = (int)((g.tl >> (8 * k)) & 255), d = (int)((g.br >> (8 * k)) & 255);
-                if (c != 255) b[(P8::x_of(c) * N + P8::y_of(c)) * cn + k] = 1.f; if (d != 255) b[(P8::x_of(d) * N + P8::y_of(d)) * cn + k] = -1.f; } }
-        (void)tl; (void)br;
+        int dice_v = WITH_CODEC(N, L, ([&] { Game<C> g; unpack(g, state, i, geo);
+            for (int k = 0; k < cn; k++) { int c = C::get(g.tl, k), d = C::get(g.br, k);
+                if (c != (int)C::FM) b[(C::x_of(c) * N + C::y_of(c)) * cn + k] = 1.f; if (d != (int)C::FM) b[(C::x_of(d) * N + C::y_of(d)) * cn + k] = -1.f; }
+            return g.dice; })());
         if (dice) { for (int k = 0; k < cn; k++) dice[i * cn + k] = 0.f; if (dice_v >= 1 && dice_v <= cn) dice[i * cn + dice_v - 1] = 1.f; }
     }
     return EWN_OK;
@@ -408,15 +415,14 @@ int ewn_decode_onehot(const uint64_t* state, float* board, float* dice, int64_t 
 int ewn_flip(const uint64_t* state, uint64_t* out, int64_t n, int N, int L, void*) {
     if (!state || !out || n < 0 || !config_ok(N, L)) return EWN_EARG;
     Geo geo = make_geo(N, L);
-    return BY_CODEC(N, t_flip<P5>(state, out, n, geo), t_flip<P8>(state, out, n, geo));
+    return WITH_CODEC(N, L, t_flip<C>(state, out, n, geo));
 }
 int ewn_counter_add(uint64_t* counter, uint64_t k, void*) { if (!counter) return EWN_EARG; *counter += k; return EWN_OK; }
 int ewn_evaluate(const uint64_t* state, double* value, int64_t n, int N, int L, int heuristic, void*) {
     if (!state || !value || n < 0 || !config_ok(N, L) || heuristic < 0 || heuristic > 3) return EWN_EARG;
     Geo geo = make_geo(N, L);
     for (int64_t i = 0; i < n; i++) {
-        if (use_p5(N)) { Game<P5> g; unpack(g, state, i); value[i] = evaluate<P5>(g, geo, heuristic); }
-        else { Game<P8> g; unpack(g, state, i); value[i] = evaluate<P8>(g, geo, heuristic); }
+        value[i] = WITH_CODEC(N, L, ([&] { Game<C> g; unpack(g, state, i, geo); return evaluate<C>(g, geo, heuristic); })());
     }
     return EWN_OK;
 }

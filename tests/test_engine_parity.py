@@ -18,7 +18,7 @@ def bits(x):
 
 
 # --------------------------------------------------------------------------------------------------- codec + rules
-@pytest.mark.parametrize("name", ["rules_5x5.npz", "rules_7x7.npz"])
+@pytest.mark.parametrize("name", ["rules_5x5.npz", "rules_7x7.npz", "rules_6x6_L4.npz", "rules_7x7_L5.npz"])
 def test_rules_golden(backend, name):
     """restore_env_with_obs round trip, check_win, all four heuristics, every (die, action) ply, ordered legal lists."""
     z = load(name)
@@ -65,7 +65,8 @@ def test_initial_layout_and_reset(backend):
 
 
 # --------------------------------------------------------------------------------------------------- config 1: replay
-@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz"])
+@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz", "random_games_7x7_L4.npz",
+                                  "random_games_9x9_L7.npz"])
 def test_replay_reference_games(backend, name):
     """Config 1: every env.step of the reference's eval_random loop, all games in one batch, dice/opponent injected.
     Checks legal mask before, board / reward / flags / dice after every step; 5x5: 5,215 wins over 108,978 steps."""
@@ -168,7 +169,7 @@ def test_expectiminimax_vs_oracle_unpruned_and_deep(backend):
 
 
 # --------------------------------------------------------------------------------------------------- config 2: free-running step
-@pytest.mark.parametrize("N,L", [(5, 3), (7, 3), (4, 2)])
+@pytest.mark.parametrize("N,L", [(5, 3), (7, 3), (4, 2), (7, 4), (9, 7)])
 @pytest.mark.parametrize("agent_random", [True, False])
 def test_step_philox_vs_oracle(backend, N, L, agent_random):
     """Config 2 on a 4,096-env subset: Philox dice, in-kernel random opponent, auto-reset, observation + terminal
@@ -214,9 +215,10 @@ def test_step_philox_vs_oracle(backend, N, L, agent_random):
         ob, od = ref["board"], ref["dice"]
         wins += int((ref["code"] == O.CODE_AGENT_WON).sum()); losses += int((ref["code"] == O.CODE_AGENT_LOST).sum())
         illegal += int((ref["code"] == O.CODE_AGENT_ILLEGAL).sum())
-    assert wins > 300 and losses > 300
+    thr = 300 if L <= 3 else 40                    # games on the big layouts last several times longer
+    assert wins > thr and losses > thr
     assert to_np(stats).tolist()[:2] == [wins, losses] and to_np(stats)[2] == illegal and to_np(stats)[3] == wins + losses + illegal
-    assert (illegal == 0) if agent_random else (illegal > 300)
+    assert (illegal == 0) if agent_random else (illegal > thr)
 
 
 def test_random_action_matches_in_kernel_agent(backend):
@@ -260,7 +262,7 @@ def test_action_dtypes_and_out_of_range(backend):
 
 
 # --------------------------------------------------------------------------------------------------- config 5: shaped env
-@pytest.mark.parametrize("name", ["shaped_5x5.npz", "shaped_7x7.npz"])
+@pytest.mark.parametrize("name", ["shaped_5x5.npz", "shaped_7x7.npz", "shaped_7x7_L4.npz"])
 def test_shaped_env_traces(backend, name):
     """envs/training_ewn.py:40-99 recorded from the reference (tolerance budget, delta-evaluate reward, resets)."""
     z = load(name)
@@ -369,9 +371,11 @@ def test_device_step_counter(backend):
     assert int(to_np(ctr)[0]) == 6
 
 
-@pytest.mark.parametrize("N,L", [(3, 1), (4, 1), (4, 2), (5, 1), (5, 2), (6, 3), (8, 3), (9, 3), (9, 1), (6, 2)])
+@pytest.mark.parametrize("N,L", [(3, 1), (4, 1), (4, 2), (5, 1), (5, 2), (6, 3), (8, 3), (9, 3), (9, 1), (6, 2), (6, 4), (7, 4), (7, 5), (8, 6), (9, 7),
+                                 (9, 4)])
 def test_every_supported_board_size(backend, N, L):
-    """3 <= board_size <= 9 with every cube_layer < board_size - 1 (envs/ewn.py:47): both codecs (one word up to 5x5, two words above),
+    """3 <= board_size <= 9 with cube_layer < board_size - 1 (envs/ewn.py:47) up to the maximum 7 (28 cubes per side): the three codecs
+    (one word up to 5x5, two words above, the generic byte-per-cube codec for cube_layer >= 4),
     the run-time-N kernel instantiations, VecEnv surface + generic surface, legal lists, and search / playouts where the reference
     allows them (six-face die: cube_layer 3)."""
     e = make_engine(backend, N, L)
@@ -403,7 +407,8 @@ def test_every_supported_board_size(backend, N, L):
         assert np.array_equal(to_np(w).astype(np.uint32), ow) and np.array_equal(to_np(nch), onch)
 
 
-@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz"])
+@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz", "random_games_7x7_L4.npz",
+                                  "random_games_9x9_L7.npz"])
 def test_eval_random_from_seeds_alone(backend, name):
     """ewn_numpy_random_games: the reference's eval_random.py games reproduced from the SEEDS (numpy legacy MT19937 + randint in
     the reference's consumption order) -- result, number of env.step calls, final board and the whole dice / action log (as a hash)

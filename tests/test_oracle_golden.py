@@ -27,7 +27,8 @@ def test_initial_layout_matches_reference_probe():
             assert c[0] == 3 and lst[0, :3].tolist() == [[0, 0], [0, 1], [0, 2]]
 
 
-@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz"])
+@pytest.mark.parametrize("name", ["random_games_5x5.npz", "random_games_7x7.npz", "random_games_4x4_L2.npz", "random_games_7x7_L4.npz",
+                                  "random_games_9x9_L7.npz"])
 def test_replay_reference_games(name):
     """Every env.step of the reference's eval_random loop: legal mask before, board/reward/flags after."""
     g = game_traces(name)
@@ -55,7 +56,7 @@ def test_replay_reference_games(name):
         assert (g["game_rewards"] > 0).sum() == 5215 and len(S) == 108978
 
 
-@pytest.mark.parametrize("name", ["rules_5x5.npz", "rules_7x7.npz"])
+@pytest.mark.parametrize("name", ["rules_5x5.npz", "rules_7x7.npz", "rules_6x6_L4.npz", "rules_7x7_L5.npz"])
 def test_rules_plies_and_heuristics(name):
     z = load(name)
     N, L = int(z["N"]), int(z["L"])
@@ -105,7 +106,7 @@ def test_expectiminimax_survey_probe_values():
         assert struct.pack(">d", v[0]).hex() == want7[d] and a[0].tolist() == [0, 2]
 
 
-@pytest.mark.parametrize("name", ["shaped_5x5.npz", "shaped_7x7.npz"])
+@pytest.mark.parametrize("name", ["shaped_5x5.npz", "shaped_7x7.npz", "shaped_7x7_L4.npz"])
 def test_shaped_env_traces(name):
     """envs/training_ewn.py:40-99 through the oracle's replay (tolerance budget, delta-evaluate reward)."""
     z = load(name)
