@@ -29,8 +29,12 @@ N_BOARD, N_LAYER = 5, 3
 N_SETS = 4
 SEED = 9487
 # algorithmic bytes per env step, 5x5 gym surface: state 8 R + 8 W, action int64x2 16 R, reward f32 4 W,
-# terminated + truncated 2 W, board int16[25] 50 W, dice int64 8 W.  Terminal-observation rows are extra, uncounted.
+# terminated + truncated 2 W, board int16[25] 50 W, dice int64 8 W.
 BYTES_PER_STEP = 8 + 8 + 16 + 4 + 2 + 50 + 8
+# ... plus, per FINISHED game, its compacted terminal observation (info["terminal_observation"] of the VecEnv contract):
+# board int16[25] 50 W, dice int64 8 W, env index int32 4 W.  Counted from the episodes that really finished in the timed steps.
+BYTES_PER_TERMINAL_ROW = 50 + 8 + 4
+BYTES_PER_STEP_AGENT_RANDOM = BYTES_PER_STEP - 16            # the in-kernel agent reads no action array
 
 
 def peaks():
@@ -107,13 +111,37 @@ def cpu_port_steps(n_envs, min_seconds, threads):
             return steps / el, t, el
 
 
+def reference_python(seconds=10.0):
+    """The reference's OWN Python (eval_random.py:17-51 loop, MctsAgent.simulate, ExpectiMinimaxAgent(4).predict), one process per
+    core.  Timed live when a reference tree travels with the repo (baseline/_ref, or EWN_REFERENCE_ROOT); otherwise the committed
+    measurement of the same script in the build container is quoted (profiles/r2_reference_python.json) and labelled as such --
+    /root/reference does not exist on the GPU box and bench.py never reads it."""
+    root = os.environ.get("EWN_REFERENCE_ROOT") or os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isfile(os.path.join(root, "envs", "ewn.py")):
+        os.environ["EWN_REFERENCE_ROOT"] = root
+        try:
+            from oracle import time_reference
+            out = time_reference.measure(seconds)
+            out["where"] = "this machine, live"
+            return out
+        except Exception as err:                                   # noqa: BLE001
+            return {"unavailable": f"reference at {root} failed to run: {err}"[:300]}
+    try:
+        out = json.load(open(os.path.join(ROOT, "profiles", "r2_reference_python.json")))
+        out["where"] = "build container, committed measurement (profiles/r2_reference_python.json): the pure-Python reference does not travel to the GPU box"
+        return out
+    except Exception:
+        return {"unavailable": "no reference tree on this machine and no committed measurement"}
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU algorithm for the same workload on the box's host cores (C port of the
-    pure-Python reference; the Python original cannot travel to the GPU box). Rank 0 only."""
+    """--impl reference: the reference's CPU algorithm for the same workload (same number of concurrent games) on the box's host
+    cores: the C restatement oracle/ewn_oracle.c ("port", ours) timed on all cores, with the reference's own Python quoted beside it
+    (`cpu_baseline.reference_python`).  Rank 0 only."""
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_s = 1 << 18
+    n_s = args.envs
     from oracle import oracle as O
     board, dice = O.reset_philox(n_s, SEED, 0)
     rng = np.random.default_rng(1)
@@ -130,8 +158,9 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "env_steps_per_sec", "value": v, "unit": "env steps/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": workload_config(args, n_s),
-            "cpu_baseline": {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port",
-                             "sample": f"{n_s} concurrent 5x5 games per step, uniform random actions, auto-reset, {args.steps} steps"},
+            "cpu_baseline": {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port", "label": "ours: oracle/ewn_oracle.c on all host threads",
+                             "sample": f"{n_s} concurrent 5x5 games per step, uniform random actions, auto-reset, {args.steps} steps",
+                             "reference_python": None if args.skip_reference_python else reference_python()},
             "e2e": {"value": v, "unit": "env steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -185,10 +214,23 @@ def run_ours(args, rank, world, local_rank):
         k = t // N_SETS
         sets[t % N_SETS]["plans"][k & 1].launch(k + 1)
 
+    # the same surface with the agent = uniform over its LEGAL list inside the kernel (first variant): games run
+    # to real wins and losses (captures, nearest-cube fallback, corner / elimination endings) instead of dying on illegal openings
+    stats_ar = torch.zeros(4, dtype=torch.int64, device=dev)
+    for s_i, S in enumerate(sets):
+        S["state_ar"] = e.reset(n, seed=SEED + 16 + s_i, step=0, env_id0=env_id0)
+        S["plans_ar"] = [e.step_plan(S["state_ar"], None, seed=SEED + 16 + s_i, step=0, env_id0=env_id0, autoreset=True, stats=stats_ar, want=want,
+                                     out=S["out"], agent_random=True, term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b])) for b in (0, 1)]
+
+    def one_step_ar(t):
+        k = t // N_SETS
+        sets[t % N_SETS]["plans_ar"][k & 1].launch(k + 1)
+
     t = 0
     for _ in range(max(args.warmup, 3)):
         one_step(t); t += 1
     torch.cuda.synchronize()
+    stats_before = stats.clone()
     if dist: dist.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = lib.ewn_launch_count()
@@ -204,6 +246,41 @@ def run_ours(args, rank, world, local_rank):
     if dist: dist.barrier()
     ms_step = ev0.elapsed_time(ev1) / args.steps
     kernel_ms = ms_step
+    finished_timed = int((stats - stats_before)[3].item())      # episodes that ended inside the timed steps of this rank
+    # ---- agent = uniform over the legal list: mid-game mix first (40 untimed steps: games are at every stage), then the same protocol
+    ar = None
+    if not args.skip_agent_random:
+        for S in sets:
+            S["cnt"].zero_()                           # the two phases share the append counters
+        ta = 0
+        for _ in range(40 * N_SETS + max(args.warmup, 3)):
+            one_step_ar(ta); ta += 1
+        torch.cuda.synchronize()
+        st0 = stats_ar.clone()
+        if dist: dist.barrier()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0.record()
+        for k in range(args.steps):
+            one_step_ar(ta); ta += 1
+        b1.record(); torch.cuda.synchronize()
+        ar_ms = b0.elapsed_time(b1) / args.steps
+        st_ar = stats_ar - st0
+        if dist:
+            tt = torch.tensor([ar_ms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ar_ms_max = float(tt.item())
+            dist.all_reduce(st_ar)
+        else:
+            ar_ms_max = ar_ms
+        sa = st_ar.cpu().tolist()
+        rows = sa[3] / (args.steps * world)
+        ar_bytes = BYTES_PER_STEP_AGENT_RANDOM * n + BYTES_PER_TERMINAL_ROW * rows
+        hbm_ar, _ = peaks()
+        ar = {"value": world * n / (ar_ms_max / 1e3), "unit": "env steps/s", "ms_per_step": ar_ms_max,
+              "config": {"agent": "uniform over legal list (in-kernel, random_policy.py:11-15 on Philox word 3)", "envs_per_gpu": n,
+                         "bytes_per_env_step": BYTES_PER_STEP_AGENT_RANDOM, "kernel": "k_vstep<P5,5,AR>"},
+              "episodes": {"agent_wins": sa[0], "agent_losses": sa[1], "illegal_endings": sa[2], "finished": sa[3], "steps_timed": args.steps},
+              "roofline": {"bound": "hbm", "achieved": ar_bytes / (ar_ms / 1e3) / 1e9, "peak": hbm_ar, "unit": "GB/s",
+                           "frac": ar_bytes / (ar_ms / 1e3) / 1e9 / hbm_ar, "algorithmic_bytes_per_launch": ar_bytes,
+                           "terminal_rows_per_launch": rows}}
     # the timed region is milliseconds long; keep the identical load running so that nvidia-smi (100 ms period) sees it
     t_end = time.perf_counter() + (0.0 if args.skip_clocks else max(0.0, 1.5 - wall))
     while time.perf_counter() < t_end:
@@ -285,6 +362,20 @@ def run_ours(args, rank, world, local_rank):
                              "nccl_allreduce_argmax_ms": nccl_ms, "identical_to_nccl": True}
                 dist.barrier(); ex.close()
             dist.all_reduce(plies)
+            # SURVEY 8d config 3 "1-vs-8-GPU counts identical": rank 0 replays a fixed sub-batch of the LAST timed decision alone -- all
+            # 1024 playouts of every root action, same Philox keys (root id, action, playout index) -- and the merged N-rank counters
+            # (tot_ref: the sum over ranks of 1024 / N playouts each) must equal them, or no line is printed
+            sub = 512
+            if rank == 0:
+                w1, _ = e.mc_root_wins(roots[:sub], seed=SEED + iters - 1, first=0, count=per * world)
+                bad = 0.0 if bool(torch.equal(w1, tot_ref[:sub])) else 1.0
+            else:
+                bad = 0.0
+            tt = torch.tensor([bad], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            if float(tt.item()):
+                raise SystemExit("Monte-Carlo win counts of the N-rank run differ from the single-rank run with the same Philox keys")
+            merge["identical_to_single_rank"] = True
+            merge["identity_check"] = f"rank 0 alone: {sub} roots x all actions x {per * world} playouts == merged counters of {world} ranks"
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
                    "playouts_per_child": 1024, "decisions_timed": iters, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
@@ -315,7 +406,17 @@ def run_ours(args, rank, world, local_rank):
             sizes[roots_n] = {"roots_per_s": roots_n / (ems / 1e3), "ms": ems}
             del roots, v, a
         emm = {"value": sizes[1 << 20]["roots_per_s"], "unit": "roots/s (depth 4, hybrid, pruned semantics)", "ms": sizes[1 << 20]["ms"],
-               "roots": 1 << 20, "per_gpu": True, "at_65536_roots": sizes[65536]}
+               "roots": 1 << 20, "per_gpu": True, "at_65536_roots": sizes[65536], "kernel": "k_emm_fused<P5,hybrid> (one launch, tree on chip)"}
+        try:    # on-chip kernel: bound by the SM issue rate; instructions per root from the committed ncu capture of this kernel
+            prof = json.load(open(os.path.join(ROOT, "profiles", "k_emm_issue.json")))
+            wi = prof["warp_instructions_per_root"] * emm["value"]
+            emm["roofline"] = {"bound": "issue", "achieved": wi, "peak": prof["issue_peak_warp_instructions_per_s"], "unit": "warp-instructions/s",
+                               "frac": wi / prof["issue_peak_warp_instructions_per_s"], "warp_instructions_per_root": prof["warp_instructions_per_root"],
+                               "alu_pipe_pct_ncu": prof["alu_pipe_pct"],
+                               "hbm": {"achieved_gbs": 18 * emm["value"] / 1e9, "algorithmic_bytes_per_root": 18,
+                                       "note": "8 B packed state in, 8 B value + 2 B action out; no node records leave the chip at depth 3 / 4"}}
+        except Exception:
+            pass
 
     # ---- secondary: configs[4], 7x7 MiniMaxHeuristicEnv rollout collection, 4096 envs x 128 steps over all ranks, counters all-reduced
     rollout = None
@@ -325,8 +426,12 @@ def run_ours(args, rank, world, local_rank):
         st7 = e7.reset(n7, seed=SEED + 3, env_id0=rank * n7)
         tol = torch.full((n7,), 10, dtype=torch.int32, device=dev)
         prev = e7.evaluate(st7, "hybrid")
-        pool = [torch.stack([torch.randint(0, 2, (n7,), generator=g, device=dev), torch.randint(0, 3, (n7,), generator=g, device=dev)], 1).contiguous()
-                for _ in range(8)]                 # policy stub (SB3 is not installed): uniform MultiDiscrete([2,3]) samples
+        # policy stub (SB3 is not installed): uniform MultiDiscrete([2,3]) samples.  The pool is a function of the GLOBAL env id (same
+        # generator on every rank, each rank takes its slice), so that the N-rank job plays the same games as one rank would
+        g7 = torch.Generator(device=dev); g7.manual_seed(4242)
+        pool_global = [torch.stack([torch.randint(0, 2, (n7 * world,), generator=g7, device=dev),
+                                    torch.randint(0, 3, (n7 * world,), generator=g7, device=dev)], 1).contiguous() for _ in range(8)]
+        pool = [p_[rank * n7:(rank + 1) * n7].contiguous() for p_ in pool_global]
         want7 = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice")
         out7 = {k: None for k in want7}
         st_roll = torch.zeros(4, dtype=torch.int64, device=dev)
@@ -381,6 +486,34 @@ def run_ours(args, rank, world, local_rank):
         rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
                                "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
 
+        def rollout_stats(lo, hi):                  # one rollout of the games with global ids [lo, hi) from a fresh reset -> stats[4]
+            m = hi - lo
+            st = e7.reset(m, seed=SEED + 5, env_id0=lo)
+            tl_, pv_ = torch.full((m,), 10, dtype=torch.int32, device=dev), None
+            pv_ = e7.evaluate(st, "hybrid")
+            acc = torch.zeros(4, dtype=torch.int64, device=dev)
+            chk = torch.zeros(1, dtype=torch.int64, device=dev)
+            for t in range(T):
+                o = e7.step(st, pool_global[t % 8][lo:hi].contiguous(), seed=SEED + 5, step=t + 1, env_id0=lo, shaped=True, illegal_move_reward=-1.0,
+                            tolerance=tl_, prev_score=pv_, stats=acc, want=("reward_f32", "terminated"))
+                chk += (o["reward_f32"].double() * 1024).round().long().sum() + o["terminated"].long().sum() * (t + 1)
+            return torch.cat([acc, chk])
+
+        if dist:
+            # env ids are global, so the N-rank rollout statistics (all-reduced) must equal the single-rank ones -- rank 0
+            # plays all 4,096 games alone and compares {wins, losses, illegal endings, episodes, reward/done checksum}
+            mine_ = rollout_stats(rank * n7, (rank + 1) * n7)
+            dist.all_reduce(mine_)
+            bad = 0.0
+            if rank == 0:
+                alone = rollout_stats(0, n7 * world)
+                bad = 0.0 if bool(torch.equal(alone, mine_)) else 1.0
+            tt = torch.tensor([bad], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            if float(tt.item()):
+                raise SystemExit("rollout statistics of the N-rank run differ from the single-rank run of the same games")
+            rollout["identical_to_single_rank"] = True
+            rollout["identity_check"] = f"rank 0 alone: {n7 * world} games x {T} steps == all-reduced stats + reward/done checksum of {world} ranks"
+
     # ---- e2e through the public host-buffer API (EWNVecEnv.step: pinned host actions in, host observations out), every rank at once
     from ewn_gym_b200.vec_env import EWNVecEnv
     e2e = None
@@ -401,7 +534,7 @@ def run_ours(args, rank, world, local_rank):
             t0 = time.perf_counter()
             obs, rew, done, infos = env.step(abuf)   # H2D actions + kernel + D2H obs/reward/done/terminal obs, synchronous
             tot += time.perf_counter() - t0
-            term_rows += int(env._b["tcount"].array[0])
+            term_rows += env.terminal_count
         if dist:                                     # whole job: all ranks step their own games over their own PCIe link; slowest rank counts
             tt = torch.tensor([tot], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); tot = float(tt.item())
         nn = N_BOARD * N_BOARD
@@ -412,6 +545,34 @@ def run_ours(args, rank, world, local_rank):
                        + ("results staged in HBM and copied back (D2H)" if args.e2e_staged else "results stored by the kernel straight into the page-locked host buffers over PCIe")
                        + "; PCIe-bound"}
         env.close()
+        # the ceiling of this line: page-locked D2H of the same bytes with a concurrent H2D of the actions, every rank at once (what the
+        # host side of the box moves when all its PCIe links are busy together)
+        d_bytes, h_bytes = int(e2e["d2h_bytes_per_step"] // world), int(e2e["h2d_bytes_per_step"] // world)
+        db, hb = torch.empty(d_bytes, dtype=torch.uint8, device=dev), torch.empty(d_bytes, dtype=torch.uint8).pin_memory()
+        db2, hb2 = torch.empty(h_bytes, dtype=torch.uint8, device=dev), torch.empty(h_bytes, dtype=torch.uint8).pin_memory()
+        s2 = torch.cuda.Stream(device=dev)
+        for _ in range(3):
+            hb.copy_(db, non_blocking=True)
+        torch.cuda.synchronize()
+        if dist: dist.barrier()
+        reps = 10
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            hb.copy_(db, non_blocking=True)
+            with torch.cuda.stream(s2):
+                db2.copy_(hb2, non_blocking=True)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / reps
+        if dist:
+            tt = torch.tensor([dt], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); dt = float(tt.item())
+        ceil_gbs = world * (d_bytes + h_bytes) / dt / 1e9
+        got_gbs = (e2e["d2h_bytes_per_step"] + e2e["h2d_bytes_per_step"]) / (e2e["ms_per_step"] / 1e3) / 1e9
+        e2e["host_ceiling_gbs"] = ceil_gbs
+        e2e["achieved_gbs"] = got_gbs
+        e2e["frac_of_ceiling"] = got_gbs / ceil_gbs
+        e2e["host_ceiling_note"] = (f"cudaMemcpyAsync of the step's {d_bytes} B D2H + {h_bytes} B H2D per rank between page-locked and device "
+                                    f"memory, {world} rank(s) concurrently, max over ranks")
+        del db, hb, db2, hb2
 
     # ---- the same step through the device-resident VecEnv class (CUDA tensors in and out: what a policy on the GPU calls)
     device_env = None
@@ -443,9 +604,16 @@ def run_ours(args, rank, world, local_rank):
         return
 
     hbm, peak_src = peaks()
-    achieved = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
+    rows_per_launch = finished_timed / args.steps
+    alg_bytes = BYTES_PER_STEP * n + BYTES_PER_TERMINAL_ROW * rows_per_launch
+    achieved = alg_bytes / (kernel_ms / 1e3) / 1e9
+    obs_only = BYTES_PER_STEP * n / (kernel_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": "k_vstep<P5,5>", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": BYTES_PER_STEP * n}
+                "traffic": None, "peak_source": peak_src, "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                "bytes": {"per_env_step": BYTES_PER_STEP, "per_terminal_row": BYTES_PER_TERMINAL_ROW, "terminal_rows_per_launch": rows_per_launch,
+                          "note": "96 B per env step (state R+W, action R, reward, flags, board, dice) + 62 B per finished game (its compacted "
+                                  "terminal observation: board, dice, env index), rows counted from the episodes that ended in the timed steps"},
+                "without_terminal_rows": {"achieved": obs_only, "frac": obs_only / hbm, "note": "round-1 accounting (96 B x games only)"}}
     prof = os.path.join(ROOT, "profiles", "k_step_traffic.json")
     if os.path.exists(prof):
         try:
@@ -455,15 +623,19 @@ def run_ours(args, rank, world, local_rank):
     cpu = None
     if not args.skip_cpu:
         cores = os.cpu_count() or 1
-        v, nsteps, el = cpu_port_steps(1 << 18, 10.0, cores)
-        cpu = {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port",
-               "sample": f"{1 << 18} concurrent 5x5 games x {nsteps} steps ({el:.1f} s) of oracle/ewn_oracle.c, uniform random actions, auto-reset"}
+        v, nsteps, el = cpu_port_steps(n, 10.0, cores)
+        cpu = {"value": v, "unit": "env steps/s", "cores": cores, "kind": "port", "label": "ours: oracle/ewn_oracle.c on all host threads",
+               "sample": f"{n} concurrent 5x5 games x {nsteps} steps ({el:.1f} s) of oracle/ewn_oracle.c, uniform random actions, auto-reset",
+               "reference_python": None if args.skip_reference_python else reference_python()}
     st = stats.cpu().tolist()
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env steps/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": roofline, "cpu_baseline": cpu, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout, "device_env": device_env,
-            "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3]},
+            "roofline": roofline, "cpu_baseline": cpu, "agent_uniform_legal": ar, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
+            "device_env": device_env,
+            "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3],
+                         "agent": "uniform over MultiDiscrete([2,3]) (host-supplied int64 actions; most games end on an illegal opening move -- "
+                                  "the in-kernel legal agent run is `agent_uniform_legal`)"},
             "wall_s_timed_region": wall}
     print(json.dumps(line), flush=True)
     if dist: dist.destroy_process_group()
@@ -477,6 +649,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=1 << 20, help="concurrent games per GPU")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-agent-random", action="store_true")
+    ap.add_argument("--skip-reference-python", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-playouts", action="store_true")
     ap.add_argument("--skip-search", action="store_true")

@@ -631,13 +631,14 @@ template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* ter
 }
 
 // asynchronous copy of one game's packed state and int64 action pair into the thread's 32-byte shared slot
-template <class C> __device__ __forceinline__ void prefetch_game(unsigned slot, const u64* state, const int64_t* action, int i) {
+template <class C, bool AR> __device__ __forceinline__ void prefetch_game(unsigned slot, const u64* state, const int64_t* action, int i) {
     if (C::WORDS == 1) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(slot), "l"(state + i) : "memory");
     else               asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot), "l"(state + 2 * (size_t)i) : "memory");
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + 16u), "l"(action + 2 * (size_t)i) : "memory");
+    if (!AR) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + 16u), "l"(action + 2 * (size_t)i) : "memory");
 }
 
-template <class C, int NT> __global__ void __launch_bounds__(VTPB, VMINB)
+// AR: the agent is the in-kernel uniform-over-the-legal-list player (random_policy.py:11-15, Philox word 3): no action array is read
+template <class C, int NT, bool AR> __global__ void __launch_bounds__(VTPB, VMINB)
 k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     extern __shared__ uint4 smem_raw[];
     __shared__ unsigned s_won, s_lost, s_row0, s_wcnt[VTPB / 32];
@@ -668,7 +669,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
         const int i0 = (int)blockIdx.x * VTPB + (int)tid;
         if (i0 < n) {                                  // the first unit only: all seven units measured slower (27.3 vs 26.5 us)
             if ((tid & 15u) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.state + (size_t)i0 * C::WORDS));
-            if ((tid & 7u) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.action_i64 + 2 * (size_t)i0));
+            if (!AR && (tid & 7u) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.action_i64 + 2 * (size_t)i0));
         }
     }
 #endif
@@ -684,7 +685,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     bool mine = i < n;
     // prefetch slot of this thread: state (8 / 16 B) + action (16 B), filled by cp.async while the previous unit is computed
     const unsigned pf = (unsigned)__cvta_generic_to_shared(s_pf) + tid * 32u;
-    if (mine) prefetch_game<C>(pf, a.state, a.action_i64, i);
+    if (mine) prefetch_game<C, AR>(pf, a.state, a.action_i64, i);
     const bool obs_vec = (reinterpret_cast<uintptr_t>(a.obs_board) & 15) == 0;
     unsigned tally_c = 0;                                          // wins | losses << 16 of this thread
     unsigned wcnt = 0;                                             // finished games of this warp so far (warp-uniform)
@@ -693,10 +694,11 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     while (u < n_units) {                                          // block-uniform
         asm volatile("cp.async.wait_all;" ::: "memory");
         const ulonglong2 sw = s_pf[2 * tid];                        // own slot: no cross-thread hazard
-        const longlong2 act = reinterpret_cast<const longlong2*>(s_pf)[2 * tid + 1];
+        longlong2 act = make_longlong2(0, 0);
+        if (!AR) act = reinterpret_cast<const longlong2*>(s_pf)[2 * tid + 1];
         const int un = u + (int)gridDim.x, in = un * VTPB + (int)tid;
         const bool mine_n = in < n;
-        if (mine_n) prefetch_game<C>(pf, a.state, a.action_i64, in);
+        if (mine_n) prefetch_game<C, AR>(pf, a.state, a.action_i64, in);
         Game<C> g, term;
         g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = 0; term = g;
         StepOut out; out.term = 0; out.code = CODE_ONGOING;
@@ -711,7 +713,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             { u32 blk[4]; env_block_rk(ka.p.rk, ka.p.env_id0 + (u64)i, step, TAG_STEP, blk);
               out.reward = 0.0; out.trunc = 0; g.dice = 1 + (int)bounded(blk[0] ^ blk[1] ^ blk[2] ^ blk[3] ^ (u32)(al + ad), 6u); }
 #else
-            step_one_cfg<C>(g, term, ka.p, geol, 0, 0, 0, step, i, al, ad, inj, &tol, &prev, out);
+            step_one_cfg<C>(g, term, ka.p, geol, 0, 0, AR ? 1 : 0, step, i, al, ad, inj, &tol, &prev, out);
 #endif
             pack(g, a.state, i);
             __stcs(a.reward_f32 + i, (float)out.reward);
@@ -1502,8 +1504,10 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     const unsigned grid = (unsigned)((a->n + STPB - 1) / STPB);
     const bool need_smem = a->obs_board || a->term_board;
     if (a->term_count && !a->term_index) return EWN_EARG;
-    const bool vec = a->action_i64 && a->reward_f32 && a->terminated && a->truncated && a->obs_board && a->obs_dice && !a->reward_f64 &&
-                     !a->code && !a->action_out && !a->agent_random && !replay && !a->shaped;
+    const bool vec_out = a->reward_f32 && a->terminated && a->truncated && a->obs_board && a->obs_dice && !a->reward_f64 && !a->code &&
+                         !a->action_out && !replay && !a->shaped;
+    const bool vec = vec_out && a->action_i64 && !a->agent_random;
+    const bool vec_ar = vec_out && a->agent_random;               // the same surface with the in-kernel random agent
 #define LAUNCH_STEP(C, NT)                                                                           \
     do {                                                                                             \
         size_t sm = need_smem ? step_smem(ka.p.geo) : 0;                                             \
@@ -1514,7 +1518,7 @@ int ewn_step(const ewn_step_args* a, void* stream) {
     const int N = a->board_size;
     // the VecEnv surface with compacted (or no) terminal observations runs on the persistent kernel
     const int codec = codec_of(N, a->cube_layer);
-    if (codec != 2 && vec && !(a->flags & EWN_STEP_BLOCK_KERNEL) && (a->term_count || (!a->term_board && !a->term_dice && !a->term_code)) && a->n < ((int64_t)1 << 30)) {
+    if (codec != 2 && (vec || vec_ar) && !(a->flags & EWN_STEP_BLOCK_KERNEL) && (a->term_count || (!a->term_board && !a->term_dice && !a->term_code)) && a->n < ((int64_t)1 << 30)) {
         const int64_t n_units = (a->n + VTPB - 1) / VTPB;
         int64_t blocks = (int64_t)sm_count() * VMINB;
         if (blocks > n_units) blocks = n_units;
@@ -1531,10 +1535,15 @@ int ewn_step(const ewn_step_args* a, void* stream) {
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = (a->flags & EWN_STEP_NO_PDL) ? 0 : 1;
         cudaError_t le;
-        if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5>, ka, cap);
-        else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0>, ka, cap);
-        else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7>, ka, cap);
-        else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0>, ka, cap);
+        if (vec_ar) {
+            if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5, true>, ka, cap);
+            else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0, true>, ka, cap);
+            else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7, true>, ka, cap);
+            else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0, true>, ka, cap);
+        } else if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5, false>, ka, cap);
+        else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0, false>, ka, cap);
+        else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7, false>, ka, cap);
+        else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0, false>, ka, cap);
         if (le != cudaSuccess) return cuda_fail(le, "k_vstep");
         LAUNCHED("k_vstep");
         return EWN_OK;
@@ -1629,7 +1638,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
         const size_t sm = heuristic == H_HYBRID ? (size_t)2 * (emm_pad(N) + emm_tab_entries(N)) * sizeof(double) : 0;
         const int pr = pruned & 1;
 #define LAUNCH_FUSED(C)                                                                                                     \
-    if (sm > 48 * 1024) CU(cudaFuncSetAttribute(k_emm_fused<C, H_HYBRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); /* 9x9 */ \
+    if (sm > 40 * 1024) CU(cudaFuncSetAttribute(k_emm_fused<C, H_HYBRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); /* 9x9: static + dynamic > 48 KB */ \
     switch (heuristic) {                                                                                                    \
         case H_HYBRID: k_emm_fused<C, H_HYBRID><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break; \
         case H_MIN_DIST: k_emm_fused<C, H_MIN_DIST><<<grid, FTPB, sm, st>>>(state, n, geo, depth, pr, tabs, value, action); break; \

@@ -14,10 +14,15 @@ the two classes produce identical observations, rewards, dones and terminal obse
 Contract details (envs/ewn.py:436-494, SB3 VecEnv):
   * finished games are reset inside the same call; `obs` then holds the new episode's first observation and the terminal
     observation is appended, compacted, to `infos.terminal_rows()` -> (env index int32[k], board int16[k,N,N], dice int64[k]);
-  * `infos[i]` builds the SB3 dict (`terminal_observation`, `TimeLimit.truncated`, `message`) on demand (one device read);
-  * returned tensors are owned by the env and overwritten by the next `step`;
+  * `infos[i]` builds the SB3 dict (`terminal_observation`, `TimeLimit.truncated`, `message`) on demand (one device read); the
+    message comes from the result code the kernel stored for the finished game, not from the reward's sign;
+  * the tensors a `step` returns stay valid across the NEXT `step` (two output sets alternate): SB3's `collect_rollouts` adds
+    `_last_obs` / `_last_episode_starts` to its buffer only after it has called `env.step()` again;
+  * `seed(s)` (train.py:135): from the next `reset()` on, game i draws from the Philox stream (key s, counter env_id0 + i);
+  * `opponent_policy` (envs/ewn.py:265-296): None / "random" = the in-kernel random opponent (one launch per step); "minimax",
+    "mcts" or any `arena.BatchPolicy` = the opponent's move comes from that policy on the flipped board, between the two plies;
   * `shaped=True` = `MiniMaxHeuristicEnv` (envs/training_ewn.py:40-99), `stats` = int64[4] {wins, losses, illegal endings, episodes}.
-One kernel launch per step, enqueued on torch's current stream; nothing synchronises unless the caller reads a value.
+Everything is enqueued on torch's current stream; nothing synchronises unless the caller reads a value.
 """
 from __future__ import annotations
 
@@ -25,15 +30,70 @@ from collections.abc import Sequence
 
 import numpy as np
 
-from .engine import Engine, MESSAGES, CODE_AGENT_ILLEGAL, CODE_AGENT_WON, CODE_AGENT_LOST
+from .constants import ClassicalPolicy
+from .engine import Engine, MESSAGES, CODE_AGENT_ILLEGAL, CODE_AGENT_WON, CODE_AGENT_LOST, CODE_OPP_ILLEGAL, BOTTOM_RIGHT, TOP_LEFT
 from .spaces import Box, Dict, Discrete, MultiDiscrete
+
+
+class EmptyInfos(Sequence):
+    """`reset_infos` of a VecEnv with n envs -- n empty dicts -- without building a million of them"""
+
+    def __init__(self, n):
+        self._n = int(n)
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [{} for _ in range(*i.indices(self._n))]
+        if not -self._n <= i < self._n:
+            raise IndexError(i)
+        return {}
+
+
+def seed_list(seed, n):
+    """what VecEnv.seed returns: the seed of every sub-environment, seed + i (None: unseeded)"""
+    if seed is None:
+        return [None] * n
+    r = range(int(seed), int(seed) + n)
+    return list(r) if n <= (1 << 16) else r              # a range is a Sequence too; a million-entry list helps nobody
+
+
+def code_from_flags(reward, truncated):
+    """Fallback when no result code was stored (terminal_observation=False): envs/ewn.py:445-478 by elimination on
+    (reward sign, truncated).  Ambiguous only for a goal reward of 0; envs with terminal observations never come here."""
+    if truncated:
+        return CODE_AGENT_ILLEGAL if reward < 0 else CODE_OPP_ILLEGAL
+    return CODE_AGENT_WON if reward > 0 else CODE_AGENT_LOST
+
+
+def resolve_opponent(opponent_policy, policy_kwargs):
+    """envs/ewn.py:265-287 load_opponent_policy for a batch: -> None (in-kernel random opponent) or an arena.BatchPolicy"""
+    from . import arena
+    if opponent_policy is None or isinstance(opponent_policy, arena.BatchPolicy):
+        return opponent_policy
+    if isinstance(opponent_policy, str):
+        opponent_policy = ClassicalPolicy.from_string(opponent_policy)
+    kw = dict(policy_kwargs or {})
+    if opponent_policy == ClassicalPolicy.random:
+        return None
+    if opponent_policy == ClassicalPolicy.minimax:
+        return arena.MinimaxPolicy(int(kw.get("max_depth", 3)), kw.get("heuristic", "hybrid"))
+    if opponent_policy == ClassicalPolicy.mcts:
+        return arena.MonteCarloPolicy(int(kw.get("num_simulations", 10)), int(kw.get("num_env_copies", 5)), seed=int(kw.get("seed", 0)))
+    raise NotImplementedError(f"opponent_policy {opponent_policy!r}: AlphaZero / SB3-checkpoint opponents are out of scope (DESIGN.md 9)")
+
+
+def _host(x):
+    return x.cpu().numpy() if hasattr(x, "cpu") else np.asarray(x)
 
 
 class DeviceInfos(Sequence):
     """`infos` of a device step.  Stays on the GPU until somebody asks for an entry."""
 
-    def __init__(self, env, count, index, board, dice, done, trunc, reward):
-        self._env, self._count, self._index, self._board, self._dice = env, count, index, board, dice
+    def __init__(self, env, count, index, board, dice, code, done, trunc, reward):
+        self._env, self._count, self._index, self._board, self._dice, self._code = env, count, index, board, dice, code
         self._done, self._trunc, self._reward = done, trunc, reward
         self._host = None
 
@@ -51,14 +111,20 @@ class DeviceInfos(Sequence):
         k = self.terminal_count()
         return self._index[:k], self._board[:k], self._dice[:k]
 
+    def terminal_codes(self):
+        """EWN_CODE_* uint8[k] of the rows of terminal_rows()"""
+        if self._count is None:
+            raise RuntimeError("the env was created with terminal_observation=False")
+        return self._code[: self.terminal_count()]
+
     def _pull(self):
         if self._host is None:
-            done, trunc, rew = (x.cpu().numpy() for x in (self._done, self._trunc, self._reward))
+            done, trunc, rew = (_host(x) for x in (self._done, self._trunc, self._reward))
             rows = {}
             if self._count is not None:
-                idx, b, d = (x.cpu().numpy() for x in self.terminal_rows())
+                idx, b, d = (_host(x) for x in self.terminal_rows())
                 rows = {int(i): k for k, i in enumerate(idx)}
-                self._tb, self._td = b, d
+                self._tb, self._td, self._tc = b, d, _host(self.terminal_codes())
             self._host = (done, trunc, rew, rows)
         return self._host
 
@@ -70,16 +136,11 @@ class DeviceInfos(Sequence):
         done, trunc, rew, rows = self._pull()
         if not done[i]:
             return {}
-        r = float(rew[i])
-        if trunc[i]:
-            code = CODE_AGENT_ILLEGAL if r < 0 else 3
-        else:
-            code = CODE_AGENT_WON if r > 0 else CODE_AGENT_LOST
-        info = {"message": MESSAGES[code], "TimeLimit.truncated": False}
         if i in rows:
             k = rows[i]
-            info["terminal_observation"] = {"board": self._tb[k].copy(), "dice_roll": int(self._td[k])}
-        return info
+            return {"message": MESSAGES[int(self._tc[k])], "TimeLimit.truncated": False,
+                    "terminal_observation": {"board": self._tb[k].copy(), "dice_roll": int(self._td[k])}}
+        return {"message": MESSAGES[code_from_flags(float(rew[i]), bool(trunc[i]))], "TimeLimit.truncated": False}
 
 
 class EWNDeviceVecEnv:
@@ -87,17 +148,19 @@ class EWNDeviceVecEnv:
 
     def __init__(self, num_envs: int, board_size: int = 5, cube_layer: int = 3, seed: int = 9487, reward: float = 1.0,
                  shaped: bool = False, illegal_move_reward: float = -1.0, illegal_move_tolerance: int = 10, device=None,
-                 env_id0: int = 0, terminal_observation: bool = True, engine: Engine = None, **_ignored):
+                 env_id0: int = 0, terminal_observation: bool = True, engine: Engine = None, opponent_policy=None, **policy_kwargs):
         assert cube_layer < board_size - 1
         self.e = engine if engine is not None else Engine(board_size, cube_layer, device=device)
         xp = self.e.xp
-        self.torch = xp.torch
+        self.torch = getattr(xp, "torch", None)
         self.num_envs, self.board_size, self.cube_layer = int(num_envs), int(board_size), int(cube_layer)
         self.cube_num = cube_layer * (cube_layer + 1) // 2
         self.shaped = bool(shaped)
         self.reward = 1.0 if shaped else float(reward)             # MinimaxEnv drops goal_reward (envs/minimax_ewn.py:17-19)
         self.illegal_move_reward, self.illegal_move_tolerance = float(illegal_move_reward), int(illegal_move_tolerance)
         self.seed_value, self.env_id0 = int(seed), int(env_id0)
+        self._next_seed = None
+        self.opponent = resolve_opponent(opponent_policy, policy_kwargs)
         self.action_space = MultiDiscrete([2, 3])
         self.observation_space = Dict({
             "board": Box(low=-self.cube_num, high=self.cube_num, shape=(board_size, board_size), dtype=np.int16),
@@ -108,77 +171,117 @@ class EWNDeviceVecEnv:
         self._t = 0
         self.stats = xp.zeros((4,), "i64")
         self._action = xp.zeros((n, 2), "i64")
-        self._out = {"reward_f32": xp.empty((n,), "f32"), "terminated": xp.empty((n,), "u8"), "truncated": xp.empty((n,), "u8"),
-                     "obs_board": xp.empty((n, N, N), "i16"), "obs_dice": xp.empty((n,), "i64")}
         self._want_term = bool(terminal_observation)
+        # two output sets alternate by step parity: what step t returned is still intact after step t + 1
+        self._outs = []
+        for _ in (0, 1):
+            o = {"reward_f32": xp.empty((n,), "f32"), "terminated": xp.empty((n,), "u8"), "truncated": xp.empty((n,), "u8"),
+                 "obs_board": xp.empty((n, N, N), "i16"), "obs_dice": xp.empty((n,), "i64")}
+            if self._want_term:
+                o["term_board"], o["term_dice"], o["term_code"] = xp.empty((n, N, N), "i16"), xp.empty((n,), "i64"), xp.empty((n,), "u8")
+            self._outs.append(o)
         if self._want_term:
-            self._out["term_board"] = xp.empty((n, N, N), "i16")
-            self._out["term_dice"] = xp.empty((n,), "i64")
             self._cnt = xp.zeros((2,), "i32")
-            self._tidx = xp.empty((n,), "i32")
+            self._tidx = [xp.empty((n,), "i32"), xp.empty((n,), "i32")]
         if self.shaped:
             self._tol = xp.empty((n,), "i32")
             self._prev = xp.empty((n,), "f64")
+        if self.opponent is not None:
+            self._br = xp.asarray(np.full(n, BOTTOM_RIGHT, np.int32), "i32")
         self._plans = None
         self._pending = False
+        self._last = 0                                              # output set of the latest reset / step
         self.render_mode = None
-        self.reset_infos = [{} for _ in range(min(n, 1))]
+        self.reset_infos = EmptyInfos(n)
 
     # ------------------------------------------------------------------ VecEnv API
-    def _obs(self):
-        return {"board": self._out["obs_board"], "dice_roll": self._out["obs_dice"]}
+    def _obs(self, b):
+        return {"board": self._outs[b]["obs_board"], "dice_roll": self._outs[b]["obs_dice"]}
+
+    def _copy_into(self, dst, src):
+        if self.torch is not None:
+            dst.copy_(src)
+        else:
+            np.copyto(dst, src)
 
     def reset(self):
         e, n = self.e, self.num_envs
+        if self._next_seed is not None:                             # VecEnv.seed(): takes effect here (train.py:135-136)
+            self.seed_value, self._next_seed = int(self._next_seed), None
+            self._plans = None
         fresh = e.reset(n, seed=self.seed_value, step=self._t, env_id0=self.env_id0)
         if self.state is None:
             self.state = fresh
             if self.shaped:                                         # training_ewn.py:35-38: set once, at construction
-                self._tol.fill_(self.illegal_move_tolerance)
-                self._prev.copy_(e.evaluate(self.state))
-            self._bind()
+                self._tol[...] = self.illegal_move_tolerance
+                self._copy_into(self._prev, e.evaluate(self.state))
         else:
-            self.state.copy_(fresh)                                 # the pre-bound launches keep pointing at self.state
+            self._copy_into(self.state, fresh)                      # the pre-bound launches keep pointing at self.state
+        if self._plans is None and self.opponent is None:
+            self._bind()
         if self._want_term:
-            self._cnt.zero_()                                       # a reset shifts the step parity: no counter may carry a count over
-        b, d = e.decode(self.state)
-        self._out["obs_board"].copy_(b)
-        self._out["obs_dice"].copy_(d)
+            self._cnt[...] = 0                                      # a reset shifts the step parity: no counter may carry a count over
+        b = self._t & 1
+        bd, dc = e.decode(self.state)
+        self._copy_into(self._outs[b]["obs_board"], bd)
+        self._copy_into(self._outs[b]["obs_dice"], dc)
         self._t += 1
-        return self._obs()
+        self._last = b
+        return self._obs(b)
 
-    def _bind(self):
+    def _step_kw(self, b):
         kw = dict(seed=self.seed_value, step=0, env_id0=self.env_id0, reward=self.reward, autoreset=True, shaped=self.shaped,
-                  illegal_move_reward=self.illegal_move_reward, stats=self.stats, want=tuple(self._out), out=self._out)
+                  illegal_move_reward=self.illegal_move_reward, stats=self.stats, want=tuple(self._outs[b]), out=self._outs[b])
         if self.shaped:
             kw.update(tolerance=self._tol, prev_score=self._prev)
         if self._want_term:                                         # two append counters alternate; a launch clears the other one
-            self._plans = [self.e.step_plan(self.state, self._action, term_compact=(self._cnt[b:b + 1], self._tidx, self._cnt[1 - b:2 - b]), **kw)
-                           for b in (0, 1)]
-        else:
-            self._plans = [self.e.step_plan(self.state, self._action, **kw)] * 2
+            kw["term_compact"] = (self._cnt[b:b + 1], self._tidx[b], self._cnt[1 - b:2 - b])
+        return kw
+
+    def _bind(self):
+        self._plans = [self.e.step_plan(self.state, self._action, **self._step_kw(b)) for b in (0, 1)]
 
     def step_async(self, actions):
         if self.state is None:
             raise RuntimeError("reset() first")
         a = self._action
         if actions is not a:
-            a.copy_(self.torch.as_tensor(actions, device=a.device).reshape(self.num_envs, 2))
+            if self.torch is not None:
+                a.copy_(self.torch.as_tensor(actions, device=a.device).reshape(self.num_envs, 2))
+            else:
+                np.copyto(a, np.asarray(actions).reshape(self.num_envs, 2), casting="unsafe")
         self._pending = True
+
+    def _step_external(self, b):
+        """envs/ewn.py:436-486 with a policy as opponent: its answer is computed between the two plies on the flipped board
+        (:289-296) and handed to the step kernel in replay mode together with the very dice the fused step would have drawn."""
+        e, n, t = self.e, self.num_envs, self._t
+        d_opp, d_next = e.step_dice(n, self.seed_value, t, self.env_id0)
+        peek = self.state.clone() if self.torch is not None else self.state.copy()
+        e.ply(peek, e.xp.asarray(self._action, "i32"), TOP_LEFT)     # the agent's ply on a copy (:439-442)
+        e.set_dice(peek, d_opp, self._br)                           # :457-458 switch_player + roll_dice
+        opp = self.opponent.action(e, e.flip(peek), t)              # :289-296; ignored by the kernel where the game ended at the agent's ply
+        kw = self._step_kw(b)
+        kw["step"] = t
+        e.step(self.state, self._action, inject=(d_opp, opp, d_next), **kw)
 
     def step_wait(self):
         assert self._pending, "step_async first"
         self._pending = False
         b = self._t & 1
-        self._plans[b].stream = self.e.xp.stream()                 # torch's current stream, not the one reset() saw
-        self._plans[b].launch(self._t)
+        if self.opponent is None:
+            self._plans[b].stream = self.e.xp.stream()             # torch's current stream, not the one reset() saw
+            self._plans[b].launch(self._t)
+        else:
+            self._step_external(b)
         self._t += 1
-        o = self._out
-        done = o["terminated"].view(self.torch.bool)
-        cnt = self._cnt[b:b + 1] if self._want_term else None
-        infos = DeviceInfos(self, cnt, self._tidx if self._want_term else None, o.get("term_board"), o.get("term_dice"), done, o["truncated"],
-                            o["reward_f32"])
-        return self._obs(), o["reward_f32"], done, infos
+        self._last = b
+        o = self._outs[b]
+        done = o["terminated"].view(self.torch.bool) if self.torch is not None else o["terminated"].view(np.bool_)
+        T = self._want_term
+        infos = DeviceInfos(self, self._cnt[b:b + 1] if T else None, self._tidx[b] if T else None, o.get("term_board"), o.get("term_dice"),
+                            o.get("term_code"), done, o["truncated"], o["reward_f32"])
+        return self._obs(b), o["reward_f32"], done, infos
 
     def step(self, actions):
         self.step_async(actions)
@@ -190,7 +293,11 @@ class EWNDeviceVecEnv:
         return self._action
 
     def seed(self, seed=None):
-        return [None if seed is None else seed + i for i in range(min(self.num_envs, 1))]
+        """SB3 VecEnv.seed (train.py:135): sub-environment i is seeded with seed + i at the next reset().  Here every game already
+        owns a Philox stream (key, env_id0 + i), so the key becomes `seed` at the next reset(); returns the per-env seeds."""
+        if seed is not None:
+            self._next_seed = int(seed)
+        return seed_list(seed, self.num_envs)
 
     def close(self):
         self._plans = None
@@ -202,7 +309,24 @@ class EWNDeviceVecEnv:
         setattr(self, name, value)
 
     def env_method(self, method_name, *args, indices=None, **kwargs):
-        raise NotImplementedError("games live in one packed device array; there is no per-env Python object")
+        """Per-env Python objects do not exist (the games are one packed array); the methods of the reference env that read a game
+        are served from the batch: get_legal_actions / check_win / evaluate -> one result per selected env."""
+        idx = list(self._indices(indices))
+        e = self.e
+        sel = self.state[idx] if self.torch is None else self.state[self.torch.as_tensor(idx, device=self.state.device)]
+        host = (lambda x: x.cpu().numpy()) if self.torch is not None else np.asarray
+        if method_name == "check_win":
+            return [bool(v) for v in host(e.check_win(sel))]
+        if method_name == "evaluate":
+            return [float(v) for v in host(e.evaluate(sel, kwargs.get("heuristic", args[0] if args else "hybrid")))]
+        if method_name == "get_legal_actions":
+            player = args[0] if args else kwargs.get("player", TOP_LEFT)
+            player = getattr(player, "value", player)
+            _, lst, cnt = e.legal(sel, int(player))
+            lst, cnt = host(lst), host(cnt)
+            return [[list(map(int, a)) for a in lst[i, : cnt[i]]] for i in range(len(idx))]
+        raise NotImplementedError(f"env_method({method_name!r}): games live in one packed device array; available: "
+                                  "check_win, evaluate, get_legal_actions")
 
     def env_is_wrapped(self, wrapper_class, indices=None):
         return [False] * len(self._indices(indices))

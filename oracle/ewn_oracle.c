@@ -9,7 +9,7 @@
  *
  * Parity pinning: this file is validated against golden vectors produced by running the UNMODIFIED
  * reference in the build container (tests/golden/make_golden.py -> tests/golden/ *.npz) and, when
- * /root/reference is present, against the live reference (tests/test_oracle_vs_reference.py).
+ * /root/reference is present, against the live reference (tests/test_oracle_vs_reference.py: marker `reference`).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
  * this library.  The product package (ewn_gym_b200) never does.
@@ -42,6 +42,14 @@ typedef struct {
     int8_t alive[2][ORC_MAXC];             /* !mask */
 } orc_game;
 
+/* an empty game of this configuration: only what the configuration uses is cleared (the piece-list arrays are sized for 28 cubes,
+ * the common six-cube games should not pay for that) */
+static void g_clear(orc_game *g, int N, int L) {
+    g->N = N; g->L = L; g->cube_num = L * (L + 1) / 2;
+    memset(g->board, 0, sizeof(int16_t) * (size_t)(N * N));
+    for (int s = 0; s < 2; s++) { memset(g->alive[s], 0, (size_t)g->cube_num); memset(g->px[s], 0, (size_t)g->cube_num); memset(g->py[s], 0, (size_t)g->cube_num); }
+}
+
 static inline int side_of(int player) { return player == TOP_LEFT ? 0 : 1; }
 static inline int opponent_of(int player) { return player == TOP_LEFT ? BOTTOM_RIGHT : TOP_LEFT; } /* constants/player.py:10-17 */
 
@@ -51,8 +59,7 @@ static inline int opponent_of(int player) { return player == TOP_LEFT ? BOTTOM_R
 
 /* envs/ewn.py:94-107 setup_game (without the trailing roll_dice) */
 static void g_setup(orc_game *g, int N, int L) {
-    memset(g, 0, sizeof(*g));
-    g->N = N; g->L = L; g->cube_num = L * (L + 1) / 2;
+    g_clear(g, N, L);
     g->dice = 1; g->player = TOP_LEFT;
     int cnt = 1;
     for (int i = 1; i <= L; i++) {
@@ -70,8 +77,7 @@ static void g_setup(orc_game *g, int N, int L) {
 
 /* classical_policies/minimax.py:75-87 restore_env_with_obs: piece list rebuilt by scanning the board */
 static void g_from_board(orc_game *g, int N, int L, const int16_t *board, int dice, int player) {
-    memset(g, 0, sizeof(*g));
-    g->N = N; g->L = L; g->cube_num = L * (L + 1) / 2;
+    g_clear(g, N, L);
     g->dice = dice; g->player = player;
     for (int i = 0; i < N; i++)
         for (int j = 0; j < N; j++) {

@@ -8,7 +8,8 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("N,L,shaped,staged", [(5, 3, False, False), (5, 3, False, True), (7, 3, False, False), (7, 3, True, False),
-                                               (5, 3, True, False), (4, 2, False, False)])
+                                               (5, 3, True, False), (4, 2, False, False), (7, 4, False, False), (6, 4, True, False),
+                                               (9, 7, False, True)])
 def test_vec_env_matches_oracle(N, L, shaped, staged):
     """staged = outputs through device staging arrays + D2H copies; default = the kernel writes the page-locked host buffers directly"""
     from ewn_gym_b200.vec_env import EWNVecEnv
@@ -48,6 +49,66 @@ def test_vec_env_matches_oracle(N, L, shaped, staged):
             tol, prev = ref["tolerance"], ref["prev_score"]
     assert seen_done > n // 2
     env.close()
+
+
+def test_host_env_contract_buffers_seed_codes():
+    """the VecEnv contract on the host-buffer class: outputs of step t intact after step t + 1, seed() effective at the next reset
+    and returning seed + i per env, reset_infos of length num_envs, messages from the stored result code (goal reward 0)"""
+    from ewn_gym_b200.vec_env import EWNVecEnv
+    N, L, n, id0 = 5, 3, 5000, 9
+    env = EWNVecEnv(n, N, L, seed=1, reward=0.0, env_id0=id0, chunks=3)
+    assert len(env.reset_infos) == n and env.reset_infos[n - 1] == {}
+    rng = np.random.default_rng(0)
+    mk = lambda: np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+    obs0 = env.reset()
+    keep0 = obs0["board"].copy()
+    obs1, rew1, done1, infos1 = env.step(mk())
+    assert np.array_equal(obs0["board"], keep0)
+    keep1 = (obs1["board"].copy(), obs1["dice_roll"].copy(), done1.copy())
+    env.step(mk())
+    assert np.array_equal(obs1["board"], keep1[0]) and np.array_equal(obs1["dice_roll"], keep1[1]) and np.array_equal(done1, keep1[2])
+    assert list(env.seed(4242)) == list(range(4242, 4242 + n))
+    obs = env.reset()                                               # fourth call: RESET block of step index 3
+    ob, od = O.reset_philox(n, 4242, 3, id0, N, L)
+    assert np.array_equal(obs["board"], ob) and np.array_equal(obs["dice_roll"], od)
+    want = {O.CODE_AGENT_ILLEGAL: "Invalid move for player! End the game.", O.CODE_AGENT_WON: "You won!", O.CODE_AGENT_LOST: "You lost!"}
+    seen = set()
+    for t in range(4, 30):
+        a = mk()
+        _, lst, cnt = O.legal(ob, od, 1, N, L)
+        rows = rng.random(n) < 0.9
+        a[rows] = lst[np.arange(n), rng.integers(0, 1 << 30, n) % cnt][rows]
+        obs, rew, done, infos = env.step(a)
+        ref = O.step_philox(ob, od, a, 4242, t, id0, N, L, reward=0.0)
+        assert np.array_equal(obs["board"], ref["board"]) and not rew.any()
+        for i in np.flatnonzero(done)[:30]:
+            assert infos[int(i)]["message"] == want[int(ref["code"][i])]
+            seen.add(int(ref["code"][i]))
+        ob, od = ref["board"], ref["dice"]
+    assert seen == set(want)
+    la = env.env_method("get_legal_actions", 1, indices=[0, 7])
+    _, lst, cnt = O.legal(ob[[0, 7]], od[[0, 7]], 1, N, L)
+    assert la == [lst[k, : cnt[k]].tolist() for k in range(2)]
+    env.close()
+
+
+def test_host_env_with_minimax_opponent_equals_device_env():
+    """opponent_policy on the host-buffer class is served by the device class: same games"""
+    import torch
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.vec_env import EWNVecEnv
+    n = 512
+    kw = dict(board_size=5, cube_layer=3, seed=3, env_id0=5, opponent_policy="minimax", max_depth=2)
+    host, devv = EWNVecEnv(n, **kw), EWNDeviceVecEnv(n, **kw)
+    oh, od = host.reset(), devv.reset()
+    assert np.array_equal(oh["board"], od["board"].cpu().numpy())
+    rng = np.random.default_rng(2)
+    for t in range(20):
+        a = np.stack([rng.integers(0, 2, n), rng.integers(0, 3, n)], 1).astype(np.int64)
+        oh, rh, dh, ih = host.step(a)
+        od, rd, dd, idv = devv.step(torch.from_numpy(a).cuda())
+        assert np.array_equal(oh["board"], od["board"].cpu().numpy()) and np.array_equal(rh, rd.cpu().numpy()) and np.array_equal(dh, dd.cpu().numpy())
+    host.close(); devv.close()
 
 
 def test_vec_env_surface():
@@ -101,6 +162,43 @@ def test_persistent_step_kernel_vs_block_kernel_and_oracle(N, L, n):
     assert torch.equal(stats_a, stats_b) and int(stats_a[3].item()) > 0
 
 
+@pytest.mark.parametrize("N,L,n", [(5, 3, 200_000 + 33), (7, 3, 70_001)])
+def test_persistent_kernel_with_in_kernel_random_agent(N, L, n):
+    """k_vstep<AR>: the VecEnv surface with the agent = uniform over its legal list inside the kernel (no action array), against the
+    block kernel and the oracle; result codes of the finished games (term_code) included"""
+    import torch
+    from ewn_gym_b200.engine import Engine
+    e = Engine(N, L)
+    seed, env_id0 = 77, 123456
+    want = ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice", "term_board", "term_dice", "term_code")
+    sa, sb = e.reset(n, seed=seed, env_id0=env_id0), e.reset(n, seed=seed, env_id0=env_id0)
+    m = min(n, 3000)
+    ob, od = (x.cpu().numpy()[:m].copy() for x in e.decode(sa))
+    wins = 0
+    for t in range(1, 30):
+        ca, cb = torch.zeros(1, dtype=torch.int32, device="cuda"), torch.zeros(1, dtype=torch.int32, device="cuda")
+        ia, ib = torch.empty(n, dtype=torch.int32, device="cuda"), torch.empty(n, dtype=torch.int32, device="cuda")
+        ra = e.step(sa, None, seed=seed, step=t, env_id0=env_id0, agent_random=True, term_compact=(ca, ia), want=want)
+        rb = e.step(sb, None, seed=seed, step=t, env_id0=env_id0, agent_random=True, term_compact=(cb, ib), want=want, block_kernel=True)
+        assert torch.equal(sa, sb), t
+        for k in ("reward_f32", "terminated", "truncated", "obs_board", "obs_dice"):
+            assert torch.equal(ra[k], rb[k]), (t, k)
+        F = int(ca.item())
+        assert F == int(cb.item()) == int(ra["terminated"].sum().item())
+        pa, pb = torch.argsort(ia[:F]), torch.argsort(ib[:F])
+        assert torch.equal(ia[:F][pa], ib[:F][pb])
+        for k in ("term_board", "term_dice", "term_code"):
+            assert torch.equal(ra[k][:F][pa], rb[k][:F][pb]), (t, k)
+        ref = O.step_philox(ob, od, None, seed, t, env_id0, N, L, reward=1.0, autoreset=True, agent_random=True, threads=4)
+        assert np.array_equal(ra["obs_board"][:m].cpu().numpy(), ref["board"]) and np.array_equal(ra["obs_dice"][:m].cpu().numpy(), ref["dice"])
+        sel = (ia[:F][pa] < m).cpu().numpy()
+        assert np.array_equal(ra["term_code"][:F][pa].cpu().numpy()[sel], ref["code"][ref["terminated"] == 1])
+        assert not ra["truncated"].any()                              # a legal-list agent never makes an illegal move
+        wins += int((ref["code"] == O.CODE_AGENT_WON).sum())
+        ob, od = ref["board"], ref["dice"]
+    assert wins > 100
+
+
 def test_full_size_properties_1mi_games():
     """BASELINE.json configs[1] at full size (1,048,576 games): properties that do not need the oracle -- every board holds each
     cube number at most once and only in range, finished games were reset to the initial layout, the compacted terminal list has
@@ -152,7 +250,8 @@ def test_full_size_properties_1mi_games():
 
 
 
-@pytest.mark.parametrize("N,L,shaped,term", [(5, 3, False, True), (5, 3, True, True), (7, 3, True, True), (6, 3, False, False)])
+@pytest.mark.parametrize("N,L,shaped,term", [(5, 3, False, True), (5, 3, True, True), (7, 3, True, True), (6, 3, False, False), (7, 4, False, True),
+                                             (8, 5, True, True)])
 def test_device_env_equals_host_env(N, L, shaped, term):
     """EWNDeviceVecEnv (tensors stay in HBM) and EWNVecEnv (host buffers) are the same environment"""
     import torch
@@ -196,6 +295,6 @@ def test_device_env_equals_host_env(N, L, shaped, term):
         assert np.array_equal(oh["board"], od["board"].cpu().numpy()) and np.array_equal(rh, rd.cpu().numpy())
         assert idv.terminal_count() == int(dh.sum())                # the append counters start from zero after a reset
         if term:
-            assert int(host._b["tcount"].array[0]) == int(dh.sum())
+            assert host.terminal_count == int(dh.sum())
     finally:
         host.close(); devv.close()
