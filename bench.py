@@ -248,7 +248,7 @@ def run_ours(args, rank, world, local_rank):
     kernel_ms = ms_step
     finished_timed = int((stats - stats_before)[3].item())      # episodes that ended inside the timed steps of this rank
     # ---- agent = uniform over the legal list: mid-game mix first (40 untimed steps: games are at every stage), then the same protocol
-    ar = None
+    ar_run = None
     if not args.skip_agent_random:
         for S in sets:
             S["cnt"].zero_()                           # the two phases share the append counters
@@ -274,7 +274,7 @@ def run_ours(args, rank, world, local_rank):
         rows = sa[3] / (args.steps * world)
         ar_bytes = BYTES_PER_STEP_AGENT_RANDOM * n + BYTES_PER_TERMINAL_ROW * rows
         hbm_ar, _ = peaks()
-        ar = {"value": world * n / (ar_ms_max / 1e3), "unit": "env steps/s", "ms_per_step": ar_ms_max,
+        ar_run = {"value": world * n / (ar_ms_max / 1e3), "unit": "env steps/s", "ms_per_step": ar_ms_max,
               "config": {"agent": "uniform over legal list (in-kernel, random_policy.py:11-15 on Philox word 3)", "envs_per_gpu": n,
                          "bytes_per_env_step": BYTES_PER_STEP_AGENT_RANDOM, "kernel": "k_vstep<P5,5,AR>"},
               "episodes": {"agent_wins": sa[0], "agent_losses": sa[1], "illegal_endings": sa[2], "finished": sa[3], "steps_timed": args.steps},
@@ -631,7 +631,7 @@ def run_ours(args, rank, world, local_rank):
     line = {"metric": "env_steps_per_sec", "value": value, "unit": "env steps/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": roofline, "cpu_baseline": cpu, "agent_uniform_legal": ar, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
+            "roofline": roofline, "cpu_baseline": cpu, "agent_uniform_legal": ar_run, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
             "device_env": device_env,
             "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3],
                          "agent": "uniform over MultiDiscrete([2,3]) (host-supplied int64 actions; most games end on an illegal opening move -- "

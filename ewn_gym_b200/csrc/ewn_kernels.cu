@@ -523,11 +523,14 @@ k_step(const __grid_constant__ StepKArgs ka) {
 //     shared atomic per warp; after the loop the block reserves its rows of the compacted terminal-observation arrays
 //     with ONE global atomic and all threads decode the boards together, one (game, cube) pair per thread.
 // ------------------------------------------------------------------------------------------------
+// 128-thread blocks x 10 per SM = 40 resident warps at 48 registers: measured best on B200 (profiles/r2_k1_sweeps.txt: 26.0 us per
+// 1 Mi games against 26.6 for 32 x 32 = 32 warps at 60 registers, 26.1 for 64 x 20, 26.2 for 256 x 5; 48 warps need 40 registers,
+// which spills inside the loop: 27.6).  An SM holds at most 32 blocks, so one-warp blocks cannot go beyond 32 warps.
 #ifndef EWN_VTPB
-#define EWN_VTPB 32
+#define EWN_VTPB 128
 #endif
 #ifndef EWN_VMINB
-#define EWN_VMINB 32
+#define EWN_VMINB 10
 #endif
 #ifndef EWN_VITER_MAX
 #define EWN_VITER_MAX 8
@@ -573,6 +576,16 @@ template <class C, int NT> __device__ __forceinline__ void scatter_row(const Gam
 #endif
 #ifndef EWN_VPRE
 #define EWN_VPRE 1
+#endif
+// EWN_VSTAG = 1: every block (one warp: EWN_VTPB == 32) also flushes the terminal rows it has collected so far after unit
+// EWN_VSTAG_LO + blockIdx % (iters - 1 - EWN_VSTAG_LO) of its walk, so that most rows leave while other warps of the SM are
+// computing and the flush at the end of the grid -- where every warp of the machine is in its latency chain at the same moment --
+// has only the rows of the last units left.
+#ifndef EWN_VSTAG
+#define EWN_VSTAG 0
+#endif
+#ifndef EWN_VSTAG_LO
+#define EWN_VSTAG_LO 2
 #endif
 // Terminal rows of one block, after its loop: thread r owns finished game r of the pass (its dice, its env index and the
 // scatter of its twelve cubes into the staging tile), then the tile leaves as 16-byte vectors.  Kept out of line so that its
@@ -691,7 +704,20 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     unsigned wcnt = 0;                                             // finished games of this warp so far (warp-uniform)
     const unsigned seg = (unsigned)cap / (VTPB / 32);              // list entries per warp: one per game the warp can meet
     int16_t* const sm = smb + warp * 32 * NN;
-    while (u < n_units) {                                          // block-uniform
+#if EWN_VSTAG
+    static_assert(VTPB == 32, "the staggered flush is written for one-warp blocks");
+    const int iters_b = (n_units + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int stag_at = iters_b - 1 > EWN_VSTAG_LO ? EWN_VSTAG_LO + (int)(blockIdx.x % (unsigned)(iters_b - 1 - EWN_VSTAG_LO)) : -1;
+    unsigned flushed = 0;
+    // two passes over the same loop body: units up to the block's flush point, the flush (a call: kept OUT of the unit loop so that
+    // nothing of the loop's register allocation has to survive it), then the rest
+    const int u_split = stag_at < 0 ? n_units : min(n_units, (int)blockIdx.x + (stag_at + 1) * (int)gridDim.x);
+    for (int phase = 0; phase < 2; phase++) {
+    const int u_end = phase == 0 ? u_split : n_units;
+#else
+    const int u_end = n_units;
+#endif
+    while (u < u_end) {                                            // block-uniform
         asm volatile("cp.async.wait_all;" ::: "memory");
         const ulonglong2 sw = s_pf[2 * tid];                        // own slot: no cross-thread hazard
         longlong2 act = make_longlong2(0, 0);
@@ -762,6 +788,17 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
         }
         u = un; i = in; mine = mine_n;
     }
+#if EWN_VSTAG
+        if (phase == 0 && compact && wcnt) {                       // block-uniform (one warp): rows of the units walked so far
+            if (tid == 0) { s_wcnt[0] = wcnt; s_row0 = atomicAdd(a.term_count, wcnt); }
+            __syncthreads();
+            vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_code, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, (int)wcnt,
+                               (int64_t)s_row0);
+            __syncthreads();
+            flushed += wcnt; wcnt = 0;
+        }
+    }
+#endif
     if (!tally) return;
     {
         const unsigned wl = __reduce_add_sync(0xffffffffu, tally_c);          // <= 32 * VITER_MAX per half: no carry
@@ -772,15 +809,31 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     pre[0] = 0;
 #pragma unroll
     for (int w = 0; w < VTPB / 32; w++) pre[w + 1] = pre[w] + s_wcnt[w];
-    const int F = (int)pre[VTPB / 32];
-    if (F == 0) return;                                            // uniform over the block
+    const int F = (int)pre[VTPB / 32];                             // rows still to flush
+#if EWN_VSTAG
+    const int Ftot = F + (int)flushed;
+#else
+    const int Ftot = F;
+#endif
+    if (Ftot == 0) return;                                         // uniform over the block
     if (a.stats && tid < 4) {
         const unsigned w = s_won, l = s_lost;
-        const unsigned v = tid == 0 ? w : tid == 1 ? l : tid == 2 ? (unsigned)F - w - l : (unsigned)F;
+        const unsigned v = tid == 0 ? w : tid == 1 ? l : tid == 2 ? (unsigned)Ftot - w - l : (unsigned)Ftot;
         if (v) atomicAdd(a.stats + tid, (unsigned long long)v);
     }
-    if (!compact) return;
+    if (!compact || F == 0) return;
+#if defined(EWN_EXP_NOFLUSH)         /* diagnostic build: in-loop append kept, no reservation, no rows written (tools/k1_sweep.py) */
+    return;
+#elif defined(EWN_EXP_NOATOMIC)      /* diagnostic build: rows at a fixed per-block offset instead of the atomic reservation */
+    if (tid == 0) s_row0 = blockIdx.x * 96u;                     /* timing only: rows are not compact (and F <= 96 is assumed) */
+#elif defined(EWN_EXP_ATOMIC_ONLY)   /* diagnostic build: the reservation alone, no rows written */
     if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+    __syncthreads();
+    if (s_row0 == 0xFFFFFFFFu) a.term_index[0] = 0;                /* keep the result live */
+    return;
+#else
+    if (tid == 0) s_row0 = atomicAdd(a.term_count, (unsigned)F);
+#endif
 #if EWN_VFLUSH
     __syncthreads();
     vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_code, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, F, (int64_t)s_row0);
@@ -1307,6 +1360,15 @@ static int launch_playouts(const void* pairs, const uint32_t* root_ids, const in
         }                                                                \
     } while (0)
 
+// k_vstep launch; shared memory above the 48 KB default (large EWN_VTPB experiment builds, 9x9 boards) needs the opt-in attribute
+template <class C, int NT, bool AR> cudaError_t launch_vstep(const cudaLaunchConfig_t& cfg, const StepKArgs& ka, int cap) {
+    if (cfg.dynamicSmemBytes > 40 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_vstep<C, NT, AR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.dynamicSmemBytes);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaLaunchKernelEx(&cfg, k_vstep<C, NT, AR>, ka, cap);
+}
+
 }  // namespace
 
 // ================================================================================================
@@ -1536,14 +1598,14 @@ int ewn_step(const ewn_step_args* a, void* stream) {
         cfg.attrs = attr; cfg.numAttrs = (a->flags & EWN_STEP_NO_PDL) ? 0 : 1;
         cudaError_t le;
         if (vec_ar) {
-            if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5, true>, ka, cap);
-            else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0, true>, ka, cap);
-            else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7, true>, ka, cap);
-            else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0, true>, ka, cap);
-        } else if (N == 5) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 5, false>, ka, cap);
-        else if (use_p5(N)) le = cudaLaunchKernelEx(&cfg, k_vstep<P5, 0, false>, ka, cap);
-        else if (N == 7) le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 7, false>, ka, cap);
-        else le = cudaLaunchKernelEx(&cfg, k_vstep<P8, 0, false>, ka, cap);
+            if (N == 5) le = launch_vstep<P5, 5, true>(cfg, ka, cap);
+            else if (use_p5(N)) le = launch_vstep<P5, 0, true>(cfg, ka, cap);
+            else if (N == 7) le = launch_vstep<P8, 7, true>(cfg, ka, cap);
+            else le = launch_vstep<P8, 0, true>(cfg, ka, cap);
+        } else if (N == 5) le = launch_vstep<P5, 5, false>(cfg, ka, cap);
+        else if (use_p5(N)) le = launch_vstep<P5, 0, false>(cfg, ka, cap);
+        else if (N == 7) le = launch_vstep<P8, 7, false>(cfg, ka, cap);
+        else le = launch_vstep<P8, 0, false>(cfg, ka, cap);
         if (le != cudaSuccess) return cuda_fail(le, "k_vstep");
         LAUNCHED("k_vstep");
         return EWN_OK;
