@@ -82,6 +82,8 @@ PROTOTYPES = {
     "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
     "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
     "ewn_expectiminimax": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void, p_void, C.c_size_t, p_void]),
+    "ewn_sim_winrate": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, u64, u32, p_void, p_void]),
+    "ewn_expectiminimax_sim": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u64, p_void, p_void, p_void]),
     "ewn_playouts": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void]),
     "ewn_mc_workspace": (C.c_size_t, [i64]),
     "ewn_mc_root_wins": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),

@@ -49,7 +49,7 @@ class MinimaxPolicy(BatchPolicy):
         self.name = f"minimax(d={max_depth},{heuristic})"
 
     def action(self, engine, state, ply):
-        _, a = engine.expectiminimax(state, self.max_depth, self.heuristic, self.pruned)   # int8[n,2]; (-1,-1) on finished roots
+        _, a = engine.expectiminimax(state, self.max_depth, self.heuristic, self.pruned, seed=ply)   # int8[n,2]; (-1,-1) on finished roots
         return engine.xp.asarray(a, "i32")
 
 

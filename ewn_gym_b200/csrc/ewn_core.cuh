@@ -138,7 +138,7 @@ struct GeoLut : Geo {
 };
 
 enum { SIDE_TL = 0, SIDE_BR = 1 };
-enum { H_HYBRID = 0, H_MIN_DIST = 1, H_TWO_MIN_DIST = 2, H_ATTK = 3 };
+enum { H_HYBRID = 0, H_MIN_DIST = 1, H_TWO_MIN_DIST = 2, H_ATTK = 3, H_SIM_WINRATE = 4 };
 enum { CODE_ONGOING = 0, CODE_AGENT_ILLEGAL = 1, CODE_AGENT_WON = 2, CODE_OPP_ILLEGAL = 3, CODE_AGENT_LOST = 4,
        CODE_ILLEGAL_TOLERATED = 5 };
 
@@ -592,6 +592,9 @@ EWN_HD double inv_count(int c) {   // 1.0 / c, correctly rounded (compile-time I
     }
 }
 template <class C> EWN_HD double evaluate(const Game<C>& g, const Geo& geo, int heuristic) {
+    // 'sim_winrate' is dispatched before the terminal tests (minimax_ewn.py:36-37): on a finished game simulate() plays nothing and
+    // returns win_count / num_simulations = 1.0 or 0.0 (:231-233).  Live positions are evaluated by sim_unit_value, not here.
+    if (heuristic == H_SIM_WINRATE) return tl_won<C>(g, geo) ? 1.0 : 0.0;
     if (tl_won<C>(g, geo)) return 10.0;                                   // minimax_ewn.py:42-44
     if (any_at<C>(g.br, 0) || all_dead<C>(g.tl)) return -10.0;            // :45-47
     SideStats p = side_stats<C>(g.tl), n = side_stats<C>(g.br);
@@ -755,6 +758,53 @@ template <class C> EWN_HD int playout(Game<C> g, const Geo& geo, u64 seed, u32 r
     if (plies_out) *plies_out = plies;
     return tl_won<C>(g, geo) ? 1 : 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// MinimaxEnv.simulate (envs/minimax_ewn.py:215-238), the 'sim_winrate' leaf: num_simulations random playouts, fraction TOP_LEFT wins.
+// The loop is switch_player -> roll -> random legal move (:220-229), and NOTHING restores current_player afterwards: a playout
+// ends on the winner's move, so the next playout of the same env is opened by the side that just LOST.  The side that opens is
+// therefore a two-state chain over the playouts of a position (opened by BOTTOM_RIGHT -> TOP_LEFT wins -> BOTTOM_RIGHT opens again
+// ...), and the returned fraction is the mixture that chain produces -- not the win rate under either fixed opener.  Reproduced here:
+// both openers are played for every playout index (independent Philox streams), and the chain picks, for playout j, the result under
+// the opener the previous result dictates.  The first playout of a position is opened by BOTTOM_RIGHT (a fresh MinimaxEnv has
+// current_player = TOP_LEFT, envs/ewn.py:71; the carry-over from the previous position's last playout is not modelled: 1 of n).
+// ------------------------------------------------------------------------------------------------
+// one playout from g with the given opener (1 = BOTTOM_RIGHT, 0 = TOP_LEFT); Philox stream (unit, opener, index).  Returns 1 if TOP_LEFT won.
+template <class C, class G> EWN_HD int sim_playout(Game<C> g, const G& geo, const RoundKeys& rk, u32 unit, int opener_br, u32 index) {
+    bool over = full_win<C>(g, geo);
+    u32 j = 0;
+    while (!over) {
+        u32 blk[4];
+        playout_block_rk(rk, unit, (u32)opener_br, index, j++, blk);
+        g.dice = 1 + (int)bounded(blk[0], 6u);                            // random.randint(1, 6): six faces whatever the layout (:223)
+        over = opener_br ? random_ply<C, SIDE_BR>(g, geo, blk[1], nullptr, nullptr) : random_ply<C, SIDE_TL>(g, geo, blk[1], nullptr, nullptr);
+        if (over) break;
+        g.dice = 1 + (int)bounded(blk[2], 6u);
+        over = opener_br ? random_ply<C, SIDE_TL>(g, geo, blk[3], nullptr, nullptr) : random_ply<C, SIDE_BR>(g, geo, blk[3], nullptr, nullptr);
+    }
+    return tl_won<C>(g, geo) ? 1 : 0;
+}
+// the chain over n playouts: bits_br / bits_tl = TOP_LEFT-win bit of playout j under either opener (32 per word). -> win count
+EWN_HD int sim_chain(const u32* bits_br, const u32* bits_tl, int n) {
+    int wins = 0, opener_br = 1;
+    for (int j = 0; j < n; j++) {
+        const u32 w = ((opener_br ? bits_br : bits_tl)[j >> 5] >> (j & 31)) & 1u;
+        wins += (int)w;
+        opener_br = (int)w;                                               // TOP_LEFT won -> BOTTOM_RIGHT lost -> BOTTOM_RIGHT opens the next one
+    }
+    return wins;
+}
+EWN_HD int sim_words(int n) { return (n + 31) >> 5; }
+// evaluate('sim_winrate') of one LIVE position, everything in one worker (host simulator; the CUDA path spreads the playouts over threads)
+template <class C, class G> EWN_HD double sim_unit_value(const Game<C>& g, const G& geo, const RoundKeys& rk, u32 unit, int n) {
+    u32 bb[8] = {0, 0, 0, 0, 0, 0, 0, 0}, bt[8] = {0, 0, 0, 0, 0, 0, 0, 0};          // n <= 256
+    for (int j = 0; j < n; j++) {
+        if (sim_playout<C>(g, geo, rk, unit, 1, (u32)j)) bb[j >> 5] |= 1u << (j & 31);
+        if (sim_playout<C>(g, geo, rk, unit, 0, (u32)j)) bt[j >> 5] |= 1u << (j & 31);
+    }
+    return f64_div((double)sim_chain(bb, bt, n), (double)n);
+}
+static constexpr int SIM_MAX = 256;                  // num_simulations supported (the reference hard-codes 100, minimax_ewn.py:21)
 
 // ------------------------------------------------------------------------------------------------
 // The reference's OWN random stream: numpy's legacy global RandomState, i.e. MT19937 seeded by `np.random.seed(seed)`
@@ -964,6 +1014,7 @@ EWN_HD double f64_inf() { return bits_to_f64(0x7FF0000000000000ull); }
 // Record codecs.  double: the value itself (any heuristic).  uint16_t ('hybrid' with the value table vt, device only): the
 // table index of a live position, or one of four marks -- a quarter of the bytes, and sixteen records per 32-byte sector.
 static constexpr uint16_t EMM16_ABSENT = 0xFFFF, EMM16_INTERIOR = 0xFFFE, EMM16_WIN = 0xFFFD, EMM16_LOSS = 0xFFFC;
+static constexpr u64 EMM_PENDING = 0xFFF8000000000002ull;      // 'sim_winrate' leaf whose playouts have not been played yet (| 4: six-fold leaf)
 EWN_HD void emm_mark(double* p, bool absent) { *p = bits_to_f64(absent ? EMM_ABSENT : EMM_INTERIOR); }
 EWN_HD void emm_mark(uint16_t* p, bool absent) { *p = absent ? EMM16_ABSENT : EMM16_INTERIOR; }
 EWN_HD bool emm_is_absent(double r) { return f64_to_bits(r) == EMM_ABSENT; }
@@ -981,6 +1032,15 @@ EWN_HD double emm_value(uint16_t r, const double* vt) {
 }
 template <class C, class G> EWN_HD void emm_leaf(double* p, const Game<C>& g, const G& geo, int heuristic, bool over, int mover_br, bool fold) {
     *p = leaf_value<C>(g, geo, heuristic, over, mover_br, fold);
+}
+// 'sim_winrate' search: geometry + where the leaf POSITIONS go (a u64[WORDS] slot per record, parallel to the record array); the
+// leaf's value is filled in after its playouts have been played (ewn_expectiminimax_sim)
+template <class Base> struct GeoSimT : Base { u64* sim_states; const double* sim_base; };
+template <class C, class Base> EWN_HD void emm_leaf(double* p, const Game<C>& g, const GeoSimT<Base>& geo, int, bool over, int mover_br, bool fold) {
+    if (over) { *p = mover_br ? 0.0 : 1.0; return; }                      // simulate() on a finished game: the mover has just won
+    *p = bits_to_f64(EMM_PENDING | (fold ? 4ull : 0ull));
+    Game<C> t = g; t.dice = 1; t.player = SIDE_TL;
+    pack(t, geo.sim_states, (long)(p - geo.sim_base), static_cast<const Geo&>(geo));
 }
 #if defined(__CUDA_ARCH__)
 template <class C> __device__ __forceinline__ void emm_leaf(uint16_t* p, const Game<C>& g, const GeoLut& geo, int, bool over, int mover_br, bool fold) {

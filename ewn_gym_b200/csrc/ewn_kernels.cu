@@ -917,8 +917,10 @@ __global__ void __launch_bounds__(TPB) k_emm_table(double* vt, int N) {
     if (i < emm_table_size(N)) vt[i] = emm_table_entry(N, i);
 }
 
+// sim_states != nullptr ('sim_winrate' search, R = double): leaves are stored as POSITIONS (a u64[WORDS] slot per record) and marked
+// pending; their values are filled in by k_sim_playouts + k_sim_values before the replay
 template <class C, class R> __global__ void __launch_bounds__(TPB) k_emm_expand(const u64* state, R* vals, int64_t n_roots, Geo geo,
-                                                                                int depth, int heuristic, const double* vt) {
+                                                                                int depth, int heuristic, const double* vt, u64* sim_states) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
     GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
     geol.vt = vt;
@@ -931,7 +933,65 @@ template <class C, class R> __global__ void __launch_bounds__(TPB) k_emm_expand(
     Game<C> g; unpack(g, state, (long)root);
     g.player = SIDE_TL;
     if (full_win<C>(g, geo)) return;               // finished root: phase 2 evaluates it directly
-    emm_expand_parent<C>(g, geol, depth, heuristic, tp, vals + (int64_t)root * emm_level_offset(m + 1));
+    const int64_t per_root = emm_level_offset(m + 1);
+    if constexpr (sizeof(R) == sizeof(double)) {
+        if (sim_states) {
+            GeoSimT<GeoLut> gs;
+            static_cast<GeoLut&>(gs) = geol;
+            gs.sim_base = reinterpret_cast<const double*>(vals) + (int64_t)root * per_root;
+            gs.sim_states = sim_states + (int64_t)root * per_root * C::WORDS;
+            emm_expand_parent<C>(g, gs, depth, heuristic, tp, reinterpret_cast<double*>(vals) + (int64_t)root * per_root);
+            return;
+        }
+    }
+    emm_expand_parent<C>(g, geol, depth, heuristic, tp, vals + (int64_t)root * per_root);
+}
+
+// ------------------------------------------------------------------------------------------------
+// 'sim_winrate' leaves (envs/minimax_ewn.py:215-238).  recs: one double per position, EMM_PENDING (| 4: evaluated six times, minimax.py:
+// 64-73 over six depth-0 calls) where playouts are wanted; states: the positions (u64[WORDS] each); bits: per (position, fold, opener)
+// the TOP_LEFT-win bit of every playout index.  One thread per (position, fold, opener, playout): a slow, simple kernel for a leaf
+// evaluation that costs 200 to 1,200 random games per position by definition.
+// ------------------------------------------------------------------------------------------------
+template <class C> __global__ void __launch_bounds__(TPB) k_sim_playouts(const double* recs, const u64* states, int64_t n_slots, u32 unit0, int nsim,
+                                                                         Geo geo, const RoundKeys rk, u32* bits) {
+    __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
+    const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);
+    __syncthreads();
+    const int64_t gid = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    const int64_t per_slot = 12LL * nsim;                           // 6 folds x 2 openers x playouts
+    if (gid >= n_slots * per_slot) return;
+    const int64_t slot = gid / per_slot;
+    const int r = (int)(gid - slot * per_slot);
+    const int fo = r / nsim, j = r - fo * nsim, f = fo >> 1, opener_br = 1 - (fo & 1);
+    const u64 rec = f64_to_bits(recs[slot]);
+    if ((rec & ~4ull) != EMM_PENDING || f >= ((rec & 4ull) ? 6 : 1)) return;
+    Game<C> g; unpack(g, states, (long)slot, geo);
+    if (sim_playout<C>(g, geol, rk, (unit0 + (u32)slot) * 6u + (u32)f, opener_br, (u32)j))
+        atomicOr(bits + ((slot * 6 + f) * 2 + (opener_br ? 0 : 1)) * sim_words(nsim) + (j >> 5), 1u << (j & 31));
+}
+
+__global__ void __launch_bounds__(TPB) k_sim_values(double* recs, int64_t n_slots, int nsim, const u32* bits) {
+    const int64_t slot = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (slot >= n_slots) return;
+    const u64 rec = f64_to_bits(recs[slot]);
+    if ((rec & ~4ull) != EMM_PENDING) return;
+    const int W = sim_words(nsim), folds = (rec & 4ull) ? 6 : 1;
+    double e = 0.0, v = 0.0;
+    for (int f = 0; f < folds; f++) {
+        const u32* b = bits + ((slot * 6 + f) * 2) * W;
+        v = f64_div((double)sim_chain(b, b + W, nsim), (double)nsim);       // win_count / self.num_simulations (:238)
+        e = f64_add(e, f64_div(v, 6.0));                                     // minimax.py:64-73 over six depth-0 evaluations
+    }
+    recs[slot] = folds == 1 ? v : e;
+}
+
+// evaluate('sim_winrate') for a batch of positions: marks finished ones 1.0 / 0.0, the others pending
+template <class C> __global__ void __launch_bounds__(TPB) k_sim_mark(const u64* state, double* recs, int64_t n, Geo geo) {
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i, geo);
+    recs[i] = full_win<C>(g, geo) ? (tl_won<C>(g, geo) ? 1.0 : 0.0) : bits_to_f64(EMM_PENDING);
 }
 
 template <class C, int M, class R> __global__ void __launch_bounds__(128) k_emm_replay(const u64* state, const R* vals, const double* vt, int64_t n_roots,
@@ -1360,6 +1420,19 @@ static int launch_playouts(const void* pairs, const uint32_t* root_ids, const in
         }                                                                \
     } while (0)
 
+// pending records -> values: zero the bit planes, play, reduce.  `bits` holds n_slots * 12 * sim_words(nsim) words.
+template <class C> static int sim_fill(double* recs, const u64* states, int64_t n_slots, uint32_t unit0, int nsim, const Geo& geo, uint64_t seed,
+                                       uint32_t* bits, cudaStream_t st) {
+    const int64_t threads = n_slots * 12LL * nsim;
+    if (threads >= ((int64_t)1 << 31) * TPB) return EWN_ENOSUP;
+    CU(cudaMemsetAsync(bits, 0, (size_t)n_slots * 12 * sim_words(nsim) * sizeof(uint32_t), st));
+    k_sim_playouts<C><<<(unsigned)((threads + TPB - 1) / TPB), TPB, 0, st>>>(recs, states, n_slots, unit0, nsim, geo, make_round_keys(seed), bits);
+    LAUNCHED("k_sim_playouts");
+    k_sim_values<<<blocks_for(n_slots), TPB, 0, st>>>(recs, n_slots, nsim, bits);
+    LAUNCHED("k_sim_values");
+    return EWN_OK;
+}
+
 // k_vstep launch; shared memory above the 48 KB default (large EWN_VTPB experiment builds, 9x9 boards) needs the opt-in attribute
 template <class C, int NT, bool AR> cudaError_t launch_vstep(const cudaLaunchConfig_t& cfg, const StepKArgs& ka, int cap) {
     if (cfg.dynamicSmemBytes > 40 * 1024) {
@@ -1736,7 +1809,7 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
 #define LAUNCH_EMM(C, R)                                                                                           \
     do {                                                                                                           \
         R* vals = (R*)workspace;                                                                                   \
-        k_emm_expand<C, R><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic, vt);                        \
+        k_emm_expand<C, R><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, heuristic, vt, nullptr);               \
         LAUNCHED("k_emm_expand");                                                                                  \
         switch (m) {                                                                                               \
             case 1: k_emm_replay<C, 1, R><<<grid2, 128, 0, st>>>(state, vals, vt, nr, r0, geo, heuristic, pruned, value, action); break; \
@@ -1749,6 +1822,62 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
         if (use_p5(N)) { if (compact) LAUNCH_EMM(P5, uint16_t); else LAUNCH_EMM(P5, double); }
         else           { if (compact) LAUNCH_EMM(P8, uint16_t); else LAUNCH_EMM(P8, double); }
 #undef LAUNCH_EMM
+    }
+    return EWN_OK;
+}
+
+int ewn_sim_winrate(const uint64_t* state, int64_t n, int N, int L, int num_simulations, uint64_t seed, uint32_t unit0, double* value, void* stream) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || num_simulations < 1 || num_simulations > SIM_MAX) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;      // six-face die hard-coded in simulate() (minimax_ewn.py:223)
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    void* ws = nullptr;
+    int rc = scratch_get((size_t)n * 12 * sim_words(num_simulations) * sizeof(uint32_t), &ws, st);
+    if (rc) return rc;
+    if (use_p5(N)) { k_sim_mark<P5><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo); LAUNCHED("k_sim_mark"); return sim_fill<P5>(value, state, n, unit0, num_simulations, geo, seed, (uint32_t*)ws, st); }
+    k_sim_mark<P8><<<blocks_for(n), TPB, 0, st>>>(state, value, n, geo); LAUNCHED("k_sim_mark");
+    return sim_fill<P8>(value, state, n, unit0, num_simulations, geo, seed, (uint32_t*)ws, st);
+}
+
+int ewn_expectiminimax_sim(const uint64_t* state, int64_t n, int N, int L, int depth, int pruned, int num_simulations, uint64_t seed,
+                           double* value, int8_t* action, void* stream) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || num_simulations < 1 || num_simulations > SIM_MAX) return EWN_EARG;
+    if (depth < 1 || depth > 4) return EWN_ENOSUP;       // 216 leaf positions x up to 1,200 playouts per root at depth 3 / 4 is the practical limit
+    if (L != 3) return EWN_ENOSUP;
+    if (n == 0) return EWN_OK;
+    Geo geo = make_geo(N, L);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int m = emm_levels(depth), words = use_p5(N) ? 1 : 2, W = sim_words(num_simulations);
+    const int64_t per_root = emm_level_offset(m + 1), slots = emm_level_size(m);
+    const size_t bytes_root = (size_t)per_root * (8 + 8 * words + 12 * W * 4);
+    int64_t chunk = (int64_t)(((size_t)512 << 20) / bytes_root);
+    if (chunk < 1) chunk = 1;
+    if (chunk > n) chunk = n;
+    void* ws = nullptr;
+    int rc = scratch_get(bytes_root * (size_t)chunk, &ws, st);
+    if (rc) return rc;
+    double* vals = (double*)ws;
+    uint64_t* sst = (uint64_t*)(vals + chunk * per_root);
+    uint32_t* bits = (uint32_t*)(sst + chunk * per_root * words);
+    for (int64_t r0 = 0; r0 < n; r0 += chunk) {
+        const int64_t nr = (n - r0 < chunk) ? (n - r0) : chunk;
+        if ((uint64_t)(r0 + nr) * (uint64_t)per_root * 6u >= ((uint64_t)1 << 32)) return EWN_ENOSUP;     // Philox unit ids are 32-bit
+        const uint64_t* s0 = state + r0 * words;
+        const unsigned grid1 = blocks_for(nr * (slots / 6)), grid2 = (unsigned)((nr + 127) / 128);
+        const uint32_t unit0 = (uint32_t)(r0 * per_root);
+#define SIM_SEARCH(C)                                                                                                              \
+    do {                                                                                                                           \
+        k_emm_expand<C, double><<<grid1, TPB, 0, st>>>(s0, vals, nr, geo, depth, H_SIM_WINRATE, nullptr, sst);                     \
+        LAUNCHED("k_emm_expand");                                                                                                  \
+        rc = sim_fill<C>(vals, sst, nr * per_root, unit0, num_simulations, geo, seed, bits, st);                                   \
+        if (rc) return rc;                                                                                                         \
+        if (m == 1) k_emm_replay<C, 1, double><<<grid2, 128, 0, st>>>(state, vals, nullptr, nr, r0, geo, H_SIM_WINRATE, pruned & 1, value, action); \
+        else        k_emm_replay<C, 2, double><<<grid2, 128, 0, st>>>(state, vals, nullptr, nr, r0, geo, H_SIM_WINRATE, pruned & 1, value, action); \
+        LAUNCHED("k_emm_replay");                                                                                                  \
+    } while (0)
+        if (use_p5(N)) SIM_SEARCH(P5); else SIM_SEARCH(P8);
+#undef SIM_SEARCH
     }
     return EWN_OK;
 }

@@ -12,7 +12,7 @@ from typing import Optional
 from . import _lib
 from ._lib import StepArgs
 
-HEURISTICS = {"hybrid": 0, "min_dist": 1, "two_min_dist": 2, "attk": 3}
+HEURISTICS = {"hybrid": 0, "min_dist": 1, "two_min_dist": 2, "attk": 3, "sim_winrate": 4}
 TOP_LEFT, BOTTOM_RIGHT = 1, 2
 CODE_ONGOING, CODE_AGENT_ILLEGAL, CODE_AGENT_WON, CODE_OPP_ILLEGAL, CODE_AGENT_LOST, CODE_ILLEGAL_TOLERATED = range(6)
 MESSAGES = {  # info["message"] strings of envs/ewn.py:448,454,473,478
@@ -292,11 +292,25 @@ class Engine:
                   "ewn_evaluate")
         return v
 
-    def expectiminimax(self, state, depth: int, heuristic="hybrid", pruned=True, replay_path=False, out=None):
+    def sim_winrate(self, state, num_simulations: int = 100, seed: int = 0, unit0: int = 0):
+        """MinimaxEnv.evaluate('sim_winrate') = simulate() (minimax_ewn.py:215-238) for every position -> f64[n]"""
+        n = self._n(state)
+        v = self.xp.empty((n,), "f64")
+        self._chk(self.lib.ewn_sim_winrate(self.xp.ptr(state), n, self.N, self.L, int(num_simulations), seed, unit0, self.xp.ptr(v),
+                                           self.xp.stream()), "ewn_sim_winrate")
+        return v
+
+    def expectiminimax(self, state, depth: int, heuristic="hybrid", pruned=True, replay_path=False, out=None, num_simulations: int = 100,
+                       seed: int = 0):
         """-> (value f64[n], action i8[n,2]); action (-1,-1) = None for finished roots (minimax.py:22-23).
-        replay_path: run depth 3 / 4 on the record + replay kernels (the depth >= 5 path) instead of the fused kernel (A/B)."""
+        replay_path: run depth 3 / 4 on the record + replay kernels (the depth >= 5 path) instead of the fused kernel (A/B).
+        heuristic 'sim_winrate': leaves are evaluated by num_simulations random playouts (Philox key `seed`), depth <= 4."""
         n = self._n(state)
         v, a = out if out is not None else (self.xp.empty((n,), "f64"), self.xp.empty((n, 2), "i8"))
+        if heuristic == "sim_winrate":
+            self._chk(self.lib.ewn_expectiminimax_sim(self.xp.ptr(state), n, self.N, self.L, depth, int(bool(pruned)), int(num_simulations), seed,
+                                                      self.xp.ptr(v), self.xp.ptr(a), self.xp.stream()), "ewn_expectiminimax_sim")
+            return v, a
         self._chk(self.lib.ewn_expectiminimax(self.xp.ptr(state), n, self.N, self.L, depth, HEURISTICS[heuristic],
                                               int(bool(pruned)) | (2 if replay_path else 0),
                                               self.xp.ptr(v), self.xp.ptr(a), None, 0, self.xp.stream()), "ewn_expectiminimax")

@@ -317,23 +317,22 @@ class MinimaxEnv(EinsteinWuerfeltNichtEnv):
         return self.evaluate("attk")
 
     def simulate(self) -> float:
-        """num_simulations random playouts from the current position, fraction TOP_LEFT wins (minimax_ewn.py:215-238).
-        The side that moves first is the opponent of current_player, as in the reference's switch-then-move loop."""
-        st = self._clone()
+        """num_simulations random playouts from the current position, fraction TOP_LEFT wins (minimax_ewn.py:215-238), on the engine's
+        'sim_winrate' kernels: the opener of every playout follows the reference's never-restored current_player toggle within the
+        call (Engine.sim_winrate); the call's first playout is opened by the opponent of current_player, as in the reference.
+        (The reference also leaves current_player toggled by the number of plies it played; this class leaves it alone.)"""
+        n = self.num_simulations
+        if self.check_win():                                           # the playout loop never runs: win_count / n is 1.0 or 0.0 (:231-238)
+            return 1.0 if (self.board[-1, -1] > 0 or not np.any(self.board < 0)) else 0.0
         first = Player.get_opponent(self.current_player)
-        if first == Player.BOTTOM_RIGHT:
-            wins = self._engine.playouts(st, seed=int(np.random.randint(0, 2 ** 31 - 1)), first=0, count=self.num_simulations,
-                                         root_ids=[self._sim_calls])
-            w = int(_np(wins)[0])
-        else:
-            # mirror the position (rotate by 180 degrees and negate: envs/ewn.py:289-296) so that the kernel's
-            # BOTTOM_RIGHT-moves-first playout plays TOP_LEFT first; TOP_LEFT wins = playouts - mirrored TOP_LEFT wins
+        st = self._clone()
+        if first == Player.TOP_LEFT:
+            # the kernels open a position's first playout with BOTTOM_RIGHT: hand them the mirrored position (envs/ewn.py:289-296) and
+            # read the result from the other side: TOP_LEFT wins = n - mirrored TOP_LEFT wins
             st = self._engine.encode(np.rot90(-self.board, 2)[None].copy(), [1], [Player.BOTTOM_RIGHT.value])
-            wins = self._engine.playouts(st, seed=int(np.random.randint(0, 2 ** 31 - 1)), first=0, count=self.num_simulations,
-                                         root_ids=[self._sim_calls])
-            w = self.num_simulations - int(_np(wins)[0])
+        v = float(_np(self._engine.sim_winrate(st, n, seed=int(np.random.randint(0, 2 ** 31 - 1)), unit0=self._sim_calls))[0])
         self._sim_calls += 1
-        return w / self.num_simulations
+        return v if first == Player.BOTTOM_RIGHT else (n - round(v * n)) / n
 
 
 class MiniMaxHeuristicEnv(MinimaxEnv):

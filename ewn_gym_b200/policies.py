@@ -59,7 +59,8 @@ class ExpectiMinimaxAgent(PolicyBase):
         """-> (actions int8[n,2] with (-1,-1) for finished positions, values float64[n]) as host arrays"""
         e = self.engine
         st = e.encode(board, dice_roll)
-        v, a = e.expectiminimax(st, self.max_depth, self.heuristic, self.pruned)
+        self._calls = getattr(self, "_calls", 0) + 1          # 'sim_winrate': fresh playout streams for every call
+        v, a = e.expectiminimax(st, self.max_depth, self.heuristic, self.pruned, seed=self._calls)
         return _host(a), _host(v)
 
     def expectiminimax_value(self, obs):

@@ -230,6 +230,21 @@ EWN_API size_t ewn_expectiminimax_workspace(int64_t n, int depth);
 EWN_API int ewn_expectiminimax(const uint64_t *state, int64_t n, int board_size, int cube_layer, int depth, int heuristic, int pruned,
                        double *value, int8_t *action, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- the 'sim_winrate' heuristic (envs/minimax_ewn.py:36-37, :215-238 MinimaxEnv.simulate) ------------------------------------
+ * evaluate('sim_winrate') of n positions -> f64[n]: num_simulations (<= 256; the reference hard-codes 100, :21) random playouts with a
+ * six-face die, fraction that TOP_LEFT wins; 1.0 / 0.0 on a finished game.  simulate() never restores current_player, so the side
+ * that opens a playout is the one that lost the previous playout of the same call sequence; the first playout of a position is
+ * opened by BOTTOM_RIGHT here (a fresh env).  Philox streams: (seed; unit = (unit0 + i) * 6, opener, playout index). */
+#define EWN_H_SIM_WINRATE 4
+EWN_API int ewn_sim_winrate(const uint64_t *state, int64_t n, int board_size, int cube_layer, int num_simulations, uint64_t seed,
+                    uint32_t unit0, double *value, void *stream);
+/* ExpectiMinimaxAgent(heuristic='sim_winrate').predict (eval_minimax.py --heuristic sim_winrate) for depth 1..4: the tree is expanded
+ * to leaf POSITIONS, every live leaf is evaluated by ewn_sim_winrate's playouts (six independent evaluations at even depth,
+ * minimax.py:64-73), finished positions are worth 1.0 / 0.0, then minimax.py:19-73 is replayed over the values.  Results are
+ * reproducible in (seed, root index) and statistically -- not bit for bit -- those of the reference (CPython's `random`). */
+EWN_API int ewn_expectiminimax_sim(const uint64_t *state, int64_t n, int board_size, int cube_layer, int depth, int pruned, int num_simulations,
+                           uint64_t seed, double *value, int8_t *action, void *stream);
+
 /* classical_policies/mcts.py:21-45 simulate: random playouts from n states with BOTTOM_RIGHT to move.
  * wins[i] += number of playouts with index in [first, first+count) that TOP_LEFT wins (u32[n], caller zeroes).
  * root_ids: u32[n] Philox stream ids (NULL = 0..n-1). plies: optional u64[1] accumulator of plies played. */

@@ -317,6 +317,70 @@ def gen_mc(name, N, L, n_states, n_play):
     print(f"{name}: {len(roots)} states x {n_play} playouts, {time.time() - t:.1f}s")
 
 
+def run_simulate(args):
+    """MinimaxEnv.simulate (minimax_ewn.py:215-238) called `calls` times in a row on one position with a FRESH env (current_player =
+    TOP_LEFT: the first playout is opened by BOTTOM_RIGHT; within the calls the never-restored toggle runs as in the reference)."""
+    N, L, board, calls, seed = args
+    import random
+    random.seed(seed)
+    env = R.MinimaxEnv(board_size=N, cube_layer=L)
+    ag = R.ExpectiMinimaxAgent(max_depth=1, cube_layer=L, board_size=N)
+    ag.env = env
+    ag.restore_env_with_obs({"board": board.astype(np.int16), "dice_roll": 1})
+    tot = 0
+    first = None
+    for c in range(calls):
+        v = env.simulate()
+        if first is None:
+            first = v
+        tot += int(round(v * env.num_simulations))
+    return tot, int(round(first * env.num_simulations))
+
+
+def gen_sim(name, N, L, n_states, calls):
+    """'sim_winrate' statistics of the unmodified reference: per sampled position the TOP_LEFT wins over calls x 100 playouts (one env,
+    consecutive calls) and of the first call alone."""
+    t = time.time()
+    boards, dice = get_states(N, L, n_states * 2)
+    menv = R.MinimaxEnv(board_size=N, cube_layer=L)
+    ag = R.ExpectiMinimaxAgent(max_depth=1, cube_layer=L, board_size=N)
+    ag.env = menv
+    keep = []
+    for b, d in zip(boards, dice):
+        ag.restore_env_with_obs({"board": b.astype(np.int16), "dice_roll": int(d)})
+        if not menv.check_win():
+            keep.append(b)
+        if len(keep) == n_states:
+            break
+    res = pmap(run_simulate, [(N, L, b, calls, 4321 + i) for i, b in enumerate(keep)])
+    np.savez_compressed(os.path.join(HERE, name), N=N, L=L, boards=np.array(keep, np.int8), wins=np.array([r[0] for r in res], np.int64),
+                        wins_first_call=np.array([r[1] for r in res], np.int64), playouts=calls * 100, num_simulations=100)
+    print(f"{name}: {len(keep)} states x {calls} calls x 100 playouts, {time.time() - t:.1f}s")
+
+
+def run_sim_search(args):
+    N, L, depth, boards, dice, seed = args
+    import random
+    random.seed(seed)
+    ag = R.ExpectiMinimaxAgent(max_depth=depth, cube_layer=L, board_size=N, heuristic="sim_winrate")
+    vals = []
+    for b, d in zip(boards, dice):
+        obs = {"board": b.astype(np.int16), "dice_roll": int(d)}
+        ag.restore_env_with_obs(obs)
+        v, a = ag.expectiminimax(depth, ag.env.agent_player, None, -float("inf"), float("inf"))
+        vals.append(float(v))
+    return np.array(vals)
+
+
+def gen_sim_search(name, N, L, n_states, depth, reps):
+    """root values of ExpectiMinimaxAgent(heuristic='sim_winrate') at `depth`, `reps` independent runs per state (they are random)"""
+    t = time.time()
+    boards, dice = get_states(N, L, n_states)
+    res = pmap(run_sim_search, [(N, L, depth, boards, dice, 99 + r) for r in range(reps)])
+    np.savez_compressed(os.path.join(HERE, name), N=N, L=L, depth=depth, boards=boards, dice=dice, values=np.stack(res))
+    print(f"{name}: {n_states} states x {reps} runs at depth {depth}, {time.time() - t:.1f}s")
+
+
 def count_games(args):
     N, L, seeds = args
     env = R.EinsteinWuerfeltNichtEnv(board_size=N, cube_layer=L)
@@ -392,6 +456,8 @@ TARGETS = {
     "rules6L4": lambda: gen_rules("rules_6x6_L4.npz", 6, 4, 300),
     "rules7L5": lambda: gen_rules("rules_7x7_L5.npz", 7, 5, 150),
     "shaped7L4": lambda: gen_shaped("shaped_7x7_L4.npz", 7, 4, 16, 96, 10),
+    "sim5": lambda: gen_sim("sim_winrate_5x5.npz", 5, 3, 40, 30),
+    "simsearch5": lambda: gen_sim_search("sim_search_5x5.npz", 5, 3, 24, 1, 16),
     "mm5": lambda: gen_minimax("minimax_5x5.npz", 5, 3, 2000, {1: 2000, 2: 2000, 3: 2000, 4: 2000, 5: 320}),
     "mm7": lambda: gen_minimax("minimax_7x7.npz", 7, 3, 600, {1: 600, 2: 600, 3: 600, 4: 600, 5: 96}, heur_count=100),
     "rules5": lambda: gen_rules("rules_5x5.npz", 5, 3, 4000),

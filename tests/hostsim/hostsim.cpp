@@ -272,6 +272,45 @@ template <class C> static int t_flip(const uint64_t* in, uint64_t* out, int64_t 
     for (int64_t i = 0; i < n; i++) { Game<C> g; unpack(g, in, i, geo); flip_game<C>(g, geo); pack(g, out, i, geo); }
     return EWN_OK;
 }
+template <class C> int t_sim_winrate(const uint64_t* state, int64_t n, const Geo& geo, int nsim, u64 seed, u32 unit0, double* value) {
+    const RoundKeys rk = make_round_keys(seed);
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g; unpack(g, state, i, geo);
+        value[i] = full_win<C>(g, geo) ? (tl_won<C>(g, geo) ? 1.0 : 0.0) : sim_unit_value<C>(g, geo, rk, (unit0 + (u32)i) * 6u, nsim);
+    }
+    return EWN_OK;
+}
+// the 'sim_winrate' search as the CUDA path does it: expand to leaf positions, evaluate the pending ones, replay
+template <class C> int t_emm_sim(const uint64_t* state, int64_t n, const Geo& geo, int depth, int pruned, int nsim, u64 seed, double* value, int8_t* action) {
+    const int m = emm_levels(depth);
+    const long slots = emm_level_size(m), per_root = emm_level_offset(m + 1);
+    const RoundKeys rk = make_round_keys(seed);
+    std::vector<double> vals((size_t)per_root);
+    std::vector<u64> sst((size_t)per_root * C::WORDS);
+    for (int64_t r = 0; r < n; r++) {
+        Game<C> g; unpack(g, state, r); g.player = SIDE_TL;
+        if (!full_win<C>(g, geo)) {
+            GeoSimT<Geo> gs; static_cast<Geo&>(gs) = geo; gs.sim_base = vals.data(); gs.sim_states = sst.data();
+            for (long tp = 0; tp < slots / 6; tp++) emm_expand_parent<C>(g, gs, depth, H_SIM_WINRATE, (u32)tp, vals.data());
+            for (long s = 0; s < per_root; s++) {
+                const u64 rec = f64_to_bits(vals[s]);
+                if ((rec & ~4ull) != EMM_PENDING) continue;
+                Game<C> leaf; unpack(leaf, sst.data(), s, geo);
+                const int folds = (rec & 4ull) ? 6 : 1;
+                double e = 0.0, v = 0.0;
+                for (int f = 0; f < folds; f++) {
+                    v = sim_unit_value<C>(leaf, geo, rk, (u32)((r * per_root + s) * 6 + f), nsim);
+                    e = f64_add(e, f64_div(v, 6.0));
+                }
+                vals[s] = folds == 1 ? v : e;
+            }
+        }
+        int la, di;
+        value[r] = m == 1 ? emm_root<C, 1>(g, geo, H_SIM_WINRATE, pruned & 1, vals.data(), la, di) : emm_root<C, 2>(g, geo, H_SIM_WINRATE, pruned & 1, vals.data(), la, di);
+        if (action) { action[2 * r] = (int8_t)la; action[2 * r + 1] = (int8_t)di; }
+    }
+    return EWN_OK;
+}
 #define BY_CODEC(N, call_p5, call_p8) (use_p5(N) ? (call_p5) : (call_p8))
 
 extern "C" {
@@ -433,6 +472,19 @@ int ewn_expectiminimax(const uint64_t* state, int64_t n, int N, int L, int depth
     if (depth < 1 || depth > EWN_MAX_DEPTH || L != 3) return EWN_ENOSUP;
     Geo geo = make_geo(N, L);
     return BY_CODEC(N, t_emm<P5>(state, n, geo, depth, heuristic, pruned, value, action), t_emm<P8>(state, n, geo, depth, heuristic, pruned, value, action));
+}
+int ewn_sim_winrate(const uint64_t* state, int64_t n, int N, int L, int nsim, uint64_t seed, uint32_t unit0, double* value, void*) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || nsim < 1 || nsim > SIM_MAX) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_sim_winrate<P5>(state, n, geo, nsim, seed, unit0, value), t_sim_winrate<P8>(state, n, geo, nsim, seed, unit0, value));
+}
+int ewn_expectiminimax_sim(const uint64_t* state, int64_t n, int N, int L, int depth, int pruned, int nsim, uint64_t seed, double* value,
+                           int8_t* action, void*) {
+    if (!state || !value || n < 0 || !config_ok(N, L) || nsim < 1 || nsim > SIM_MAX) return EWN_EARG;
+    if (depth < 1 || depth > 4 || L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_emm_sim<P5>(state, n, geo, depth, pruned, nsim, seed, value, action), t_emm_sim<P8>(state, n, geo, depth, pruned, nsim, seed, value, action));
 }
 int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
                  uint32_t* wins, unsigned long long* plies, void*) {
