@@ -486,6 +486,32 @@ def run_ours(args, rank, world, local_rank):
         rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
                                "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
 
+        # the same collection with a POLICY between the steps (train.py:144-155 -> A2C.collect_rollouts: MultiInputPolicy forward, sample,
+        # env.step, buffer add), everything on the device: what an SB3-style trainer pays per rollout on this env
+        try:
+            from ewn_gym_b200.device_env import EWNDeviceVecEnv
+            from ewn_gym_b200.train import A2C
+            penv = EWNDeviceVecEnv(n7, 7, 3, seed=SEED + 7, shaped=True, env_id0=rank * n7, engine=e7)
+            a2c = A2C("MultiInputPolicy", penv, n_steps=T, seed=rank)
+            a2c.collect_rollouts(); torch.cuda.synchronize()
+            if dist: dist.barrier()
+            p0, p1, p2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            p0.record()
+            for _ in range(3):
+                a2c.collect_rollouts()
+            p1.record()
+            a2c.train()
+            p2.record(); torch.cuda.synchronize()
+            pms, tms = p0.elapsed_time(p1) / 3, p1.elapsed_time(p2)
+            if dist:
+                tt = torch.tensor([pms, tms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); pms, tms = tt.tolist()
+            rollout["with_policy"] = {"ms_per_rollout": pms, "env_steps_per_s": n7 * world * T / (pms / 1e3), "a2c_update_ms": tms,
+                                      "policy": "MultiInputPolicy (board + one-hot dice -> 64-64 Tanh towers), eager torch, actions written into the env's action tensor",
+                                      "episodes_last_rollout": a2c.logger.get("rollout/episodes")}
+            penv.close()
+        except Exception as err:                     # noqa: BLE001
+            rollout["with_policy"] = {"unavailable": str(err)[:200]}
+
         def rollout_stats(lo, hi):                  # one rollout of the games with global ids [lo, hi) from a fresh reset -> stats[4]
             m = hi - lo
             st = e7.reset(m, seed=SEED + 5, env_id0=lo)
