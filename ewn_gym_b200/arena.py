@@ -13,6 +13,7 @@ host-simulator test backend), policies are batched engine calls:
   RandomPolicy            ewn_random_action            uniform over the ordered legal list (random_policy.py:11-15)
   MinimaxPolicy(d, h)     ewn_expectiminimax           bit-exact ExpectiMinimaxAgent (minimax.py:19-93)
   MonteCarloPolicy(k)     ewn_mc_root_wins + best      flat Monte-Carlo "MCTS" (mcts.py:47-84), k playouts per root action
+  UctPolicy(r, b)         ewn_uct_search               UCB1 at the root, r rounds of b playouts (ucth_temp.py's intent)
 
 Finished games stay in the batch (their state is frozen) so that all calls keep a fixed shape.
 """
@@ -71,6 +72,21 @@ class MonteCarloPolicy(BatchPolicy):
             return engine.xp.asarray(a, "i32")
         wins, _ = engine.mc_root_wins(state, self.seed, 0, self.playouts, root_ids=rid)
         return engine.xp.asarray(engine.mc_best_action(state, wins), "i32")
+
+
+class UctPolicy(BatchPolicy):
+    """UCB1 over the root's legal moves with batched random playouts (Engine.uct_search): `rounds` x `batch` playouts per decision,
+    spent where the upper confidence bound is best instead of evenly as MonteCarloPolicy does"""
+
+    def __init__(self, rounds: int = 16, batch: int = 32, c: float = 1.41, seed: int = 0):
+        self.rounds, self.batch, self.c, self.seed = int(rounds), int(batch), float(c), int(seed)
+        self.name = f"uct({rounds}x{batch})"
+
+    def action(self, engine, state, ply):
+        n = int(state.shape[0])
+        rid = engine.xp.asarray((np.arange(n, dtype=np.int64) + ply * n).astype(np.uint32), "u32")     # fresh playout streams per ply
+        a, _, _ = engine.uct_search(state, self.seed, self.rounds, self.batch, self.c, root_ids=rid)
+        return engine.xp.asarray(a, "i32")
 
 
 def _is_torch(x):

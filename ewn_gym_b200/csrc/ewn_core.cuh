@@ -1317,4 +1317,58 @@ template <class C, class G> EWN_HD double emm2_root_serial(const Game<C>& root, 
     return best;
 }
 
+// ------------------------------------------------------------------------------------------------
+// UCT at the root (the intent of the reference's unfinished ucth_temp.py:6-89: expand the root's legal moves, pick the child with the best
+// UCB1 score, simulate from it, back the result up; final move = best win rate).  Batched: every round each root picks ONE child and
+// plays `batch` random playouts from it (mcts.py:24-41 playouts, BOTTOM_RIGHT to move), wins / visits are kept per legal-list position.
+//   score = wins / visits + c * sqrt(ln(total visits) / visits)   (ucth_temp.py:37-40, c = 1.41), unvisited children first, ties -> first.
+// ln(total) is passed in by the host (one libm, the same for the CUDA path and the host build); division and sqrt are IEEE-exact.
+// ------------------------------------------------------------------------------------------------
+EWN_HD double f64_sqrt(double a) {
+#if defined(__CUDA_ARCH__)
+    return __dsqrt_rn(a);
+#else
+    volatile double r = __builtin_sqrt(a); return r;
+#endif
+}
+// -> list position of the child to simulate next (n_children >= 1)
+EWN_HD int uct_select(const u32* wins, const u32* visits, int n_children, double c, double ln_total) {
+    int best = 0; double best_score = -f64_inf();
+    for (int j = 0; j < n_children; j++) {
+        double score;
+        if (visits[j] == 0) score = f64_inf();                                   // ucth_temp.py:35-36
+        else {
+            const double v = (double)visits[j];
+            score = f64_add(f64_div((double)wins[j], v), f64_mul(c, f64_sqrt(f64_div(ln_total, v))));
+        }
+        if (score > best_score) { best_score = score; best = j; }
+    }
+    return best;
+}
+// final move: the child with the best win rate (ucth_temp.py:76), first maximum; children never visited count as 0
+EWN_HD int uct_best(const u32* wins, const u32* visits, int n_children) {
+    int best = 0; double bv = -1.0;
+    for (int j = 0; j < n_children; j++) {
+        const double r = visits[j] ? f64_div((double)wins[j], (double)visits[j]) : 0.0;
+        if (r > bv) { bv = r; best = j; }
+    }
+    return best;
+}
+// One round for one root: fold the previous round's result in, pick the next child, hand its position out.  Returns the chosen list
+// position (or -1 for a finished root).  g = root (TOP_LEFT to move), child = position after the chosen move (BOTTOM_RIGHT to move).
+template <class C, class G> EWN_HD int uct_round(const Game<C>& g, const G& geo, u32* wins, u32* visits, int prev, u32 prev_wins, u32 batch,
+                                                  double c, double ln_total, Game<C>& child, int& n_children) {
+    n_children = 0;
+    if (full_win<C>(g, geo)) return -1;
+    const Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+    n_children = legal_count(l);
+    if (prev >= 0) { wins[prev] += prev_wins; visits[prev] += batch; }
+    const int j = uct_select(wins, visits, n_children, c, ln_total);
+    int la, di, sh; legal_pick(l, j, la, di, sh);
+    child = g;
+    apply_move<C, SIDE_TL>(child, sh, di);
+    child.player = SIDE_BR;
+    return j;
+}
+
 }  // namespace ewn

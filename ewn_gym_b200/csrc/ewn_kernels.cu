@@ -10,6 +10,7 @@
 // so there is no tensor-core path.  K1 streams 8 (5x5) or 16 (<=9x9) bytes of state per game with fully coalesced
 // vector accesses and stages observation rows through shared memory so that global stores are full 16-byte vectors.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdio.h>
 #include <string.h>
 #include <atomic>
@@ -1250,6 +1251,48 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     }
 }
 
+// UCT at the root, one thread per root and round (ewn_uct_search).  res = TOP_LEFT wins of the playouts of the previous round's child.
+template <class C> __global__ void __launch_bounds__(TPB) k_uct_round(const u64* state, const u32* root_ids, int64_t n, Geo geo, u32* wins, u32* visits,
+                                                                      int32_t* chosen, u32* res, u64* child, u32* child_rid, u32 batch, double c,
+                                                                      double ln_total, int first_round) {
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g, ch; unpack(g, state, i, geo);
+    g.player = SIDE_TL;
+    u32 w[6], v[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) { w[j] = first_round ? 0u : wins[i * 6 + j]; v[j] = first_round ? 0u : visits[i * 6 + j]; }
+    int nch;
+    setup<C>(ch, geo, 1);
+    const int j = uct_round<C>(g, geo, w, v, first_round ? -1 : chosen[i], res[i], batch, c, ln_total, ch, nch);
+#pragma unroll
+    for (int k = 0; k < 6; k++) { wins[i * 6 + k] = w[k]; visits[i * 6 + k] = v[k]; }
+    chosen[i] = j;
+    res[i] = 0u;
+    pack(ch, child, i, geo);                                  // a finished root hands out the initial position; its result is dropped
+    child_rid[i] = (root_ids ? root_ids[i] : (u32)i) * 6u + (u32)(j < 0 ? 0 : j);
+}
+template <class C> __global__ void __launch_bounds__(TPB) k_uct_final(const u64* state, int64_t n, Geo geo, u32* wins, u32* visits, const int32_t* chosen,
+                                                                      const u32* res, u32 batch, int8_t* action) {
+    const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+    if (i >= n) return;
+    Game<C> g; unpack(g, state, i, geo);
+    int la = -1, di = -1;
+    if (!full_win<C>(g, geo)) {
+        u32 w[6], v[6];
+#pragma unroll
+        for (int j = 0; j < 6; j++) { w[j] = wins[i * 6 + j]; v[j] = visits[i * 6 + j]; }
+        const int p = chosen[i];
+#pragma unroll
+        for (int j = 0; j < 6; j++) if (j == p) { w[j] += res[i]; v[j] += batch; }
+#pragma unroll
+        for (int j = 0; j < 6; j++) { wins[i * 6 + j] = w[j]; visits[i * 6 + j] = v[j]; }
+        const Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+        int sh; legal_pick(l, uct_best(w, v, legal_count(l)), la, di, sh);
+    }
+    if (action) { action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di; }
+}
+
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_best(const u64* state, const u32* wins, int8_t* action, int64_t n, Geo geo) {
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
@@ -1922,6 +1965,40 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     if (count == 0) return EWN_OK;
     return use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st)
                      : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st);
+}
+
+size_t ewn_uct_workspace(int64_t n) { return n <= 0 ? 0 : (size_t)n * (16 + 4 + 4 + 4) + 256; }
+
+int ewn_uct_search(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, int rounds, uint32_t batch, double c,
+                   uint32_t* wins, uint32_t* visits, int8_t* action, void* workspace, size_t workspace_bytes, void* stream) {
+    if (!state || !wins || !visits || n < 0 || !config_ok(N, L) || rounds < 1 || batch < 1) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;      // six-face die in the playouts (mcts.py:29)
+    if (n == 0) return EWN_OK;
+    if (n > ((int64_t)1 << 29)) return EWN_ENOSUP;        // root id * 6 + child is a 32-bit Philox stream id
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t need = ewn_uct_workspace(n);
+    if (!workspace || workspace_bytes == 0) { int rc = scratch_get(need, &workspace, st); if (rc) return rc; }
+    else if (workspace_bytes < need) return EWN_ESPACE;
+    Geo geo = make_geo(N, L);
+    char* w = (char*)workspace;
+    uint64_t* child = (uint64_t*)w;                       // n x 2 words
+    uint32_t* rid = (uint32_t*)(w + (size_t)n * 16);
+    uint32_t* res = rid + n;
+    int32_t* chosen = (int32_t*)(res + n);
+    CU(cudaMemsetAsync(res, 0, (size_t)n * 4, st));
+    for (int r = 0; r < rounds; r++) {
+        const double ln_total = r ? log((double)r * (double)batch) : 0.0;       // visits of the root so far; host libm on every path
+        if (use_p5(N)) k_uct_round<P5><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, wins, visits, chosen, res, child, rid, batch, c, ln_total, r == 0);
+        else           k_uct_round<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, wins, visits, chosen, res, child, rid, batch, c, ln_total, r == 0);
+        LAUNCHED("k_uct_round");
+        int rc = use_p5(N) ? launch_playouts<P5, true>(child, rid, nullptr, n, (uint32_t)r * batch, batch, res, nullptr, geo, seed, st)
+                           : launch_playouts<P8, true>(child, rid, nullptr, n, (uint32_t)r * batch, batch, res, nullptr, geo, seed, st);
+        if (rc) return rc;
+    }
+    if (use_p5(N)) k_uct_final<P5><<<blocks_for(n), TPB, 0, st>>>(state, n, geo, wins, visits, chosen, res, batch, action);
+    else           k_uct_final<P8><<<blocks_for(n), TPB, 0, st>>>(state, n, geo, wins, visits, chosen, res, batch, action);
+    LAUNCHED("k_uct_final");
+    return EWN_OK;
 }
 
 int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void* stream) {

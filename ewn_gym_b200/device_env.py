@@ -82,6 +82,8 @@ def resolve_opponent(opponent_policy, policy_kwargs):
         return arena.MinimaxPolicy(int(kw.get("max_depth", 3)), kw.get("heuristic", "hybrid"))
     if opponent_policy == ClassicalPolicy.mcts:
         return arena.MonteCarloPolicy(int(kw.get("num_simulations", 10)), int(kw.get("num_env_copies", 5)), seed=int(kw.get("seed", 0)))
+    if opponent_policy == ClassicalPolicy.uct:
+        return arena.UctPolicy(int(kw.get("rounds", 16)), int(kw.get("batch", 32)), float(kw.get("exploration_constant", 1.41)), seed=int(kw.get("seed", 0)))
     raise NotImplementedError(f"opponent_policy {opponent_policy!r}: AlphaZero / SB3-checkpoint opponents are out of scope (DESIGN.md 9)")
 
 

@@ -334,6 +334,16 @@ class Engine:
                                             self.xp.ptr(nch), self.xp.ptr(plies), None, 0, self.xp.stream()), "ewn_mc_root_wins")
         return w, nch
 
+    def uct_search(self, state, seed: int, rounds: int, batch: int = 32, c: float = 1.41, root_ids=None):
+        """UCT at the root over the legal moves with batched random playouts (ewn_uct_search; ucth_temp.py:6-89's intent).
+        -> (action i8[n,2], wins i32[n,6], visits i32[n,6])"""
+        n = self._n(state)
+        w, v, a = self.xp.zeros((n, 6), "u32"), self.xp.zeros((n, 6), "u32"), self.xp.empty((n, 2), "i8")
+        rid = self._opt(root_ids, "u32")
+        self._chk(self.lib.ewn_uct_search(self.xp.ptr(state), self.xp.ptr(rid), n, self.N, self.L, seed, int(rounds), int(batch), float(c),
+                                          self.xp.ptr(w), self.xp.ptr(v), self.xp.ptr(a), None, 0, self.xp.stream()), "ewn_uct_search")
+        return a, w, v
+
     def mc_best_action(self, state, wins):
         n = self._n(state)
         a = self.xp.empty((n, 2), "i8")

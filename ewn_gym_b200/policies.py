@@ -107,5 +107,30 @@ class MctsAgent(PolicyBase):
         return (None if a[0, 0] < 0 else np.array([int(a[0, 0]), int(a[0, 1])])), None
 
 
+class UctAgent(PolicyBase):
+    """ClassicalPolicy.uct (constants/policy.py:8; the reference's ucth_temp.py:6-89 never got past a sketch): UCB1 over the root's legal
+    moves, `iterations` random playouts per decision in rounds of `batch`, final move = best win rate."""
+
+    def __init__(self, cube_layer: int, board_size: int, iterations: int = 512, batch: int = 32, exploration_constant: float = 1.41,
+                 engine: Engine = None, seed: int = 0, **kwargs):
+        self.engine = engine if engine is not None else Engine(board_size, cube_layer)
+        self.board_size, self.seed, self._calls = board_size, int(seed), 0
+        self.batch, self.rounds, self.c = int(batch), max(1, int(iterations) // int(batch)), float(exploration_constant)
+
+    def predict_batch(self, board, dice_roll):
+        e = self.engine
+        st = e.encode(board, dice_roll)
+        n = len(board)
+        rid = (np.arange(n, dtype=np.int64) + self._calls).astype(np.uint32)
+        self._calls += n
+        a, w, v = e.uct_search(st, self.seed, self.rounds, self.batch, self.c, root_ids=rid)
+        return _host(a), (_host(w), _host(v))
+
+    def predict(self, obs, **kwargs):
+        board, dice = _obs_arrays(obs, self.board_size)
+        a, _ = self.predict_batch(board, dice)
+        return (None if a[0, 0] < 0 else np.array([int(a[0, 0]), int(a[0, 1])])), None
+
+
 def _host(x):
     return x if isinstance(x, np.ndarray) else x.detach().cpu().numpy()

@@ -262,6 +262,17 @@ EWN_API int ewn_mc_root_wins(const uint64_t *state, const uint32_t *root_ids, in
 EWN_API int ewn_mc_best_action(const uint64_t *state, const uint32_t *wins, int8_t *action, int64_t n, int board_size, int cube_layer,
                        void *stream);
 
+/* UCT at the root on top of the playout kernel (the intent of the reference's unfinished ucth_temp.py:6-89): `rounds` times,
+ * every root picks the legal move with the best UCB1 score wins/visits + c * sqrt(ln(total)/visits) (unvisited first, ties -> list order)
+ * and plays `batch` random playouts (mcts.py:24-41) from the position after it; the final move is the one with the best win rate.
+ * wins / visits: u32[n][6] by legal-list position (out; overwritten); action: int8[n][2] (or NULL; -1,-1 for a finished root).
+ * Playout streams are keyed (seed; root id * 6 + move, playout index), so results do not depend on how roots are batched or sharded.
+ * workspace: at least ewn_uct_workspace(n) bytes, or NULL / 0 for the library's per-stream scratch. */
+EWN_API size_t ewn_uct_workspace(int64_t n);
+EWN_API int ewn_uct_search(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed, int rounds,
+                   uint32_t batch, double c, uint32_t *wins, uint32_t *visits, int8_t *action, void *workspace, size_t workspace_bytes,
+                   void *stream);
+
 /* ---- root-statistics merge over NVLink peer memory (the one exchange step of the path) ----------- */
 /* mcts.py:59-68 sums the wins of all env copies and takes np.argmax.  With the playout range of every (root, action) split
  * over the GPUs of one node, that sum is an all-reduce of u32[n][6] followed by the arg-max.  ewn_mc_best_action_peers does

@@ -3,6 +3,7 @@
 // the CPU-only test tier can check the packed-state logic against the oracle before GPU time is spent, and so the
 // kernel bodies can be stepped in gdb / run under sanitizers.  Never loaded by the ewn_gym_b200 package; the
 // product has no CPU path (libewn_b200.so returns EWN_ECUDA without a device).
+#include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -225,6 +226,33 @@ template <class C> int t_playouts(const uint64_t* state, const uint32_t* root_id
             wins[i] += (u32)playout<C>(g, geo, seed, root_ids ? root_ids[i] : (u32)i, 7u, p, &pl);
             if (plies) *plies += (unsigned long long)pl;
         }
+    }
+    return EWN_OK;
+}
+
+template <class C> int t_uct(const uint64_t* state, const uint32_t* root_ids, int64_t n, const Geo& geo, u64 seed, int rounds, u32 batch, double c,
+                             uint32_t* wins, uint32_t* visits, int8_t* action) {
+    for (int64_t i = 0; i < n; i++) {
+        Game<C> g, ch; unpack(g, state, i, geo); g.player = SIDE_TL;
+        u32 w[6] = {0, 0, 0, 0, 0, 0}, v[6] = {0, 0, 0, 0, 0, 0}, res = 0;
+        int prev = -1, nch = 0;
+        const u32 rid = root_ids ? root_ids[i] : (u32)i;
+        for (int r = 0; r < rounds; r++) {
+            const double ln_total = r ? log((double)r * (double)batch) : 0.0;
+            const int j = uct_round<C>(g, geo, w, v, prev, res, batch, c, ln_total, ch, nch);
+            if (j < 0) break;
+            res = 0;
+            for (u32 p = (u32)r * batch; p < (u32)(r + 1) * batch; p++) res += (u32)playout<C>(ch, geo, seed, rid * 6u + (u32)j, 7u, p, nullptr);
+            prev = j;
+        }
+        int la = -1, di = -1;
+        if (prev >= 0) {
+            w[prev] += res; v[prev] += batch;
+            const Legal l = legal<C, SIDE_TL>(g, geo, movers<C>(g.tl, g.dice));
+            int sh; legal_pick(l, uct_best(w, v, legal_count(l)), la, di, sh);
+        }
+        for (int j = 0; j < 6; j++) { wins[i * 6 + j] = w[j]; visits[i * 6 + j] = v[j]; }
+        if (action) { action[2 * i] = (int8_t)la; action[2 * i + 1] = (int8_t)di; }
     }
     return EWN_OK;
 }
@@ -500,6 +528,15 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     if (L != 3) return EWN_ENOSUP;
     Geo geo = make_geo(N, L);
     return BY_CODEC(N, t_mc<P5>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies), t_mc<P8>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies));
+}
+size_t ewn_uct_workspace(int64_t) { return 0; }
+int ewn_uct_search(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, int rounds, uint32_t batch, double c,
+                   uint32_t* wins, uint32_t* visits, int8_t* action, void*, size_t, void*) {
+    if (!state || !wins || !visits || n < 0 || !config_ok(N, L) || rounds < 1 || batch < 1) return EWN_EARG;
+    if (L != 3) return EWN_ENOSUP;
+    Geo geo = make_geo(N, L);
+    return BY_CODEC(N, t_uct<P5>(state, root_ids, n, geo, seed, rounds, batch, c, wins, visits, action),
+                    t_uct<P8>(state, root_ids, n, geo, seed, rounds, batch, c, wins, visits, action));
 }
 int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void*) {
     if (!state || !wins || !action || n < 0 || !config_ok(N, L)) return EWN_EARG;
