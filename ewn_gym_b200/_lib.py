@@ -12,7 +12,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libewn_b200.so")
+# EWN_B200_LIB: load another build of the same sources instead (the -DEWN_CHECKS build of tools/checked_build.sh, experiment variants)
+LIB_PATH = os.environ.get("EWN_B200_LIB") or os.path.join(CSRC, "libewn_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xlinker", "--exclude-libs,ALL"]
 
@@ -110,6 +111,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile libewn_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
     srcs = [os.path.join(CSRC, "ewn_kernels.cu"), os.path.join(CSRC, "ewn_core.cuh"),
             os.path.join(os.path.dirname(_HERE), "include", "ewn_b200.h")]
+    if os.environ.get("EWN_B200_LIB"):
+        return LIB_PATH
     if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs):
         return LIB_PATH
     cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB_PATH, srcs[0]]

@@ -1275,6 +1275,9 @@ template <bool TAB, class C, class G> EWN_HD double emm2_min(const EmmChild<C>& 
             if (TAB) {
                 idx = hist_best(h_tl) * (36 * N) + hist_best(h_br) * 6 + kbase - (cap_t ? 6 * N : 0) - (cap_b ? 1 : 0);
                 idx = over ? -1 : idx;                                         // entry -1: minimax_ewn.py:45-47, -10
+#if defined(EWN_CHECKS) && defined(__CUDA_ARCH__)
+                if (idx < -emm_pad(N) || idx >= emm_tab_entries(N)) { printf("EWN_CHECK failed: value-table index %d\n", idx); __trap(); }
+#endif
                 v = tb.v[idx];
             } else {
                 v = over ? -10.0 : emm_summary_value(heuristic, N, h_tl, pc - (cap_t ? 1 : 0), h_br, nc - (cap_b ? 1 : 0), fold);

@@ -30,6 +30,15 @@ constexpr int WARPS = TPB / 32;
 thread_local char g_err[256] = "";
 std::atomic<long long> g_launches{0};
 
+// -DEWN_CHECKS: bounds assertions of our own on the hand-rolled indexing (compute-sanitizer is closed on the GPU pool: profiles/
+// r2_sanitize_unavailable.txt).  A violated check traps, the launch fails with an error and every test that follows fails loudly.
+// tools/checked_build.sh builds build/checked/libewn_b200.so; EWN_B200_LIB=<that file> makes the test-suite load it.
+#if defined(EWN_CHECKS)
+#define EWN_CHECK(cond) do { if (!(cond)) { printf("EWN_CHECK failed: %s (%s:%d) block %d thread %d\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define EWN_CHECK(cond) do { } while (0)
+#endif
+
 inline int cuda_fail(cudaError_t e, const char* what) {
     snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
     return EWN_ECUDA;
@@ -472,6 +481,7 @@ k_step(const __grid_constant__ StepKArgs ka) {
     }
     __syncthreads();
     const int64_t row0 = (int64_t)s_row0;
+    EWN_CHECK(F <= STPB && row0 >= 0 && row0 + F <= a.term_index_base + n);      // the caller's terminal arrays hold one row per game
     const int head = (int)(((unsigned)row0 * (unsigned)NN) & 7u);
     if ((int)tid < F) {
         Game<C> t; unpack(t, s_term, (long)tid, geo);
@@ -615,10 +625,12 @@ template <class C, int NT> __device__ __noinline__ void vstep_flush(int16_t* ter
         const int head = (int)(((unsigned)rowc * (unsigned)NN) & 7u);   // 16-byte phase of the destination
         uint4* v = reinterpret_cast<uint4*>(smb);
         const int nvec = (head + Fc * NN + 7) >> 3;
+        EWN_CHECK(nvec * 8 <= VTPB * NN + 16 && rowc >= 0);            // the staging tile: VTPB rows + 32 bytes of slack
         if (term_board) for (int k = tid; k < nvec; k += VTPB) v[k] = make_uint4(0, 0, 0, 0);
         __syncthreads();
         if (tid < Fc) {
             const int e = src(r0 + tid);
+            EWN_CHECK(e >= 0 && (unsigned)e < seg * (VTPB / 32));
             Game<C> t; unpack(t, s_term, (long)e);
             if (term_dice) __stcs(reinterpret_cast<long long*>(term_dice) + rowc + tid, (long long)t.dice);
             __stcs(term_index + rowc + tid, (int32_t)(index_base + (int64_t)(s_who[e] & 0x3FFFFFFFu)));
@@ -754,6 +766,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
             if (done) {                                            // warp-uniform; no atomics, the counter lives in a register
                 if (compact && fin) {
                     const unsigned k = (unsigned)warp * seg + wcnt + (unsigned)__popc(done & ((1u << lane) - 1u));
+                    EWN_CHECK(k < ((unsigned)warp + 1u) * seg && k < (unsigned)cap);       // the warp's own segment of the list
                     pack(term, s_term, (long)k);
                     s_who[k] = (u32)i | ((u32)(out.code - 1) << 30);        // i < 2^30; the result code (1..4) rides in the top bits
                 }
