@@ -309,10 +309,12 @@ def run_ours(args, rank, world, local_rank):
         a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
         def decide_nccl(it, count, pl=None):
-            wins.zero_()
-            _, k = e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=wins, plies=pl)
-            if dist: dist.all_reduce(wins)        # root statistics merge
-            return e.mc_best_action(roots, wins), k
+            # one rank: ewn_mc_predict = expand (clears wins) -> playouts -> arg-max, three PDL-chained launches, no memsets
+            a_, _, k = e.mc_predict(roots, seed=SEED + it, first=rank * per, count=count, wins=wins, plies=pl, want_action=not dist)
+            if dist:
+                dist.all_reduce(wins)             # root statistics merge
+                a_ = e.mc_best_action(roots, wins)
+            return a_, k
 
         def timed(fn):
             fn(0, 8)                              # warm-up
@@ -339,7 +341,7 @@ def run_ours(args, rank, world, local_rank):
                 ex, merge = None, {"kind": "NCCL all-reduce + k_mc_best", "ms": nccl_ms, "peer_memory": f"unavailable: {err}"[:300]}
             if ex is not None:
                 def decide_peers(it, count):
-                    e.mc_root_wins(roots, seed=SEED + it, first=rank * per, count=count, wins=ex.wins_buffer())
+                    e.mc_predict(roots, seed=SEED + it, first=rank * per, count=count, wins=ex.wins_buffer(zero=False), want_action=False)
                     return ex.best_action(roots)
 
                 decide_peers(0, 8); decide_peers(0, 8)    # maps the peers' memory on first touch
@@ -378,7 +380,7 @@ def run_ours(args, rank, world, local_rank):
             merge["identity_check"] = f"rank 0 alone: {sub} roots x all actions x {per * world} playouts == merged counters of {world} ranks"
         n_pairs = int(nch.sum().item())
         playout = {"value": n_pairs * 1024 / (pms / 1e3), "unit": "playouts/s", "ms": pms, "roots": roots_n, "root_children": n_pairs,
-                   "playouts_per_child": 1024, "decisions_timed": iters, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
+                   "playouts_per_child": 1024, "decisions_timed": iters, "launches_per_decision": 3, "plies_per_playout": float(plies.item()) / max(1, n_pairs * 1024), "merge": merge}
         try:    # on-chip kernel: the roofline is the SM issue rate; instructions per ply come from the committed ncu capture
             prof = json.load(open(os.path.join(ROOT, "profiles", "k_playouts_issue.json")))
             wi = prof["warp_instructions_per_ply"] * float(plies.item()) / (pms / 1e3)

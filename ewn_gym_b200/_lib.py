@@ -90,6 +90,7 @@ PROTOTYPES = {
     "ewn_mc_root_wins": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
     "ewn_uct_workspace": (C.c_size_t, [i64]),
     "ewn_uct_search": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, C.c_int, u32, C.c_double, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
+    "ewn_mc_predict": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
     "ewn_mc_best_action": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_vec_create": (C.c_int, [C.POINTER(VecConfig), C.POINTER(p_void)]),
     "ewn_vec_destroy": (None, [p_void]),

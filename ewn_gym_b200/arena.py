@@ -70,8 +70,8 @@ class MonteCarloPolicy(BatchPolicy):
             from .sharding import mc_predict_peers
             a, _ = mc_predict_peers(engine, self.exchange, state, self.seed, self.playouts, root_ids=rid)
             return engine.xp.asarray(a, "i32")
-        wins, _ = engine.mc_root_wins(state, self.seed, 0, self.playouts, root_ids=rid)
-        return engine.xp.asarray(engine.mc_best_action(state, wins), "i32")
+        a, _, _ = engine.mc_predict(state, self.seed, 0, self.playouts, root_ids=rid)
+        return engine.xp.asarray(a, "i32")
 
 
 class UctPolicy(BatchPolicy):

@@ -1141,10 +1141,20 @@ template <> struct PairRec<P8> {
 
 // `count`: playouts this launch sequence will play per pair.  A child that already ends the game (the agent's move wins,
 // mcts.py:28: the playout loop body never runs) is settled here -- all its playouts have the same result -- and gets no record.
+// zero_wins: the root's six counters are cleared here first (ewn_mc_predict: no memset launch before the decision).
+// The three kernels of a decision (expand -> playouts -> arg-max) are launched with programmatic dependent launch: each lets its
+// successor become resident early (griddepcontrol.launch_dependents) and touches global memory only after its predecessor has
+// completed (griddepcontrol.wait); both instructions are no-ops in a launch without the attribute.
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_expand(const u64* state, const u32* root_ids, int64_t n, Geo geo,
-                                                                      PairBuf pb, int32_t* n_children, u32 count, u32* wins) {
+                                                                      PairBuf pb, int32_t* n_children, u32 count, u32* wins, int zero_wins) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
+    if (zero_wins) {
+        uint2* w2 = reinterpret_cast<uint2*>(wins + i * 6);
+        w2[0] = make_uint2(0, 0); w2[1] = make_uint2(0, 0); w2[2] = make_uint2(0, 0);
+    }
     Game<C> g; unpack(g, state, i, geo);
     g.player = SIDE_TL;
     int cnt = 0;
@@ -1183,16 +1193,26 @@ inline Div31 make_div31(u32 d) {
 // result slot = index, and a state that is already finished is settled when it is picked up.
 // otherwise: `pairs` are the records k_mc_expand wrote (never finished states).
 // n_pairs * count < 2^31 (the host slices larger jobs), so all game indexing is 32-bit.
+// reset_hdr != nullptr: {pair counter, ticket} of the workspace header -- the last block to finish puts both back to zero, so the next
+// decision's k_mc_expand finds a clean counter without a memset launch (every block has read the counter before it can finish).
 template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playouts(const void* pairs, const u32* root_ids, const int* n_pairs_dev,
                                                                                   u32 n_pairs_host, u32 first, u32 count, Div31 dv, u32* wins,
-                                                                                  unsigned long long* plies, Geo geo, const RoundKeys rk) {
+                                                                                  unsigned long long* plies, Geo geo, const RoundKeys rk, int* reset_hdr) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
+    asm volatile("griddepcontrol.launch_dependents;");
     const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);       // legal directions of a cube: one LDS (two cubes per ply)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const u32 warp_id = (blockIdx.x * TPB + threadIdx.x) >> 5;
     const u32 n_warps = (gridDim.x * TPB) >> 5;
     const u32 n_pairs = n_pairs_dev ? (u32)*n_pairs_dev : n_pairs_host;
+    auto finish = [&]() {                                        // one ticket per warp; every warp has read the counter above
+        if (reset_hdr && lane == 0) {
+            __threadfence();
+            if (atomicAdd(reset_hdr + 1, 1) == (int)n_warps - 1) { reset_hdr[0] = 0; reset_hdr[1] = 0; }
+        }
+    };
     const u32 total = n_pairs * count;
     // Games are dealt to warps in chunks of CH consecutive games, round-robin (chunk c belongs to warp c % n_warps): playout
     // length depends on the root position, so a warp that owned ONE contiguous range of ~1,500 games of one or two roots
@@ -1204,7 +1224,7 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     const u32 my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
     u32 tnext = 0;                                             // warp-uniform cursor over the warp's local game indices
     const u32 tend = my_chunks * CH;
-    if (tend == 0) return;
+    if (tend == 0) { finish(); return; }
 
     Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
     bool busy = false;
@@ -1262,6 +1282,7 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
         for (int o = 16; o > 0; o >>= 1) my_plies += __shfl_xor_sync(0xffffffffu, my_plies, o);
         if (lane == 0) atomicAdd(plies, my_plies);
     }
+    finish();
 }
 
 // UCT at the root, one thread per root and round (ewn_uct_search).  res = TOP_LEFT wins of the playouts of the previous round's child.
@@ -1307,6 +1328,7 @@ template <class C> __global__ void __launch_bounds__(TPB) k_uct_final(const u64*
 }
 
 template <class C> __global__ void __launch_bounds__(TPB) k_mc_best(const u64* state, const u32* wins, int8_t* action, int64_t n, Geo geo) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
     Game<C> g; unpack(g, state, i, geo);
@@ -1394,26 +1416,29 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 // One allocation per (device, stream): calls on different streams never share scratch, so ewn_expectiminimax / ewn_mc_root_wins
 // without a caller workspace are safe from several host threads as long as each thread uses its own stream (calls on ONE stream
 // are ordered by the stream).  The table itself is guarded by a mutex; growing an entry waits for that stream only.
-struct Scratch { int dev = -1; cudaStream_t st = nullptr; void* p = nullptr; size_t bytes = 0; };
+struct Scratch { int dev = -1; cudaStream_t st = nullptr; int kind = 0; void* p = nullptr; size_t bytes = 0; };
 constexpr int MAX_SCRATCH = 256;
 Scratch g_scratch[MAX_SCRATCH];
 int g_scratch_n = 0;
 std::mutex g_scratch_mutex;
 
-int scratch_get(size_t bytes, void** out, cudaStream_t st) {
+// kind 1 = the Monte-Carlo workspace: its 256-byte header {pair counter, ticket} is zero whenever no decision is in flight (cleared
+// when allocated, put back by the last warp of k_playouts), so ewn_mc_predict / ewn_mc_root_wins launch no memset for it
+int scratch_get(size_t bytes, void** out, cudaStream_t st, int kind = 0) {
     int dev = 0;
     CU(cudaGetDevice(&dev));
     std::lock_guard<std::mutex> lock(g_scratch_mutex);
     Scratch* s = nullptr;
-    for (int i = 0; i < g_scratch_n; i++) if (g_scratch[i].dev == dev && g_scratch[i].st == st) { s = &g_scratch[i]; break; }
+    for (int i = 0; i < g_scratch_n; i++) if (g_scratch[i].dev == dev && g_scratch[i].st == st && g_scratch[i].kind == kind) { s = &g_scratch[i]; break; }
     if (!s) {
         if (g_scratch_n == MAX_SCRATCH) return EWN_ESPACE;            // pass a workspace instead
-        s = &g_scratch[g_scratch_n++]; s->dev = dev; s->st = st;
+        s = &g_scratch[g_scratch_n++]; s->dev = dev; s->st = st; s->kind = kind;
     }
     if (s->bytes < bytes) {
         if (s->p) { CU(cudaStreamSynchronize(st)); CU(cudaFree(s->p)); s->p = nullptr; s->bytes = 0; }
         CU(cudaMalloc(&s->p, bytes));
         s->bytes = bytes;
+        if (kind == 1) CU(cudaMemsetAsync(s->p, 0, 256, st));
     }
     *out = s->p;
     return EWN_OK;
@@ -1450,16 +1475,32 @@ template <class C> int playout_grid(int64_t total_games) {
 
 // k_playouts indexes games with 32 bits: a job of 2^31 games or more runs as several launches over slices of the playout
 // index range (results depend only on the global playout index, so the slicing is invisible)
+// kernel launch with the programmatic-dependent-launch attribute (pdl) or a plain one
+template <class... KArgs, class... Args>
+static cudaError_t launch_k(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st, bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 template <class C, bool DIRECT>
 static int launch_playouts(const void* pairs, const uint32_t* root_ids, const int* n_pairs_dev, int64_t max_pairs, uint32_t first, uint32_t count,
-                           uint32_t* wins, unsigned long long* plies, const Geo& geo, uint64_t seed, cudaStream_t st) {
+                           uint32_t* wins, unsigned long long* plies, const Geo& geo, uint64_t seed, cudaStream_t st, int* reset_hdr = nullptr,
+                           bool pdl = false) {
     const RoundKeys rk = make_round_keys(seed);
     const int64_t lim = (((int64_t)1 << 31) - 256) / (max_pairs > 0 ? max_pairs : 1);
     if (lim < 1) return EWN_ENOSUP;                       // more than 2^31 pairs in one call
     for (uint64_t done = 0; done < count;) {
         const uint32_t c = (uint32_t)((count - done) < (uint64_t)lim ? (count - done) : (uint64_t)lim);
         const int grid = playout_grid<C>(max_pairs * (int64_t)c);
-        k_playouts<C, DIRECT><<<grid, TPB, 0, st>>>(pairs, root_ids, n_pairs_dev, (u32)max_pairs, first + (uint32_t)done, c, make_div31(c), wins, plies, geo, rk);
+        const bool last = done + c >= count;
+        CU(launch_k(k_playouts<C, DIRECT>, (unsigned)grid, TPB, 0, st, pdl && done == 0, pairs, root_ids, n_pairs_dev, (u32)max_pairs, first + (uint32_t)done, c,
+                    make_div31(c), wins, plies, geo, rk, last ? reset_hdr : (int*)nullptr));
         LAUNCHED("k_playouts");
         done += c;
     }
@@ -1954,30 +1995,56 @@ int ewn_playouts(const uint64_t* state, const uint32_t* root_ids, int64_t n, int
                      : launch_playouts<P8, true>(state, root_ids, nullptr, n, first, count, wins, plies, geo, seed, st);
 }
 
-int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
-                     uint32_t* wins, int32_t* n_children, unsigned long long* plies, void* workspace, size_t workspace_bytes, void* stream) {
+// expand -> playouts (-> arg-max): the launches of one Monte-Carlo decision.  predict: wins are cleared by the expansion, the arg-max
+// follows when `action` is given, and the three launches are chained with programmatic dependent launch.
+static int mc_run(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                  uint32_t* wins, int32_t* n_children, unsigned long long* plies, int8_t* action, void* workspace, size_t workspace_bytes,
+                  cudaStream_t st, bool predict) {
     if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
     if (L != 3) return EWN_ENOSUP;
     if (n == 0) return EWN_OK;
     if (n > ((int64_t)1 << 28)) return EWN_ENOSUP;        // slot * 8 + child is a 32-bit word
     const size_t need = ewn_mc_workspace(n);
+    bool own = false;
     if (!workspace || workspace_bytes == 0) {
-        int rc = scratch_get(need, &workspace, (cudaStream_t)stream);
+        int rc = scratch_get(need, &workspace, st, 1);
         if (rc) return rc;
+        own = true;
     } else if (workspace_bytes < need) return EWN_ESPACE;
     Geo geo = make_geo(N, L);
-    cudaStream_t st = (cudaStream_t)stream;
     char* w = (char*)workspace;
     PairBuf pb;
     pb.n_pairs = (int*)w;
     pb.rec = w + 256;
-    CU(cudaMemsetAsync(pb.n_pairs, 0, sizeof(int), st));
-    if (use_p5(N)) k_mc_expand<P5><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children, count, wins);
-    else           k_mc_expand<P8><<<blocks_for(n), TPB, 0, st>>>(state, root_ids, n, geo, pb, n_children, count, wins);
+    // the library's own workspace keeps its header clean between decisions; a caller's buffer is cleared here
+    const bool hdr_clean = own && count != 0;
+    if (!hdr_clean) CU(cudaMemsetAsync(pb.n_pairs, 0, 2 * sizeof(int), st));
+    const bool pdl = predict;
+    if (use_p5(N)) CU(launch_k(k_mc_expand<P5>, blocks_for(n), TPB, 0, st, false, state, root_ids, n, geo, pb, n_children, count, wins, predict ? 1 : 0));
+    else           CU(launch_k(k_mc_expand<P8>, blocks_for(n), TPB, 0, st, false, state, root_ids, n, geo, pb, n_children, count, wins, predict ? 1 : 0));
     LAUNCHED("k_mc_expand");
-    if (count == 0) return EWN_OK;
-    return use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st)
-                     : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st);
+    if (count != 0) {
+        int rc = use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, pb.n_pairs, pdl)
+                           : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, pb.n_pairs, pdl);
+        if (rc) return rc;
+    }
+    if (predict && action) {
+        if (use_p5(N)) CU(launch_k(k_mc_best<P5>, blocks_for(n), TPB, 0, st, pdl, state, (const u32*)wins, action, n, geo));
+        else           CU(launch_k(k_mc_best<P8>, blocks_for(n), TPB, 0, st, pdl, state, (const u32*)wins, action, n, geo));
+        LAUNCHED("k_mc_best");
+    }
+    return EWN_OK;
+}
+
+int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                     uint32_t* wins, int32_t* n_children, unsigned long long* plies, void* workspace, size_t workspace_bytes, void* stream) {
+    return mc_run(state, root_ids, n, N, L, seed, first, count, wins, n_children, plies, nullptr, workspace, workspace_bytes, (cudaStream_t)stream, false);
+}
+
+int ewn_mc_predict(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                   uint32_t* wins, int8_t* action, int32_t* n_children, unsigned long long* plies, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+    return mc_run(state, root_ids, n, N, L, seed, first, count, wins, n_children, plies, action, workspace, workspace_bytes, (cudaStream_t)stream, true);
 }
 
 size_t ewn_uct_workspace(int64_t n) { return n <= 0 ? 0 : (size_t)n * (16 + 4 + 4 + 4) + 256; }

@@ -334,6 +334,18 @@ class Engine:
                                             self.xp.ptr(nch), self.xp.ptr(plies), None, 0, self.xp.stream()), "ewn_mc_root_wins")
         return w, nch
 
+    def mc_predict(self, state, seed: int, first: int, count: int, root_ids=None, wins=None, plies=None, want_action=True):
+        """MctsAgent.predict in one call (ewn_mc_predict): `wins` is overwritten, no memset launches, expand -> playouts -> arg-max chained
+        with programmatic dependent launch.  -> (action i8[n,2] or None, wins i32[n,6], n_children i32[n])"""
+        n = self._n(state)
+        w = self.xp.empty((n, 6), "u32") if wins is None else wins
+        a = self.xp.empty((n, 2), "i8") if want_action else None
+        nch = self.xp.empty((n,), "i32")
+        rid = self._opt(root_ids, "u32")
+        self._chk(self.lib.ewn_mc_predict(self.xp.ptr(state), self.xp.ptr(rid), n, self.N, self.L, seed, first, count, self.xp.ptr(w), self.xp.ptr(a),
+                                          self.xp.ptr(nch), self.xp.ptr(plies), None, 0, self.xp.stream()), "ewn_mc_predict")
+        return a, w, nch
+
     def uct_search(self, state, seed: int, rounds: int, batch: int = 32, c: float = 1.41, root_ids=None):
         """UCT at the root over the legal moves with batched random playouts (ewn_uct_search; ucth_temp.py:6-89's intent).
         -> (action i8[n,2], wins i32[n,6], visits i32[n,6])"""

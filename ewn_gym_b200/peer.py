@@ -123,9 +123,11 @@ class PeerExchange:
                           for par in (0, 1)]
 
     # ------------------------------------------------------------------
-    def wins_buffer(self):
-        """zeroed u32[n, 6] of the NEXT epoch (pass it to Engine.mc_root_wins(wins=...))"""
+    def wins_buffer(self, zero: bool = True):
+        """u32[n, 6] of the NEXT epoch, zeroed unless the producer overwrites it (Engine.mc_predict(wins=...) clears it in its own kernel)"""
         w = self._wins[(self.epoch + 1) & 1]
+        if not zero:
+            return w
         if hasattr(w, "zero_"):
             w.zero_()
         else:

@@ -74,8 +74,8 @@ def mc_predict_peers(engine, exchange, state, seed: int, playouts_per_action: in
     -> (action int8[n][2], wins u32[n][6]); identical on every rank and identical to mc_predict_sharded.
     check=True raises if the wait for the peers timed out (that costs a device synchronisation; arena.play_matches checks at its own)."""
     lo, hi = split_range(playouts_per_action, exchange.rank, exchange.world)
-    w = exchange.wins_buffer()
-    engine.mc_root_wins(state, seed, first + lo, hi - lo, root_ids=root_ids, wins=w)
+    w = exchange.wins_buffer(zero=False)                      # three launches per decision: expand (clears w), playouts, merge + arg-max
+    engine.mc_predict(state, seed, first + lo, hi - lo, root_ids=root_ids, wins=w, want_action=False)
     out = exchange.best_action(state)
     if check:                                    # synchronises; a timed-out wait also shows as action (-1, -1) on every root
         exchange.check()

@@ -258,6 +258,13 @@ EWN_API size_t ewn_mc_workspace(int64_t n);
 EWN_API int ewn_mc_root_wins(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
                      uint32_t first, uint32_t count, uint32_t *wins, int32_t *n_children, unsigned long long *plies,
                      void *workspace, size_t workspace_bytes, void *stream);
+/* MctsAgent.predict (mcts.py:47-69) as ONE call: wins u32[n][6] is OVERWRITTEN (cleared by the expansion kernel, no memset launch), the
+ * playouts [first, first+count) are played and, when action != NULL, the first arg-max is taken -- three kernels chained with
+ * programmatic dependent launch; with the library's own workspace (workspace == NULL) nothing else is launched.  action == NULL leaves
+ * the arg-max to the caller (ewn_mc_best_action_peers when the playout range is split over GPUs). */
+EWN_API int ewn_mc_predict(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
+                   uint32_t first, uint32_t count, uint32_t *wins, int8_t *action, int32_t *n_children, unsigned long long *plies,
+                   void *workspace, size_t workspace_bytes, void *stream);
 /* first arg-max over the legal children (np.argmax, mcts.py:68) -> action int8[n][2] */
 EWN_API int ewn_mc_best_action(const uint64_t *state, const uint32_t *wins, int8_t *action, int64_t n, int board_size, int cube_layer,
                        void *stream);

@@ -529,6 +529,15 @@ int ewn_mc_root_wins(const uint64_t* state, const uint32_t* root_ids, int64_t n,
     Geo geo = make_geo(N, L);
     return BY_CODEC(N, t_mc<P5>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies), t_mc<P8>(state, root_ids, n, geo, seed, first, count, wins, n_children, plies));
 }
+int ewn_mc_best_action(const uint64_t* state, const uint32_t* wins, int8_t* action, int64_t n, int N, int L, void*);
+int ewn_mc_predict(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                   uint32_t* wins, int8_t* action, int32_t* n_children, unsigned long long* plies, void* ws, size_t wsb, void* st) {
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    memset(wins, 0, sizeof(uint32_t) * 6 * (size_t)n);
+    int rc = ewn_mc_root_wins(state, root_ids, n, N, L, seed, first, count, wins, n_children, plies, ws, wsb, st);
+    if (rc || !action) return rc;
+    return ewn_mc_best_action(state, wins, action, n, N, L, st);
+}
 size_t ewn_uct_workspace(int64_t) { return 0; }
 int ewn_uct_search(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, int rounds, uint32_t batch, double c,
                    uint32_t* wins, uint32_t* visits, int8_t* action, void*, size_t, void*) {

@@ -474,3 +474,19 @@ def test_playout_jobs_beyond_2_31_games_are_sliced(backend):
     parts = e.playouts(st, seed=6, first=0, count=30_000)
     parts = e.playouts(st, seed=6, first=30_000, count=30_000, wins=parts)
     assert np.array_equal(to_np(whole), to_np(parts))
+
+
+def test_mc_predict_equals_root_wins_then_best(backend):
+    """ewn_mc_predict (wins cleared in the expansion kernel, three chained launches, self-resetting pair counter) == zero + ewn_mc_root_wins +
+    ewn_mc_best_action, repeatedly on the same workspace and with a dirty wins buffer"""
+    e = make_engine(backend, 5, 3)
+    n = 300 if backend == "hostsim" else 5000
+    st = e.reset(n, seed=8)
+    for s in range(1, 6):
+        e.step(st, None, seed=8, step=s, agent_random=True, autoreset=(s != 5), want=())
+    wins = e.xp.asarray(np.full((n, 6), 12345, np.uint32), "u32")
+    for it in range(4):
+        a, w, nch = e.mc_predict(st, seed=it, first=3, count=24, wins=wins)
+        w0, nch0 = e.mc_root_wins(st, seed=it, first=3, count=24)
+        assert np.array_equal(to_np(w), to_np(w0)) and np.array_equal(to_np(nch), to_np(nch0)), it
+        assert np.array_equal(to_np(a), to_np(e.mc_best_action(st, w0)))
