@@ -2017,15 +2017,24 @@ static int mc_run(const uint64_t* state, const uint32_t* root_ids, int64_t n, in
     pb.n_pairs = (int*)w;
     pb.rec = w + 256;
     // the library's own workspace keeps its header clean between decisions; a caller's buffer is cleared here
+#if defined(EWN_MC_NO_TICKET)      /* experiment build: memset per decision instead of the self-resetting counter */
+    const bool hdr_clean = false;
+#else
     const bool hdr_clean = own && count != 0;
+#endif
     if (!hdr_clean) CU(cudaMemsetAsync(pb.n_pairs, 0, 2 * sizeof(int), st));
+#if defined(EWN_MC_NO_PDL)         /* experiment build: plain stream order between the three kernels */
+    const bool pdl = false;
+#else
     const bool pdl = predict;
+#endif
     if (use_p5(N)) CU(launch_k(k_mc_expand<P5>, blocks_for(n), TPB, 0, st, false, state, root_ids, n, geo, pb, n_children, count, wins, predict ? 1 : 0));
     else           CU(launch_k(k_mc_expand<P8>, blocks_for(n), TPB, 0, st, false, state, root_ids, n, geo, pb, n_children, count, wins, predict ? 1 : 0));
     LAUNCHED("k_mc_expand");
     if (count != 0) {
-        int rc = use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, pb.n_pairs, pdl)
-                           : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, pb.n_pairs, pdl);
+        int* hdr = hdr_clean ? pb.n_pairs : nullptr;
+        int rc = use_p5(N) ? launch_playouts<P5, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, hdr, pdl)
+                           : launch_playouts<P8, false>(pb.rec, nullptr, pb.n_pairs, n * 6, first, count, wins, plies, geo, seed, st, hdr, pdl);
         if (rc) return rc;
     }
     if (predict && action) {

@@ -56,7 +56,9 @@ class MultiInputActorCritic(nn.Module):
 
     def _dists(self, f):
         logits = self.action_net(self.pi(f))
-        return th.distributions.Categorical(logits=logits[:, :2]), th.distributions.Categorical(logits=logits[:, 2:])
+        # validate_args=False: the default validation reads the logits back on the host (a device synchronisation per step)
+        return (th.distributions.Categorical(logits=logits[:, :2], validate_args=False),
+                th.distributions.Categorical(logits=logits[:, 2:], validate_args=False))
 
     def forward(self, obs, deterministic: bool = False):
         """-> (actions int64[n, 2], values f32[n], log_prob f32[n])"""
