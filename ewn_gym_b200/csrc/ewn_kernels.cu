@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <atomic>
 #include <mutex>
@@ -1195,7 +1196,11 @@ inline Div31 make_div31(u32 d) {
 // n_pairs * count < 2^31 (the host slices larger jobs), so all game indexing is 32-bit.
 // reset_hdr != nullptr: {pair counter, ticket} of the workspace header -- the last block to finish puts both back to zero, so the next
 // decision's k_mc_expand finds a clean counter without a memset launch (every block has read the counter before it can finish).
-template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playouts(const void* pairs, const u32* root_ids, const int* n_pairs_dev,
+// DYN (needs reset_hdr): chunks beyond a warp's first one are handed out by an atomic counter in the workspace header (word 2) instead
+// of round-robin -- a warp that draws short games takes more chunks, so all warps finish within about one game of each other; the next
+// chunk's number is fetched one chunk ahead (the atomic's result is first read when the current chunk runs out).  Which warp plays a
+// game does not matter: results depend only on (root id, child, playout index).
+template <class C, bool DIRECT, bool DYN> __global__ void __launch_bounds__(TPB) k_playouts(const void* pairs, const u32* root_ids, const int* n_pairs_dev,
                                                                                   u32 n_pairs_host, u32 first, u32 count, Div31 dv, u32* wins,
                                                                                   unsigned long long* plies, Geo geo, const RoundKeys rk, int* reset_hdr) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
@@ -1210,7 +1215,7 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     auto finish = [&]() {                                        // one ticket per warp; every warp has read the counter above
         if (reset_hdr && lane == 0) {
             __threadfence();
-            if (atomicAdd(reset_hdr + 1, 1) == (int)n_warps - 1) { reset_hdr[0] = 0; reset_hdr[1] = 0; }
+            if (atomicAdd(reset_hdr + 1, 1) == (int)n_warps - 1) { reset_hdr[0] = 0; reset_hdr[1] = 0; reset_hdr[2] = 0; }
         }
     };
     const u32 total = n_pairs * count;
@@ -1225,6 +1230,10 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     u32 tnext = 0;                                             // warp-uniform cursor over the warp's local game indices
     const u32 tend = my_chunks * CH;
     if (tend == 0) { finish(); return; }
+    constexpr u32 NONE = 0xFFFFFFFFu;
+    u32 base0 = warp_id * CH, used = 0, pending = 0;           // DYN: current chunk (first: chunk warp_id), games dealt from it, next chunk's ticket
+    auto fetch = [&]() { if (lane == 0) pending = atomicAdd(reinterpret_cast<unsigned*>(reset_hdr) + 2, 1u); };
+    if (DYN) fetch();
 
     Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
     bool busy = false;
@@ -1234,9 +1243,23 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
     for (;;) {
         const unsigned need = __ballot_sync(0xffffffffu, !busy);
         if (need) {
-            const u32 t = tnext + (u32)__popc(need & lt);
-            if (!busy && t < tend) {
-                const u32 gi = ((t / CH) * n_warps + warp_id) * CH + (t % CH);          // global game index
+            u32 gi = NONE;                                         // global game index this lane picks up
+            if (DYN) {
+                const u32 k = (u32)__popc(need);
+                const bool roll = base0 != NONE && used + k >= CH; // this deal uses the current chunk up (warp-uniform)
+                u32 nb = NONE;
+                if (roll) { const u32 c = n_warps + __shfl_sync(0xffffffffu, pending, 0); nb = c < n_chunks ? c * CH : NONE; }
+                if (!busy && base0 != NONE) {
+                    const u32 r = used + (u32)__popc(need & lt);
+                    if (r < CH) gi = base0 + r; else if (nb != NONE) gi = nb + (r - CH);
+                }
+                if (roll) { used = used + k - CH; base0 = nb; if (nb != NONE) fetch(); }
+                else if (base0 != NONE) used += k;
+            } else {
+                const u32 t = tnext + (u32)__popc(need & lt);
+                if (!busy && t < tend) gi = ((t / CH) * n_warps + warp_id) * CH + (t % CH);
+            }
+            if (gi != NONE) {
                 if (gi < total) {
                     const u32 pair = (u32)(((u64)gi * dv.m) >> dv.sh);
                     pidx = first + (gi - pair * count);
@@ -1258,7 +1281,7 @@ template <class C, bool DIRECT> __global__ void __launch_bounds__(TPB) k_playout
                 }
             }
             tnext += (u32)__popc(need);
-            if (!__ballot_sync(0xffffffffu, busy) && tnext >= tend) break;
+            if (!__ballot_sync(0xffffffffu, busy) && (DYN ? base0 == NONE : tnext >= tend)) break;
         }
         if (busy) {
             u32 blk[4];
@@ -1475,6 +1498,11 @@ template <class C> int playout_grid(int64_t total_games) {
 
 // k_playouts indexes games with 32 bits: a job of 2^31 games or more runs as several launches over slices of the playout
 // index range (results depend only on the global playout index, so the slicing is invisible)
+inline bool dynamic_chunks() {            // EWN_MC_STATIC=1 in the environment selects the round-robin hand-out (A/B measurements)
+    static const bool on = [] { const char* e = getenv("EWN_MC_STATIC"); return !(e && e[0] == '1'); }();
+    return on;
+}
+
 // kernel launch with the programmatic-dependent-launch attribute (pdl) or a plain one
 template <class... KArgs, class... Args>
 static cudaError_t launch_k(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st, bool pdl, Args... args) {
@@ -1499,8 +1527,13 @@ static int launch_playouts(const void* pairs, const uint32_t* root_ids, const in
         const uint32_t c = (uint32_t)((count - done) < (uint64_t)lim ? (count - done) : (uint64_t)lim);
         const int grid = playout_grid<C>(max_pairs * (int64_t)c);
         const bool last = done + c >= count;
-        CU(launch_k(k_playouts<C, DIRECT>, (unsigned)grid, TPB, 0, st, pdl && done == 0, pairs, root_ids, n_pairs_dev, (u32)max_pairs, first + (uint32_t)done, c,
-                    make_div31(c), wins, plies, geo, rk, last ? reset_hdr : (int*)nullptr));
+        // dynamic chunk hand-out needs the header's counter clean at launch: single-slice jobs on a workspace whose header resets itself
+        if (reset_hdr && done == 0 && last && !DIRECT && dynamic_chunks())
+            CU(launch_k(k_playouts<C, DIRECT, true>, (unsigned)grid, TPB, 0, st, pdl, pairs, root_ids, n_pairs_dev, (u32)max_pairs, first, c,
+                        make_div31(c), wins, plies, geo, rk, reset_hdr));
+        else
+            CU(launch_k(k_playouts<C, DIRECT, false>, (unsigned)grid, TPB, 0, st, pdl && done == 0, pairs, root_ids, n_pairs_dev, (u32)max_pairs, first + (uint32_t)done, c,
+                        make_div31(c), wins, plies, geo, rk, last ? reset_hdr : (int*)nullptr));
         LAUNCHED("k_playouts");
         done += c;
     }
