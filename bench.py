@@ -599,7 +599,8 @@ def run_ours(args, rank, world, local_rank):
         e2e["achieved_gbs"] = got_gbs
         e2e["frac_of_ceiling"] = got_gbs / ceil_gbs
         e2e["host_ceiling_note"] = (f"cudaMemcpyAsync of the step's {d_bytes} B D2H + {h_bytes} B H2D per rank between page-locked and device "
-                                    f"memory, {world} rank(s) concurrently, max over ranks")
+                                    f"memory, {world} rank(s) concurrently, max over ranks; the step's results are STORED by the kernel over PCIe "
+                                    "(no copy engine), so frac_of_ceiling can exceed 1 where the copy engines, not the host memory, limit the memcpy rate")
         del db, hb, db2, hb2
 
     # ---- the same step through the device-resident VecEnv class (CUDA tensors in and out: what a policy on the GPU calls)

@@ -395,7 +395,8 @@ k_step(const __grid_constant__ StepKArgs ka) {
         }
         StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
         if (REPLAY) {
-            inj.dice_opp = a.inject_dice_opp[i]; inj.dice_next = a.inject_dice_next[i];
+            const int cn = ka.p.geo.cube_num;                        // a die outside 1..cube_num would spill into the packed state's flag bits
+            inj.dice_opp = min(max(a.inject_dice_opp[i], 1), cn); inj.dice_next = min(max(a.inject_dice_next[i], 1), cn);
             int2 o = reinterpret_cast<const int2*>(a.inject_opp_action)[i]; inj.o_larger = o.x; inj.o_dir = o.y;
         }
         int tol = 0; double prev = 0.0;

@@ -130,7 +130,8 @@ template <class C> int t_step(const ewn_step_args& a, const Geo& geo) {
             else { int v = a.action_u8[i]; al = v >= 3; ad = v - 3 * al; }
         }
         StepInject inj = {1, 0, 0, 1};
-        if (replay) { inj.dice_opp = a.inject_dice_opp[i]; inj.dice_next = a.inject_dice_next[i]; inj.o_larger = a.inject_opp_action[2 * i]; inj.o_dir = a.inject_opp_action[2 * i + 1]; }
+        if (replay) { const int cn = geo.cube_num; auto cl = [&](int d) { return d < 1 ? 1 : (d > cn ? cn : d); };
+            inj.dice_opp = cl(a.inject_dice_opp[i]); inj.dice_next = cl(a.inject_dice_next[i]); inj.o_larger = a.inject_opp_action[2 * i]; inj.o_dir = a.inject_opp_action[2 * i + 1]; }
         int tol = 0; double prev = 0.0;
         if (p.shaped) { tol = a.tolerance[i]; prev = a.prev_score[i]; }
         StepOut out;
