@@ -1258,6 +1258,9 @@ template <bool TAB, class C, class G> EWN_HD double emm2_min(const EmmChild<C>& 
 #pragma unroll
     for (int s = 0; s < 2; s++) {
         const int set = s ? l.second : l.first, sh = s ? l.sh_second : l.sh_first;
+#if defined(__CUDA_ARCH__)
+        if (!__any_sync(0xffffffffu, set != 0)) continue;                     // every lane of the warp calls this function together (k_emm_fused)
+#endif
         const int c = cell_at<C>(g.br, sh & (int)(8 * sizeof(W) - 1));
         const u32 inc_c = sh >= 0 ? tb.inc[c] : 0u;                            // no such mover: keep the histogram arithmetic borrow-free
 #pragma unroll

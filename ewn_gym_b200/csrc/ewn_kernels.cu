@@ -1049,8 +1049,29 @@ template <class C, int H> __global__ void __launch_bounds__(FTPB) k_emm_fused(co
     EmmTabs tb; tb.inc = s_inc;
     tb.v = H == H_HYBRID ? s_tab + emm_pad(geo.N) : nullptr;
     tb.q = H == H_HYBRID ? s_tab + span + emm_pad(geo.N) : nullptr;
+    // The a1 loop of a warp runs as long as ANY of its five roots has another child: order the block's roots by fan-out (largest
+    // first) so that the roots sharing a warp have similar loop lengths.  Results are written by root index, so the order is invisible.
+    __shared__ unsigned char s_cnt[FROOTS], s_perm[FROOTS];
+    const int64_t blk0 = (int64_t)blockIdx.x * FROOTS;
+    if (threadIdx.x < FROOTS) {
+        int c = 0;
+        if (blk0 + threadIdx.x < n_roots) {
+            Game<C> g; unpack(g, state, (long)(blk0 + threadIdx.x)); g.player = SIDE_TL;
+            if (!full_win<C>(g, geo)) c = legal_count(legal<C, SIDE_TL>(g, geol, movers<C>(g.tl, g.dice)));
+        }
+        s_cnt[threadIdx.x] = (unsigned char)c;
+    }
+    __syncthreads();
+    if (threadIdx.x < FROOTS) {
+        const int c = s_cnt[threadIdx.x];
+        int rank = 0;
+        for (int j = 0; j < FROOTS; j++) { const int cj = s_cnt[j]; rank += (cj > c) || (cj == c && j < (int)threadIdx.x); }
+        s_perm[rank] = (unsigned char)threadIdx.x;
+    }
+    __syncthreads();
     const unsigned lane = threadIdx.x & 31u, grp = lane / 6u, d = lane - 6u * grp;
-    const int64_t r = ((int64_t)blockIdx.x * (FTPB / 32) + (threadIdx.x >> 5)) * 5 + grp;
+    const unsigned slot = (threadIdx.x >> 5) * 5u + (grp < 5u ? grp : 4u);
+    const int64_t r = blk0 + s_perm[slot];
     const bool active = lane < 30u && r < n_roots;
     Game<C> root; setup<C>(root, geo, 1);                             // idle lanes search the initial position and drop the result
     if (active) { unpack(root, state, (long)r); root.player = SIDE_TL; }
@@ -1071,7 +1092,7 @@ template <class C, int H> __global__ void __launch_bounds__(FTPB) k_emm_fused(co
         ch.meta = __shfl_sync(0xffffffffu, mine.meta, src);
         if (C::WORDS == 1) { ch.otl = __shfl_sync(0xffffffffu, mine.otl, src); ch.obr = __shfl_sync(0xffffffffu, mine.obr, src); ch.tl = 0; }
         else { ch.tl = __shfl_sync(0xffffffffu, mine.tl, src); ch.otl = 0; ch.obr = 0; }
-        const bool exists = (ch.meta & EMMC_EXISTS) != 0;
+        const bool exists = lane < 30u && (ch.meta & EMMC_EXISTS) != 0;          // lanes 30, 31: their shuffle source wraps to root 0's lanes
         if (!__any_sync(0xffffffffu, exists)) break;                  // children exist for a1 < #legal: no root of this warp has more
         double q;
         emm2_min<H == H_HYBRID, C>(ch, geol, tb, (int)d + 1, H, fold, pruned ? alpha : ninf, q);
