@@ -91,6 +91,8 @@ PROTOTYPES = {
     "ewn_uct_workspace": (C.c_size_t, [i64]),
     "ewn_uct_search": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, C.c_int, u32, C.c_double, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
     "ewn_mc_predict": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, p_void, C.c_size_t, p_void]),
+    "ewn_mc_static_max_roots": (i64, []),
+    "ewn_mc_predict_static": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u32, u32, p_void, p_void, p_void, p_void, p_void]),
     "ewn_mc_best_action": (C.c_int, [p_void, p_void, p_void, i64, C.c_int, C.c_int, p_void]),
     "ewn_vec_create": (C.c_int, [C.POINTER(VecConfig), C.POINTER(p_void)]),
     "ewn_vec_destroy": (None, [p_void]),
@@ -105,7 +107,8 @@ PROTOTYPES = {
 }
 # entry points a host simulator (tests/hostsim) does not provide
 _VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_vec_step2", "ewn_vec_set_seed", "ewn_host_alloc", "ewn_host_free",
-             "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id"}
+             "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id",
+             "ewn_mc_static_max_roots", "ewn_mc_predict_static"}          # (device-memory entry points: the test-only host build has none)
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

@@ -2111,6 +2111,52 @@ int ewn_mc_predict(const uint64_t* state, const uint32_t* root_ids, int64_t n, i
     return mc_run(state, root_ids, n, N, L, seed, first, count, wins, n_children, plies, action, workspace, workspace_bytes, (cudaStream_t)stream, true);
 }
 
+// ---- ewn_mc_predict without any allocation (no counterpart in the reference) ----------
+// The Monte-Carlo workspace {256-byte header, one record per (root, child)} lives in a file-scope device array instead of the
+// library's cached cudaMalloc: callers under CUDA graph capture, or in loops / harnesses that must not allocate, use this entry point.
+// Every GPU that loads the library holds the array (3 MiB) until the process exits.  All calls share it: calls that overlap on the GPU
+// (two streams, two host threads) race on it; calls on one stream are ordered by the stream.  Nothing in it needs to survive a call:
+// the header is cleared by a memset node at the head of every call, the records are rewritten by the expansion kernel.
+static __device__ __align__(256) unsigned char g_mc_static_ws[256 + (size_t)EWN_MC_STATIC_MAX_ROOTS * 6 * 32];
+
+// device address of g_mc_static_ws on the CURRENT device (in host code the array's name is only a handle for the runtime, not a pointer
+// a kernel could use): looked up once per device, with that device current
+static int mc_static_ptr(void** out) {
+    static void* cached[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { snprintf(g_err, sizeof(g_err), "ewn_mc_predict_static: device ordinal %d not supported", dev); return EWN_ENOSUP; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_mc_static_ws));
+        if (!p) { snprintf(g_err, sizeof(g_err), "ewn_mc_predict_static: cudaGetSymbolAddress returned a null address"); return EWN_ECUDA; }
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return EWN_OK;
+}
+
+int64_t ewn_mc_static_max_roots(void) { return EWN_MC_STATIC_MAX_ROOTS; }
+
+int ewn_mc_predict_static(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, uint32_t first, uint32_t count,
+                          uint32_t* wins, int8_t* action, int32_t* n_children, unsigned long long* plies, void* stream) {
+    if (n > EWN_MC_STATIC_MAX_ROOTS) {
+        snprintf(g_err, sizeof(g_err), "ewn_mc_predict_static: %lld roots exceed the static workspace (EWN_MC_STATIC_MAX_ROOTS = %d); "
+                 "split the batch or use ewn_mc_predict", (long long)n, EWN_MC_STATIC_MAX_ROOTS);
+        return EWN_ESPACE;
+    }
+    if (!state || !wins || n < 0 || !config_ok(N, L)) return EWN_EARG;
+    if (n == 0) return EWN_OK;
+    void* ws = nullptr;
+    int rc = mc_static_ptr(&ws);
+    if (rc) return rc;
+    // a caller-style workspace: mc_run clears its header (cudaMemsetAsync, 8 bytes) and launches expand -> playouts -> arg-max; no
+    // cudaMalloc / cudaFree on this path
+    return mc_run(state, root_ids, n, N, L, seed, first, count, wins, n_children, plies, action, ws, sizeof(g_mc_static_ws), (cudaStream_t)stream, true);
+}
+
 size_t ewn_uct_workspace(int64_t n) { return n <= 0 ? 0 : (size_t)n * (16 + 4 + 4 + 4) + 256; }
 
 int ewn_uct_search(const uint64_t* state, const uint32_t* root_ids, int64_t n, int N, int L, uint64_t seed, int rounds, uint32_t batch, double c,

@@ -346,6 +346,18 @@ class Engine:
                                           self.xp.ptr(nch), self.xp.ptr(plies), None, 0, self.xp.stream()), "ewn_mc_predict")
         return a, w, nch
 
+    def mc_predict_static(self, state, seed: int, first: int, count: int, wins, action, n_children=None, root_ids=None, plies=None):
+        """`mc_predict` through ewn_mc_predict_static: the workspace is the library's file-scope device array, the call allocates nothing
+        (the caller brings every output: wins u32[n,6], action i8[n,2], optionally n_children i32[n]).  At most
+        ewn_mc_static_max_roots() roots per call; calls that overlap on the GPU share -- and race on -- the one array."""
+        n = self._n(state)
+        rc = self.lib.ewn_mc_predict_static(self.xp.ptr(state), self.xp.ptr(root_ids), n, self.N, self.L, seed, first, count, self.xp.ptr(wins),
+                                            self.xp.ptr(action), self.xp.ptr(n_children), self.xp.ptr(plies), self.xp.stream())
+        if rc == _lib.EWN_ESPACE:
+            raise ValueError(self.lib.ewn_last_cuda_error().decode())
+        self._chk(rc, "ewn_mc_predict_static")
+        return action, wins, n_children
+
     def uct_search(self, state, seed: int, rounds: int, batch: int = 32, c: float = 1.41, root_ids=None):
         """UCT at the root over the legal moves with batched random playouts (ewn_uct_search; ucth_temp.py:6-89's intent).
         -> (action i8[n,2], wins i32[n,6], visits i32[n,6])"""

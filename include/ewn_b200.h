@@ -265,6 +265,17 @@ EWN_API int ewn_mc_root_wins(const uint64_t *state, const uint32_t *root_ids, in
 EWN_API int ewn_mc_predict(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
                    uint32_t first, uint32_t count, uint32_t *wins, int8_t *action, int32_t *n_children, unsigned long long *plies,
                    void *workspace, size_t workspace_bytes, void *stream);
+/* ewn_mc_predict for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  Same arguments and results as ewn_mc_predict with
+ * workspace == NULL, but the Monte-Carlo workspace is a file-scope device array of the library (3 MiB, held by every GPU that loads
+ * the library until the process exits) and the call performs no cudaMalloc / cudaFree.  Limit: n <= EWN_MC_STATIC_MAX_ROOTS, above it
+ * the call returns EWN_ESPACE and ewn_last_cuda_error() says so.  Every call on a device shares the one array: calls that overlap on
+ * the GPU (different streams or host threads) race -- keep them on one stream.  Nothing in the array has to survive between calls. */
+#define EWN_MC_STATIC_MAX_ROOTS 16384
+EWN_API int64_t ewn_mc_static_max_roots(void);
+EWN_API int ewn_mc_predict_static(const uint64_t *state, const uint32_t *root_ids, int64_t n, int board_size, int cube_layer, uint64_t seed,
+                          uint32_t first, uint32_t count, uint32_t *wins, int8_t *action, int32_t *n_children,
+                          unsigned long long *plies, void *stream);
 /* first arg-max over the legal children (np.argmax, mcts.py:68) -> action int8[n][2] */
 EWN_API int ewn_mc_best_action(const uint64_t *state, const uint32_t *wins, int8_t *action, int64_t n, int board_size, int cube_layer,
                        void *stream);
