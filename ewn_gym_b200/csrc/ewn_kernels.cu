@@ -665,6 +665,13 @@ template <class C, bool AR> __device__ __forceinline__ void prefetch_game(unsign
     if (!AR) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot + 16u), "l"(action + 2 * (size_t)i) : "memory");
 }
 
+#if defined(EWN_EXP_TIMELINE)    /* experiment build: per-warp clock stamps of the last k_vstep launch (tools/k1_sweep.py EWN_K1_TIMELINE=..., tools/k1_timeline.py) */
+__device__ unsigned long long g_tl[148 * 64 * 16];
+#define EWN_TL_SLOT ((((size_t)blockIdx.x * (VTPB / 32) + (threadIdx.x >> 5)) % (148 * 64)) * 16)
+#define EWN_TL(k) do { if ((threadIdx.x & 31) == 0) g_tl[EWN_TL_SLOT + (k)] = (unsigned long long)clock64(); } while (0)
+#else
+#define EWN_TL(k) do { } while (0)
+#endif
 // AR: the agent is the in-kernel uniform-over-the-legal-list player (random_policy.py:11-15, Philox word 3): no action array is read
 template <class C, int NT, bool AR> __global__ void __launch_bounds__(VTPB, VMINB)
 k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
@@ -689,6 +696,17 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     // before the PREVIOUS grid has completed and flushed.  Both are no-ops for launches without the PDL attribute.
     asm volatile("griddepcontrol.launch_dependents;");
     if (tid == 0) { s_won = 0; s_lost = 0; }
+#if defined(EWN_EXP_TIMELINE)
+    if ((tid & 31) == 0) {
+        unsigned long long gt; unsigned smid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        g_tl[EWN_TL_SLOT + 15] = gt; g_tl[EWN_TL_SLOT + 14] = smid;
+        for (int k = 1; k < 14; k++) g_tl[EWN_TL_SLOT + k] = 0;    // stamps of earlier launches
+    }
+    EWN_TL(0);
+    int it_ = 0;
+#endif
 #if EWN_VPRE
     // Pull the first unit's lines into L2 while the previous grid is still draining.  A prefetch has no architectural effect
     // and L2 is the coherence point, so this is safe although the previous grid may still be writing these very addresses;
@@ -704,6 +722,7 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     const GeoLut geol = make_geo_lut<C, VTPB>(geo, s_dirs);
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (tid == 0 && a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
+    EWN_TL(1);
     __syncthreads();
 
     const u64 step = ka.p.step + (a.step_dev ? __ldg(a.step_dev) : 0ull);   // device-resident step counter: CUDA-graph replays
@@ -734,6 +753,10 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
 #endif
     while (u < u_end) {                                            // block-uniform
         asm volatile("cp.async.wait_all;" ::: "memory");
+#if defined(EWN_EXP_TIMELINE)
+        if (it_ < 8) EWN_TL(2 + it_);
+        it_++;
+#endif
         const ulonglong2 sw = s_pf[2 * tid];                        // own slot: no cross-thread hazard
         longlong2 act = make_longlong2(0, 0);
         if (!AR) act = reinterpret_cast<const longlong2*>(s_pf)[2 * tid + 1];
@@ -815,6 +838,10 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
         }
     }
 #endif
+    EWN_TL(10);
+#if defined(EWN_EXP_TIMELINE)
+    if (lane == 0) g_tl[EWN_TL_SLOT + 13] = (unsigned long long)it_;
+#endif
     if (!tally) return;
     {
         const unsigned wl = __reduce_add_sync(0xffffffffu, tally_c);          // <= 32 * VITER_MAX per half: no carry
@@ -852,7 +879,9 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
 #endif
 #if EWN_VFLUSH
     __syncthreads();
+    EWN_TL(11);
     vstep_flush<C, NT>(a.term_board, a.term_dice, a.term_index, a.term_code, a.term_index_base, geo, smb, s_term, s_who, s_wcnt, seg, F, (int64_t)s_row0);
+    EWN_TL(12);
 }
 #else
     // row r of this block's output <-> entry src(r) of the segmented list
@@ -1600,6 +1629,11 @@ template <class C, int NT, bool AR> cudaError_t launch_vstep(const cudaLaunchCon
 // C ABI
 // ================================================================================================
 extern "C" {
+#if defined(EWN_EXP_TIMELINE)
+__attribute__((visibility("default"))) int ewn_debug_timeline(unsigned long long* host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, g_tl, sizeof(g_tl));
+}
+#endif
 
 int ewn_version(void) { return 100; }
 

@@ -48,6 +48,12 @@ if os.environ.get("EWN_K1_CHILD"):
         b.record(); torch.cuda.synchronize()
         res.append(a.elapsed_time(b) / 200 * 1e3)
     line = f"stream {min(res):7.2f} us (runs {' '.join(f'{x:.2f}' for x in res)})"
+    if os.environ.get("EWN_K1_TIMELINE"):                  # -DEWN_EXP_TIMELINE build: per-warp clock stamps of the last launch
+        import ctypes, numpy as np
+        tl = np.zeros(148 * 64 * 16, dtype=np.uint64)
+        rc = ctypes.CDLL(_lib.LIB_PATH).ewn_debug_timeline(tl.ctypes.data_as(ctypes.c_void_p))
+        np.save(os.environ["EWN_K1_TIMELINE"], tl.reshape(-1, 16))
+        line += f"   timeline rc={rc}"
     if os.environ.get("EWN_K1_GRAPH", "1") == "1":
         side = torch.cuda.Stream(device=dev)
         with torch.cuda.stream(side):
