@@ -39,6 +39,12 @@ class StepArgs(C.Structure):
     ]
 
 
+class PolicyNet(C.Structure):
+    """struct ewn_policy_net"""
+    _fields_ = [("hidden", i32), ("reserved", i32)] + [(k, p_void) for k in (
+        "pi_w1", "pi_b1", "pi_w2", "pi_b2", "vf_w1", "vf_b1", "vf_w2", "vf_b2", "action_w", "action_b", "value_w", "value_b")]
+
+
 class VecConfig(C.Structure):
     """struct ewn_vec_config"""
     _fields_ = [
@@ -80,6 +86,9 @@ PROTOTYPES = {
     "ewn_step": (C.c_int, [C.POINTER(StepArgs), p_void]),
     "ewn_counter_add": (C.c_int, [p_void, u64, p_void]),
     "ewn_step_dice": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void, p_void]),
+    "ewn_policy_forward": (C.c_int, [C.POINTER(PolicyNet), p_void, p_void, i64, C.c_int, C.c_int, u64, u64, p_void, u64, C.c_int, p_void, p_void, p_void,
+                                     p_void, p_void]),
+    "ewn_gae": (C.c_int, [p_void, p_void, p_void, p_void, C.c_int, i64, C.c_double, C.c_double, p_void, p_void, p_void]),
     "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
     "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
     "ewn_expectiminimax": (C.c_int, [p_void, i64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, p_void, p_void, p_void, C.c_size_t, p_void]),
@@ -108,7 +117,7 @@ PROTOTYPES = {
 # entry points a host simulator (tests/hostsim) does not provide
 _VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_vec_step2", "ewn_vec_set_seed", "ewn_host_alloc", "ewn_host_free",
              "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id",
-             "ewn_mc_static_max_roots", "ewn_mc_predict_static"}          # (device-memory entry points: the test-only host build has none)
+             "ewn_mc_static_max_roots", "ewn_mc_predict_static", "ewn_policy_forward", "ewn_gae"}          # (device-memory entry points: the test-only host build has none)
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

@@ -243,6 +243,34 @@ class EWNDeviceVecEnv:
     def _bind(self):
         self._plans = [self.e.step_plan(self.state, self._action, **self._step_kw(b)) for b in (0, 1)]
 
+    def bind_step(self, action, out, step=0, step_dev=None):
+        """A pre-bound step of THIS env's games (same seed, env ids, reward shaping, statistics) that reads `action` (int64[n,2]) and
+        writes the output tensors in `out` (names of ewn_step_args) -- e.g. slices of a rollout buffer -- instead of the env's own
+        two output sets; no terminal observations.  The caller launches it with ``plan.launch(step)``; with `step_dev` (int64[1] on the
+        device) the kernel adds that counter to the step index, so a CUDA graph of such launches can be replayed.  After driving the
+        games this way call ``advance(k)`` with the number of steps taken."""
+        if self.opponent is not None:
+            raise RuntimeError("bind_step: the in-kernel random opponent only")
+        kw = self._step_kw(0)
+        kw.pop("term_compact", None)
+        kw.update(want=tuple(out), out=dict(out), step=int(step))
+        if step_dev is not None:
+            kw["step_dev"] = step_dev
+        return self.e.step_plan(self.state, action, **kw)
+
+    def advance(self, steps: int, obs=None):
+        """account for `steps` steps taken through bind_step plans; `obs` = (board, dice) after the last of them becomes the env's
+        latest observation"""
+        self._t += int(steps)
+        if obs is not None:
+            self._copy_into(self._outs[self._last]["obs_board"], obs[0])
+            self._copy_into(self._outs[self._last]["obs_dice"], obs[1])
+
+    @property
+    def step_index(self) -> int:
+        """the step counter the NEXT step will use (the Philox counter of its dice)"""
+        return self._t
+
     def step_async(self, actions):
         if self.state is None:
             raise RuntimeError("reset() first")

@@ -279,6 +279,48 @@ class Engine:
         """*counter += k on the current stream (see ewn_step_args.step_dev)"""
         self._chk(self.lib.ewn_counter_add(self.xp.ptr(counter), int(k), self.xp.stream()), "ewn_counter_add")
 
+    # ------------------------------------------------------------------ rollout collection with a policy in the loop
+    def policy_net(self, module):
+        """ewn_policy_net over the parameters of a train.MultiInputActorCritic, read in place (fp32, contiguous, on this device)"""
+        from ._lib import PolicyNet
+        lin = {"pi_w1": module.pi[0].weight, "pi_b1": module.pi[0].bias, "pi_w2": module.pi[2].weight, "pi_b2": module.pi[2].bias,
+               "vf_w1": module.vf[0].weight, "vf_b1": module.vf[0].bias, "vf_w2": module.vf[2].weight, "vf_b2": module.vf[2].bias,
+               "action_w": module.action_net.weight, "action_b": module.action_net.bias,
+               "value_w": module.value_net.weight, "value_b": module.value_net.bias}
+        net = PolicyNet()
+        net.hidden = int(module.pi[0].weight.shape[0])
+        for k, t in lin.items():
+            if str(t.dtype) != "torch.float32" or not t.is_contiguous() or not t.is_cuda:
+                raise ValueError(f"policy parameter {k}: fp32, contiguous, on the GPU expected")
+            setattr(net, k, t.data_ptr())
+        net._keep = list(lin.values())
+        return net
+
+    def policy_forward(self, net, board, dice, *, seed=0, step=0, step_dev=None, env_id0=0, deterministic=False, actions=None, values=None,
+                       logp=None, logits=None, want=("actions", "values", "logp")):
+        """ActorCriticPolicy.forward for n observations in one launch (ewn_policy_forward) -> dict of the outputs asked for"""
+        xp = self.xp
+        n = int(board.shape[0])
+        out = {"actions": actions, "values": values, "logp": logp, "logits": logits}
+        shapes = {"actions": ((n, 2), "i64"), "values": ((n,), "f32"), "logp": ((n,), "f32"), "logits": ((n, 5), "f32")}
+        for k in want:
+            if out[k] is None:
+                out[k] = xp.empty(*shapes[k])
+        self._chk(self.lib.ewn_policy_forward(C.byref(net), xp.ptr(board), xp.ptr(dice), n, self.N, self.L, seed, step, xp.ptr(step_dev), env_id0,
+                                              int(bool(deterministic)), xp.ptr(out["actions"]), xp.ptr(out["values"]), xp.ptr(out["logp"]),
+                                              xp.ptr(out["logits"]), xp.stream()), "ewn_policy_forward")
+        return {k: v for k, v in out.items() if v is not None}
+
+    def gae(self, rewards, values, dones, last_values, gamma=0.99, gae_lambda=1.0, advantages=None, returns=None):
+        """RolloutBuffer.compute_returns_and_advantage over [T][n] tensors (ewn_gae) -> (advantages, returns)"""
+        xp = self.xp
+        T, n = int(rewards.shape[0]), int(rewards.shape[1])
+        adv = xp.empty((T, n), "f32") if advantages is None else advantages
+        ret = xp.empty((T, n), "f32") if returns is None else returns
+        self._chk(self.lib.ewn_gae(xp.ptr(rewards), xp.ptr(values), xp.ptr(dones), xp.ptr(last_values), T, n, float(gamma), float(gae_lambda),
+                                   xp.ptr(adv), xp.ptr(ret), xp.stream()), "ewn_gae")
+        return adv, ret
+
     def step_plan(self, state, action=None, **kw):
         """Pre-bind a step (pointers, sizes, flags) so that a rollout loop pays one ctypes call per launch:
         ``plan = e.step_plan(state, action, out=...); plan.launch(step)``.  Same keywords as ``step``."""

@@ -90,6 +90,23 @@ class MultiInputActorCritic(nn.Module):
         return (a[0].cpu().numpy() if single else a), None
 
 
+class _LazyLog(dict):
+    """logger values may be device scalars (the fused collector leaves its sums on the GPU): read back when somebody looks"""
+
+    def __getitem__(self, k):
+        v = dict.__getitem__(self, k)
+        return float(v) if th.is_tensor(v) else v
+
+    def get(self, k, default=None):
+        return self[k] if k in self else default
+
+    def values(self):
+        return [self[k] for k in self]
+
+    def items(self):
+        return [(k, self[k]) for k in self]
+
+
 def _t(x, device):
     """env output (CUDA tensor, or numpy array from the host-simulator test backend) -> tensor on `device`, no copy when possible"""
     return x if th.is_tensor(x) else th.as_tensor(np.asarray(x), device=device)
@@ -101,7 +118,7 @@ class A2C:
 
     def __init__(self, policy: str, env, n_steps: int = 5, learning_rate: float = 7e-4, gamma: float = 0.99, gae_lambda: float = 1.0,
                  ent_coef: float = 0.0, vf_coef: float = 0.5, max_grad_norm: float = 0.5, policy_kwargs: Dict[str, Any] | None = None,
-                 seed: int | None = None, device=None, **_ignored):
+                 seed: int | None = None, device=None, fused: bool | None = None, **_ignored):
         assert policy == "MultiInputPolicy", "the reference trains MultiInputPolicy only (train.py:41,53)"
         self.env, self.n_steps, self.gamma, self.gae_lambda = env, int(n_steps), float(gamma), float(gae_lambda)
         self.ent_coef, self.vf_coef, self.max_grad_norm = float(ent_coef), float(vf_coef), float(max_grad_norm)
@@ -122,11 +139,101 @@ class A2C:
         self.buf = {"board": th.zeros((T, n, N, N), dtype=th.int16, device=dev), "dice": th.zeros((T, n), dtype=th.int64, device=dev),
                     "actions": th.zeros((T, n, 2), dtype=th.int64, device=dev), "rewards": th.zeros((T, n), device=dev),
                     "starts": th.zeros((T, n), device=dev), "values": th.zeros((T, n), device=dev), "log_probs": th.zeros((T, n), device=dev)}
-        self.logger: Dict[str, float] = {}
+        self.logger: Dict[str, float] = _LazyLog()
+        self.policy_seed = int(seed) if seed is not None else 0
+        # fused collection (policy forward and env step as two launches per step, the whole rollout one CUDA graph) when the env is the
+        # device-resident one with its in-kernel opponent and the policy has the default 64-wide towers; the generic loop otherwise
+        self.fused = fused if fused is not None else self._can_fuse()
+        self._graph = None
+
+    # ------------------------------------------------------------------ fused collection (K5: ewn_policy_forward + ewn_step + ewn_gae)
+    def _can_fuse(self) -> bool:
+        env = self.env
+        return (self.device.type == "cuda" and hasattr(env, "bind_step") and getattr(env, "opponent", 1) is None
+                and getattr(getattr(env, "e", None), "xp", None) is not None and getattr(env.e.xp, "torch", None) is not None
+                and self.policy.pi[0].weight.shape[0] == 64 and self.policy.pi[2].weight.shape[0] == 64
+                and isinstance(self.policy.pi[1], nn.Tanh))
+
+    def _build_fused(self):
+        """One CUDA graph for a whole rollout: per step ewn_policy_forward (reads observation slot t, writes actions / values / log-probs
+        of slot t) and the env's step kernel (reads those actions, writes reward / done of slot t and the observation of slot t + 1
+        straight into the buffer -- no copies); then V of the last observation, GAE, and the step-counter bump for the next replay."""
+        env, e, T, n, N, dev = self.env, self.env.e, self.n_steps, self.env.num_envs, self.env.board_size, self.device
+        if env.state is None:
+            env.reset()
+        last = env._obs(env._last)
+        f = {"board": th.zeros((T + 1, n, N, N), dtype=th.int16, device=dev), "dice": th.zeros((T + 1, n), dtype=th.int64, device=dev),
+             "actions": th.zeros((T, n, 2), dtype=th.int64, device=dev), "rewards": th.zeros((T, n), device=dev),
+             "dones": th.zeros((T, n), dtype=th.uint8, device=dev), "trunc": th.zeros((n,), dtype=th.uint8, device=dev),
+             "values": th.zeros((T, n), device=dev), "log_probs": th.zeros((T, n), device=dev), "last_values": th.zeros((n,), device=dev),
+             "adv": th.zeros((T, n), device=dev), "ret": th.zeros((T, n), device=dev), "sums": th.zeros((2,), device=dev)}
+        f["board"][T].copy_(last["board"]); f["dice"][T].copy_(last["dice_roll"])      # a replay starts by moving slot T to slot 0
+        self.fb = f
+        self.buf = {"board": f["board"][:T], "dice": f["dice"][:T], "actions": f["actions"], "rewards": f["rewards"], "values": f["values"],
+                    "log_probs": f["log_probs"], "dones": f["dones"]}
+        self.advantages, self.returns = f["adv"], f["ret"]
+        self._ctr = th.zeros(1, dtype=th.int64, device=dev)
+        self._ctr_host = None
+        self._net = e.policy_net(self.policy)
+        # first launches load the kernels: not inside a capture
+        e.policy_forward(self._net, f["board"][0], f["dice"][0], actions=f["actions"][0], values=f["values"][0], logp=f["log_probs"][0])
+        e.gae(f["rewards"], f["values"], f["dones"], f["last_values"], self.gamma, self.gae_lambda, f["adv"], f["ret"])
+        kw = env._step_kw(0)                             # the env's own step configuration, played once on COPIES of its games
+        kw.pop("term_compact", None)
+        kw.update(stats=None, want=("reward_f32", "terminated", "truncated", "obs_board", "obs_dice"),
+                  out={"reward_f32": f["rewards"][0], "terminated": f["dones"][0], "truncated": f["trunc"], "obs_board": f["board"][1],
+                       "obs_dice": f["dice"][1]})
+        if env.shaped:
+            kw.update(tolerance=env._tol.clone(), prev_score=env._prev.clone())
+        e.step(env.state.clone(), f["actions"][0], **kw)
+        th.cuda.synchronize(dev)
+        side = th.cuda.Stream(device=dev)
+        with th.cuda.stream(side):                      # plans bind the stream that is current when they are built
+            plans = [env.bind_step(f["actions"][t], {"reward_f32": f["rewards"][t], "terminated": f["dones"][t], "truncated": f["trunc"],
+                                                     "obs_board": f["board"][t + 1], "obs_dice": f["dice"][t + 1]}, step=t, step_dev=self._ctr)
+                     for t in range(T)]
+
+            def body():
+                f["board"][0].copy_(f["board"][T]); f["dice"][0].copy_(f["dice"][T])
+                for t in range(T):
+                    e.policy_forward(self._net, f["board"][t], f["dice"][t], seed=self.policy_seed, step=t, step_dev=self._ctr, env_id0=env.env_id0,
+                                     actions=f["actions"][t], values=f["values"][t], logp=f["log_probs"][t])
+                    plans[t].launch(t)
+                e.policy_forward(self._net, f["board"][T], f["dice"][T], values=f["last_values"], want=("values",))
+                e.gae(f["rewards"], f["values"], f["dones"], f["last_values"], self.gamma, self.gae_lambda, f["adv"], f["ret"])
+                f["sums"][0] = f["dones"].sum(); f["sums"][1] = f["rewards"].mean()
+                e.counter_add(self._ctr, T)
+
+            graph = th.cuda.CUDAGraph()
+            with th.cuda.graph(graph, stream=side):
+                body()
+        th.cuda.synchronize(dev)
+        self._plans, self._graph = plans, graph
+
+    @th.no_grad()
+    def _collect_fused(self):
+        if self._graph is None:
+            self._build_fused()
+        env, f, T = self.env, self.fb, self.n_steps
+        if self._ctr_host != env.step_index:            # the env was stepped or reset behind the graph's back: re-seat the counter and
+            self._ctr.fill_(env.step_index)             # take the env's latest observation as the rollout's first
+            if self._ctr_host is not None:
+                last = env._obs(env._last)
+                f["board"][T].copy_(last["board"]); f["dice"][T].copy_(last["dice_roll"])
+        self._graph.replay()
+        env.advance(T, obs=(f["board"][T], f["dice"][T]))
+        self._ctr_host = env.step_index
+        self._last_obs = {"board": f["board"][T], "dice_roll": f["dice"][T]}
+        self._last_episode_starts = f["dones"][T - 1].float()
+        self.num_timesteps += env.num_envs * T
+        self.logger["rollout/episodes"] = f["sums"][0]
+        self.logger["rollout/mean_reward"] = f["sums"][1]
 
     # ------------------------------------------------------------------ OnPolicyAlgorithm.collect_rollouts
     @th.no_grad()
     def collect_rollouts(self):
+        if self.fused:
+            return self._collect_fused()
         env, b, dev = self.env, self.buf, self.device
         if self._last_obs is None:
             obs = env.reset()

@@ -195,6 +195,35 @@ EWN_API int ewn_step_dice(int32_t *dice_opp, int32_t *dice_next, int64_t n, int 
 /* *counter += k on `stream` (one tiny kernel; capturable).  See ewn_step_args.step_dev. */
 EWN_API int ewn_counter_add(uint64_t *counter, uint64_t k, void *stream);
 
+/* ---- rollout collection with a policy in the loop (BASELINE configs[4]) ----------------------------------- */
+
+/* The parameters of SB3's "MultiInputPolicy" as train.py:35-63 builds it (policy_kwargs = dict(activation_fn = Tanh), default
+ * net_arch pi = vf = [64, 64]), as device pointers to fp32 arrays in torch's Linear layout ([out][in] row-major; bias [out]):
+ * features = Flatten(board int16 N*N as float) ++ one-hot(dice - 1, cube_num + 1) (CombinedExtractor on envs/ewn.py:63-69);
+ * latent_pi = tanh(pi_w2 tanh(pi_w1 f + pi_b1) + pi_b2), latent_vf likewise; logits = action_w latent_pi + action_b (2 + 3 logits of
+ * MultiDiscrete([2, 3]), envs/ewn.py:61-62); value = value_w latent_vf + value_b.  stable_baselines3 is a dependency of the
+ * reference that is not vendored in it (requirement.txt); the architecture restated here is its published default. */
+typedef struct ewn_policy_net {
+    int32_t hidden;               /* width of the four hidden layers; 64 is supported (EWN_ENOSUP otherwise) */
+    int32_t reserved;
+    const float *pi_w1, *pi_b1, *pi_w2, *pi_b2;     /* [hidden][N*N + cube_num + 1], [hidden], [hidden][hidden], [hidden] */
+    const float *vf_w1, *vf_b1, *vf_w2, *vf_b2;
+    const float *action_w, *action_b;               /* [5][hidden], [5] */
+    const float *value_w, *value_b;                 /* [1][hidden], [1] */
+} ewn_policy_net;
+/* ActorCriticPolicy.forward(obs, deterministic) of train.py:144-155's model.learn() -> collect_rollouts, for n observations in ONE
+ * launch: actions int64[n][2] sampled from the two categoricals (Philox block of (seed; env_id0 + i, step [+ *step_dev]), tag POLICY;
+ * deterministic != 0: the first arg-max), values f32[n], logp f32[n] = log-probability of the sampled action, logits f32[n][5]
+ * (any output may be NULL; logp needs actions).  With actions == NULL this is predict_values(). */
+EWN_API int ewn_policy_forward(const ewn_policy_net *net, const int16_t *board, const int64_t *dice, int64_t n, int board_size, int cube_layer,
+                       uint64_t seed, uint64_t step, const uint64_t *step_dev, uint64_t env_id0, int deterministic, int64_t *actions,
+                       float *values, float *logp, float *logits, void *stream);
+/* RolloutBuffer.compute_returns_and_advantage of the same loop (GAE(gamma, lambda); A2C's default lambda = 1 gives the n-step return):
+ * rewards / values f32[T][n], dones u8[T][n] (the episode ended AT step t), last_values f32[n] = V of the observation after the last
+ * step -> advantages f32[T][n], returns f32[T][n] (or NULL).  fp32, in the operation order of the reference's tensor loop. */
+EWN_API int ewn_gae(const float *rewards, const float *values, const uint8_t *dones, const float *last_values, int T, int64_t n, double gamma,
+            double gae_lambda, float *advantages, float *returns, void *stream);
+
 /* eval_random.py:17-51 evaluation() for n seeds, from the seeds ALONE: every game draws its dice (envs/ewn.py:90-92) and both
  * random players' picks (random_policy.py:12-14) from the reference's own stream -- numpy's legacy global RandomState, MT19937
  * seeded by np.random.seed(seed) in env.reset(seed) (:488-494), np.random.randint by masked rejection -- in the reference's

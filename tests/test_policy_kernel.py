@@ -1,0 +1,183 @@
+"""K5 on the GPU: ewn_policy_forward (SB3 "MultiInputPolicy" forward + categorical draw in one launch) against the torch module it reads
+its parameters from, ewn_gae against the tensor loop of OnPolicyAlgorithm, and the fused rollout collector (one CUDA graph per
+rollout) against the generic one.  train.py:35-63 (MultiInputPolicy, Tanh), :144-155 (model.learn -> collect_rollouts)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-5          # fp32 dot products of 56..64 terms summed in a different order than cuBLAS does, tanhf on both sides
+
+
+def _module(N, L, seed=0):
+    import torch as th
+    from ewn_gym_b200.train import MultiInputActorCritic
+    th.manual_seed(seed)
+    m = MultiInputActorCritic(N, L * (L + 1) // 2).cuda()
+    with th.no_grad():                               # SB3's init makes action_net tiny (gain 0.01): spread the logits for the test
+        m.action_net.weight.mul_(60.0); m.action_net.bias.uniform_(-0.5, 0.5); m.value_net.bias.fill_(0.25)
+    return m
+
+
+def _obs(e, n, seed, steps=6):
+    st = e.reset(n, seed=seed)
+    for t in range(1, steps + 1):
+        e.step(st, None, seed=seed, step=t, agent_random=True, autoreset=True, want=())
+    b, d = e.decode(st)
+    return b, d
+
+
+@pytest.mark.parametrize("N,L,n", [(7, 3, 4096), (5, 3, 1000 + 7), (7, 3, 5), (6, 3, 333)])
+def test_policy_forward_matches_the_torch_module(N, L, n):
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    e = Engine(N, L)
+    m = _module(N, L, seed=N + n)
+    net = e.policy_net(m)
+    board, dice = _obs(e, n, seed=11)
+    obs = {"board": board, "dice_roll": dice}
+    out = e.policy_forward(net, board, dice, seed=5, step=3, env_id0=100, want=("actions", "values", "logp", "logits"))
+    with th.no_grad():
+        f = m.features(obs)
+        logits = m.action_net(m.pi(f))
+        values = m.value_net(m.vf(f)).squeeze(1)
+        v2, lp, _ = m.evaluate_actions(obs, out["actions"])
+    assert th.allclose(out["logits"], logits, atol=TOL, rtol=0), float((out["logits"] - logits).abs().max())
+    assert th.allclose(out["values"], values, atol=TOL, rtol=0) and th.allclose(out["values"], v2, atol=TOL, rtol=0)
+    assert th.allclose(out["logp"], lp, atol=4 * TOL, rtol=0), float((out["logp"] - lp).abs().max())
+    a = out["actions"]
+    assert int(a[:, 0].min()) >= 0 and int(a[:, 0].max()) <= 1 and int(a[:, 1].min()) >= 0 and int(a[:, 1].max()) <= 2
+    # the same call again draws the same actions (counter-based stream); another step index draws others
+    again = e.policy_forward(net, board, dice, seed=5, step=3, env_id0=100)
+    assert th.equal(again["actions"], a)
+    if n >= 1000:
+        other = e.policy_forward(net, board, dice, seed=5, step=4, env_id0=100)
+        assert not th.equal(other["actions"], a)
+    # deterministic = the arg-max of the probabilities, wherever the two best logits are not a numerical tie
+    det = e.policy_forward(net, board, dice, deterministic=True)["actions"]
+    top2 = logits[:, :2].sort(1).values
+    clear0 = (top2[:, 1] - top2[:, 0]) > 1e-4
+    top3 = logits[:, 2:].sort(1).values
+    clear1 = (top3[:, 2] - top3[:, 1]) > 1e-4
+    assert th.equal(det[clear0, 0], logits[:, :2].argmax(1)[clear0]) and th.equal(det[clear1, 1], logits[:, 2:].argmax(1)[clear1])
+    # predict_values: no actions asked for
+    pv = e.policy_forward(net, board, dice, want=("values",))
+    assert set(pv) == {"values"} and th.equal(pv["values"], out["values"])
+
+
+def test_sampled_actions_follow_the_categoricals():
+    """one observation repeated 200,000 times (different env ids -> different Philox counters): the frequencies of the 2 x 3 actions
+    against softmax(logits), 5 sigma per cell"""
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    N, L, n = 7, 3, 200_000
+    e = Engine(N, L)
+    m = _module(N, L, seed=3)
+    b1, d1 = _obs(e, 1, seed=2)
+    board, dice = b1.expand(n, N, N).contiguous(), d1.expand(n).contiguous()
+    out = e.policy_forward(e.policy_net(m), board, dice, seed=9, step=1, want=("actions", "logits"))
+    p0 = th.softmax(out["logits"][0, :2].double(), 0).cpu().numpy()
+    p1 = th.softmax(out["logits"][0, 2:].double(), 0).cpu().numpy()
+    a = out["actions"].cpu().numpy()
+    for i in range(2):
+        for j in range(3):
+            p = p0[i] * p1[j]
+            k = int(((a[:, 0] == i) & (a[:, 1] == j)).sum())
+            assert abs(k - n * p) <= 5 * np.sqrt(n * p * (1 - p)) + 1, (i, j, k, n * p)
+
+
+def test_unsupported_width_is_refused():
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    from ewn_gym_b200.train import MultiInputActorCritic
+    e = Engine(5, 3)
+    m = MultiInputActorCritic(5, 6, net_arch=(32, 32)).cuda()
+    b, d = _obs(e, 8, seed=1)
+    with pytest.raises(RuntimeError):
+        e.policy_forward(e.policy_net(m), b, d)
+    _ = th
+
+
+@pytest.mark.parametrize("T,n,lam", [(128, 4096, 1.0), (5, 77, 0.95), (1, 3, 1.0)])
+def test_gae_equals_the_tensor_loop(T, n, lam):
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    e = Engine(5, 3)
+    g = th.Generator(device="cuda"); g.manual_seed(T * n)
+    rewards = th.randn(T, n, device="cuda", generator=g)
+    values = th.randn(T, n, device="cuda", generator=g)
+    dones = (th.rand(T, n, device="cuda", generator=g) < 0.1).to(th.uint8)
+    last = th.randn(n, device="cuda", generator=g)
+    gamma = 0.99
+    adv, ret = e.gae(rewards, values, dones, last, gamma, lam)
+    # OnPolicyAlgorithm / RolloutBuffer.compute_returns_and_advantage as ewn_gym_b200/train.py's generic collector writes it
+    ref = th.zeros_like(rewards)
+    last_gae = th.zeros(n, device="cuda")
+    for t in reversed(range(T)):
+        nonterminal = 1.0 - dones[t].float()
+        next_values = last if t == T - 1 else values[t + 1]
+        delta = rewards[t] + gamma * next_values * nonterminal - values[t]
+        last_gae = delta + gamma * lam * nonterminal * last_gae
+        ref[t] = last_gae
+    assert th.equal(adv, ref) and th.equal(ret, ref + values)
+
+
+@pytest.mark.parametrize("N,L,shaped", [(7, 3, True), (5, 3, False)])
+def test_fused_rollouts_are_consistent_and_continue_across_replays(N, L, shaped):
+    """the graph-replayed collector: observations / rewards / dones of the buffer are what the env produces for the stored actions
+    (replayed through a second env from the same seed), values and log-probs are the torch module's, the rollouts join up, stepping
+    the env by hand in between is picked up, and a training step changes what the next replay computes (parameters read in place)"""
+    import torch as th
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.train import A2C
+    n, T, seed = 1000, 16, 21
+    env = EWNDeviceVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_tolerance=3)
+    twin = EWNDeviceVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_tolerance=3)
+    model = A2C("MultiInputPolicy", env, n_steps=T, seed=2)
+    assert model.fused
+    obs = twin.reset()
+    tb, td = obs["board"].clone(), obs["dice_roll"].clone()
+    for rollout in range(4):
+        if rollout == 2:                                          # somebody steps the env between two rollouts
+            act = th.zeros((n, 2), dtype=th.int64, device="cuda")
+            env.step(act)
+            o2, _, _, _ = twin.step(act)
+            tb, td = o2["board"].clone(), o2["dice_roll"].clone()
+        model.collect_rollouts()
+        b = model.buf
+        for t in range(T):
+            assert th.equal(b["board"][t], tb) and th.equal(b["dice"][t], td), (rollout, t)
+            o2, r2, d2, _ = twin.step(b["actions"][t].clone())
+            assert th.equal(b["rewards"][t], r2) and th.equal(b["dones"][t].bool(), d2), (rollout, t)
+            tb, td = o2["board"].clone(), o2["dice_roll"].clone()
+        assert th.equal(model._last_obs["board"], tb) and th.equal(env.state, twin.state)
+        flat = {"board": b["board"].reshape(T * n, N, N), "dice_roll": b["dice"].reshape(T * n)}
+        with th.no_grad():
+            v, lp, _ = model.policy.evaluate_actions(flat, b["actions"].reshape(T * n, 2))
+            last = model.policy.predict_values(model._last_obs)
+        assert th.allclose(b["values"].reshape(-1), v, atol=TOL, rtol=0) and th.allclose(b["log_probs"].reshape(-1), lp, atol=4 * TOL, rtol=0)
+        adv, ret = env.e.gae(b["rewards"], b["values"], b["dones"], model.fb["last_values"], model.gamma, model.gae_lambda)
+        assert th.allclose(model.fb["last_values"], last, atol=TOL, rtol=0)
+        assert th.equal(model.advantages, adv) and th.equal(model.returns, ret)
+        assert model.logger["rollout/episodes"] == float(b["dones"].sum())
+        model.train()                                             # RMSprop updates the parameters in place: the graph reads the new ones
+    assert env.step_index == twin.step_index and model.num_timesteps == 4 * T * n
+
+
+def test_generic_collector_still_runs_on_cuda():
+    """fused=False keeps the torch loop (what a policy with another net_arch, or an env with a policy opponent, gets): same buffer
+    contract; the learning run of tests/test_train.py covers the fused collector on this backend"""
+    import torch as th
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.train import A2C
+    env = EWNDeviceVecEnv(256, 5, 3, seed=5, shaped=True)
+    model = A2C("MultiInputPolicy", env, n_steps=4, seed=3, fused=False)
+    assert not model.fused
+    model.collect_rollouts()
+    first_last = model._last_obs["board"].clone()
+    model.train()
+    model.collect_rollouts()
+    assert th.equal(model.buf["board"][0], first_last) and model.num_timesteps == 2 * 4 * 256
+    wide = A2C("MultiInputPolicy", EWNDeviceVecEnv(64, 5, 3), n_steps=2, policy_kwargs={"net_arch": (32, 32)})
+    assert not wide.fused
+    wide.collect_rollouts(); wide.train()
