@@ -1490,94 +1490,138 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 // of the int16 board, one-hot of the Discrete die), two Tanh towers of two layers each (pi / vf), action_net -> the logits of
 // MultiDiscrete([2, 3]), value_net -> V(s) -- and the draw from the two categoricals, in ONE launch, reading the torch
 // parameters where they lie (Linear.weight is [out][in], fp32).  With the step kernel it makes a rollout step two launches, and a
-// rollout one CUDA graph.  A block serves PE envs with 2 * PH threads: thread (tower, unit) owns one hidden unit of one tower and
-// keeps PE accumulators; inputs / activations live in shared memory feature-major ([k][env]), so that a weight is loaded once
-// (read-only path) and meets sixteen activations with four 16-byte shared loads.  fp32 FMA in k order; tanhf.
+// rollout one CUDA graph.
+// A block serves PE = 32 envs with 256 threads.  The 2 x 64 hidden units of the two towers are one 128-wide output row; a thread
+// owns FOUR adjacent units (lane -> unit group, so a warp spans the whole row) for FOUR envs (warp -> env group): 16 accumulators,
+// and per k step one 16-byte shared load of weights (distinct per lane, conflict-free) and one of activations (warp-uniform) feed
+// 16 FMAs.  At 4096 envs the launch is 128 blocks on 148 SMs, so it is latency-, not throughput-bound (profiles/r2_k5_policy.txt: one
+// block alone takes as long as 128); 4 x 8 tiles at 128 threads and 4 x 2 tiles at 512 threads both measured slower.  Both layers'
+// weights are requested up front with cp.async (4-byte copies, transposed on the way: wt[k][tower * 64 + unit]) -- one round trip
+// in all, not one per element.  fp32 FMA in k order; tanh on the fast exponential.
 // ------------------------------------------------------------------------------------------------
-constexpr int PE = 16, PH = 64, PWS = PH + 1;                      // PWS: row stride of a transposed weight tile (bank = (k + u) % 32)
+#ifndef EWN_PT
+#define EWN_PT 256
+#endif
+constexpr int PE = 32, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PEV = 4 (2) envs per thread at 256 (512) threads   // PWS: row stride of a transposed weight tile (16-byte aligned rows)
 struct PolicyNet {
     const float *w1[2], *b1[2], *w2[2], *b2[2];      // [0] = pi tower, [1] = vf tower: Linear(F, 64), Linear(64, 64)
     const float *wa, *ba, *wv, *bv;                  // action_net Linear(64, 5), value_net Linear(64, 1)
 };
 enum { TAG_POLICY = 3 };
-inline size_t policy_smem(int F) { return ((size_t)F * PE + 4 * (size_t)PH * PE + 6 * PE + 2 * (size_t)(F > PH ? F : PH) * PWS) * sizeof(float); }
-__global__ void __launch_bounds__(2 * PH) k_policy_forward(const int16_t* board, const int64_t* dice, int64_t n, int NN, int D, PolicyNet net,
-                                                             u64 seed, u64 step, const unsigned long long* step_dev, u64 env_id0, int deterministic,
-                                                             int64_t* actions, float* values, float* logp, float* logits_out) {
+inline size_t policy_smem(int F) { return ((size_t)F * PE + 2 * (size_t)PO * PE + 6 * PE + 10 * PH + 8 + (size_t)(F + PH) * PWS) * sizeof(float); }
+__global__ void __launch_bounds__(PT) k_policy_forward(const int16_t* board, const int64_t* dice, int64_t n, int NN, int D, PolicyNet net,
+                                                       u64 seed, u64 step, const unsigned long long* step_dev, u64 env_id0, int deterministic,
+                                                       int64_t* actions, float* values, float* logp, float* logits_out) {
     extern __shared__ float4 pol_smem[];
-    float* const x = reinterpret_cast<float*>(pol_smem);         // [F][PE]
     const int F = NN + D;
-    float* const h1 = x + (size_t)F * PE;                          // [2][PH][PE]
-    float* const h2 = h1 + 2 * PH * PE;                            // [2][PH][PE]
-    float* const outv = h2 + 2 * PH * PE;                          // [6][PE]: five logits and the value
-    float* const wt = outv + 6 * PE;                               // [2][K][PWS]: the layer's weights of both towers, transposed
-    const int tid = threadIdx.x;
+    float* const wt1 = reinterpret_cast<float*>(pol_smem);       // [F][PWS]   layer 1, both towers, transposed
+    float* const wt2 = wt1 + (size_t)F * PWS;                      // [PH][PWS]  layer 2
+    float* const x = wt2 + (size_t)PH * PWS;                       // [F][PE]    features, feature-major
+    float* const h1 = x + (size_t)F * PE;                          // [PO][PE]   row = tower * 64 + unit
+    float* const h2 = h1 + (size_t)PO * PE;                        // [PO][PE]
+    float* const outv = h2 + (size_t)PO * PE;                      // [6][PE]: five logits and the value
+    float* const small = outv + 6 * PE;                            // b1[2][64], b2[2][64], action_net w[5][64], value_net w[64], their six biases
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t e0 = (int64_t)blockIdx.x * PE;
     const int ne = (int)min((int64_t)PE, n - e0);
-    // a layer's weights [PH][K] of both towers -> wt[tower][k][unit]: coalesced global reads (every block reads the same 29 / 33 KB: L2
-    // hits), conflict-free shared stores and loads thanks to the odd row stride.  Reading W[unit][k] straight from global in the k loop
-    // costs 32 sectors per load instruction (a warp's units are 224 / 256 bytes apart): measured 20 us per launch instead of 5.
-    auto stage = [&](const float* wa_, const float* wb_, int K) {
-        for (int idx = tid; idx < PH * K; idx += 2 * PH) {
-            const int u = idx / K, k = idx - u * K;
-            wt[k * PWS + u] = __ldg(wa_ + idx);
-            wt[(K + k) * PWS + u] = __ldg(wb_ + idx);
+    // W[tower][unit][k] -> dst[k][tower * 64 + unit].  Rows of a multiple of four floats (7x7: 56, 5x5: 32, layer 2: 64): a thread takes
+    // 16-byte pieces of ONE output row (lanes = adjacent rows: 32 sectors per load, twice the minimum, but conflict-free transposed
+    // stores), all loads of a layer in flight before the first store.  Other widths: 4-byte cp.async, a warp per row.
+    auto stage = [&](float* dst, const float* wa_, const float* wb_, int K) {
+        if ((K & 3) == 0 && K <= 64) {
+            constexpr int TPR = PT / PO, NQ = 16 / TPR;                     // threads per row, 16-byte pieces per thread
+            const int r = tid & (PO - 1), c0 = tid / PO, nc = K >> 2;
+            const float4* src = reinterpret_cast<const float4*>(r < PH ? wa_ + (size_t)r * K : wb_ + (size_t)(r - PH) * K);
+            float4 v[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; q++) { const int c = c0 + TPR * q; if (c < nc) v[q] = __ldg(src + c); }
+#pragma unroll
+            for (int q = 0; q < NQ; q++) {
+                const int c = c0 + TPR * q;
+                if (c < nc) { float* d = dst + (size_t)(4 * c) * PWS + r; d[0] = v[q].x; d[PWS] = v[q].y; d[2 * PWS] = v[q].z; d[3 * PWS] = v[q].w; }
+            }
+        } else {
+            for (int r = warp; r < PO; r += PT / 32) {
+                const float* src = (r < PH ? wa_ + (size_t)r * K : wb_ + (size_t)(r - PH) * K);
+                const unsigned d = (unsigned)__cvta_generic_to_shared(dst + r);
+                for (int k = lane; k < K; k += 32) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + (unsigned)(k * PWS * 4)), "l"(src + k) : "memory");
+            }
         }
     };
-    stage(net.w1[0], net.w1[1], F);
-    for (int idx = tid; idx < PE * NN; idx += 2 * PH) {          // Flatten(board) as float: SB3 does not rescale a non-image Box
+    // biases of the four hidden layers and the two heads' weights and biases: small, but a load from L2 in the middle of a phase is a
+    // round trip nobody hides at one or two warps per scheduler
+    for (int idx = tid; idx < 4 * PH + 6 * PH + 6; idx += PT) {
+        const float* src = idx < PH ? net.b1[0] + idx : idx < 2 * PH ? net.b1[1] + (idx - PH) : idx < 3 * PH ? net.b2[0] + (idx - 2 * PH)
+                         : idx < 4 * PH ? net.b2[1] + (idx - 3 * PH) : idx < 9 * PH ? net.wa + (idx - 4 * PH) : idx < 10 * PH ? net.wv + (idx - 9 * PH)
+                         : idx < 10 * PH + 5 ? net.ba + (idx - 10 * PH) : net.bv;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(small + idx)), "l"(src) : "memory");
+    }
+#if !defined(EWN_EXP_POL_NOSTAGE)
+    stage(wt1, net.w1[0], net.w1[1], F);
+    stage(wt2, net.w2[0], net.w2[1], PH);
+#endif
+    for (int idx = tid; idx < PE * NN; idx += PT) {              // Flatten(board) as float: SB3 does not rescale a non-image Box
         const int e = idx / NN, k = idx - e * NN;
         x[k * PE + e] = e < ne ? (float)board[(e0 + e) * NN + k] : 0.f;
     }
-    for (int idx = tid; idx < PE * D; idx += 2 * PH) {           // one-hot(Discrete(cube_num + 1, start = 1)): index dice - 1
+    for (int idx = tid; idx < PE * D; idx += PT) {               // one-hot(Discrete(cube_num + 1, start = 1)): index dice - 1
         const int e = idx / D, d = idx - e * D;
         int v = e < ne ? (int)dice[e0 + e] - 1 : -1;
         v = v < 0 ? 0 : (v > D - 1 ? D - 1 : v);
         x[(NN + d) * PE + e] = (e < ne && d == v) ? 1.f : 0.f;
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
-    const int p = tid / PH, u = tid - p * PH;                      // tower, hidden unit
-    float acc[PE];
-    auto layer = [&](float bias, const float* in, int K) {
-        const float* w = wt + (size_t)p * K * PWS + u;
+    const int tower = lane >> 4;                                   // this thread's four units: rows 4 * lane .. 4 * lane + 3 of the output
+    static_assert(PEV == 2 || PEV == 4, "one float2 / float4 of activations per k step");
+    float acc[4][PEV];
+    auto layer = [&](const float* wl, const float* bias, const float* in, int K) {
 #pragma unroll
-        for (int e = 0; e < PE; e++) acc[e] = bias;
+        for (int j = 0; j < 4; j++) {
+            const float b = bias[4 * lane + j];
+#pragma unroll
+            for (int e = 0; e < PEV; e++) acc[j][e] = b;
+        }
+        const float* w = wl + 4 * lane;
+        in += PEV * warp;
+#if defined(EWN_EXP_POL_NOLAYER)
+        K = 0;
+#endif
 #pragma unroll 4
         for (int k = 0; k < K; k++) {
-            const float wk = w[k * PWS];
-            const float4* v = reinterpret_cast<const float4*>(in + (size_t)k * PE);
+            const float4 w4 = *reinterpret_cast<const float4*>(w + (size_t)k * PWS);
+            float av[PEV];
+            if (PEV == 4) { const float4 a0 = *reinterpret_cast<const float4*>(in + (size_t)k * PE); av[0] = a0.x; av[1] = a0.y; av[PEV - 2] = a0.z; av[PEV - 1] = a0.w; }
+            else { const float2 a0 = *reinterpret_cast<const float2*>(in + (size_t)k * PE); av[0] = a0.x; av[1] = a0.y; }
+            const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-            for (int q = 0; q < PE / 4; q++) {
-                const float4 a = v[q];
-                acc[4 * q] = fmaf(wk, a.x, acc[4 * q]); acc[4 * q + 1] = fmaf(wk, a.y, acc[4 * q + 1]);
-                acc[4 * q + 2] = fmaf(wk, a.z, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(wk, a.w, acc[4 * q + 3]);
-            }
+            for (int j = 0; j < 4; j++)
+#pragma unroll
+                for (int e = 0; e < PEV; e++) acc[j][e] = fmaf(wv[j], av[e], acc[j][e]);
         }
     };
-    // (towers are picked with selects: a run-time index into the parameter struct would put a copy of it in local memory)
-    layer(__ldg((p ? net.b1[1] : net.b1[0]) + u), x, F);
-    {
-        float4* o = reinterpret_cast<float4*>(h1 + ((size_t)p * PH + u) * PE);
+    // tanh(v) = 1 - 2 / (1 + e^(2v)) on the fast exponential and reciprocal: absolute error ~1e-7 (the accurate tanhf is ~35 instructions
+    // and was a quarter of the kernel); saturates correctly (e^(2v) = inf -> 1, = 0 -> -1)
+    auto th = [](float v) { return 1.f - __fdividef(2.f, __expf(2.f * v) + 1.f); };
+    auto squash = [&](float* h) {                                  // tanh of the sums -> h[tower * 64 + unit][env]
 #pragma unroll
-        for (int q = 0; q < PE / 4; q++) o[q] = make_float4(tanhf(acc[4 * q]), tanhf(acc[4 * q + 1]), tanhf(acc[4 * q + 2]), tanhf(acc[4 * q + 3]));
-    }
-    __syncthreads();                                               // h1 complete, layer-1 weights no longer read
-    stage(net.w2[0], net.w2[1], PH);
+        for (int j = 0; j < 4; j++)
+            if (PEV == 4) *reinterpret_cast<float4*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float4(th(acc[j][0]), th(acc[j][1]), th(acc[j][PEV - 2]), th(acc[j][PEV - 1]));
+            else *reinterpret_cast<float2*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float2(th(acc[j][0]), th(acc[j][1]));
+    };
+    layer(wt1, small, x, F);
+    squash(h1);
     __syncthreads();
-    layer(__ldg((p ? net.b2[1] : net.b2[0]) + u), h1 + (size_t)p * PH * PE, PH);
-    {
-        float4* o = reinterpret_cast<float4*>(h2 + ((size_t)p * PH + u) * PE);
-#pragma unroll
-        for (int q = 0; q < PE / 4; q++) o[q] = make_float4(tanhf(acc[4 * q]), tanhf(acc[4 * q + 1]), tanhf(acc[4 * q + 2]), tanhf(acc[4 * q + 3]));
-    }
+    layer(wt2, small + 2 * PH, h1 + (size_t)tower * PH * PE, PH);
+    squash(h2);
     __syncthreads();
-    if (tid < 6 * PE) {                                           // heads: (output o, env e)
-        const int o = tid / PE, e = tid - o * PE;
-        const float* w = o < 5 ? net.wa + (size_t)o * PH : net.wv;
-        const float* in = h2 + (size_t)(o < 5 ? 0 : 1) * PH * PE + e;
-        float a = o < 5 ? __ldg(net.ba + o) : __ldg(net.bv);
+    for (int idx = tid; idx < 6 * PE; idx += PT) {               // heads: (output o, env e)
+        const int o = idx / PE, e = idx - o * PE;
+        const float* w = small + 4 * PH + o * PH;                 // action_net rows 0..4, then value_net
+        const float* in = h2 + (size_t)(o < 5 ? 0 : PH) * PE + e;
+        float a = small[10 * PH + o];
 #pragma unroll 8
-        for (int k = 0; k < PH; k++) a = fmaf(__ldg(w + k), in[(size_t)k * PE], a);
+        for (int k = 0; k < PH; k++) a = fmaf(w[k], in[(size_t)k * PE], a);
         outv[o * PE + e] = a;
     }
     __syncthreads();
@@ -1614,19 +1658,33 @@ __global__ void __launch_bounds__(2 * PH) k_policy_forward(const int16_t* board,
 // RolloutBuffer.compute_returns_and_advantage (GAE; A2C: lambda = 1) for rewards / values / dones laid out [T][n]; dones[t] = the
 // episode ended at step t (= episode_starts[t + 1]).  One thread per env walks t downwards; fp32, rounded operation by operation
 // in torch's order (no contraction), so the result equals the tensor loop of OnPolicyAlgorithm bit for bit.
-__global__ void __launch_bounds__(TPB) k_gae(const float* rewards, const float* values, const uint8_t* dones, const float* last_values, int T,
-                                             int64_t n, float gamma, float gamma_lambda, float* adv, float* returns) {
+__global__ void __launch_bounds__(TPB) k_gae(const float* __restrict__ rewards, const float* __restrict__ values, const uint8_t* __restrict__ dones,
+                                             const float* __restrict__ last_values, int T, int64_t n, float gamma, float gamma_lambda,
+                                             float* __restrict__ adv, float* __restrict__ returns) {
     const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
     if (i >= n) return;
     float gae = 0.f, next_v = last_values[i];
-    for (int t = T - 1; t >= 0; t--) {
-        const size_t k = (size_t)t * n + i;
-        const float nt = __fsub_rn(1.0f, dones[k] ? 1.0f : 0.0f), v = values[k];
-        const float delta = __fsub_rn(__fadd_rn(rewards[k], __fmul_rn(__fmul_rn(gamma, next_v), nt)), v);
-        gae = __fadd_rn(delta, __fmul_rn(__fmul_rn(gamma_lambda, nt), gae));
-        adv[k] = gae;
-        if (returns) returns[k] = __fadd_rn(gae, v);
-        next_v = v;
+    constexpr int CHK = 8;                                         // the loads of eight steps are issued together: the walk is a chain of
+    for (int t1 = T; t1 > 0; t1 -= CHK) {                          // dependent adds, not of dependent DRAM round trips
+        float r[CHK], v[CHK]; uint8_t d[CHK];
+#pragma unroll
+        for (int q = 0; q < CHK; q++) {
+            const int t = t1 - 1 - q;
+            const size_t k = (size_t)(t < 0 ? 0 : t) * n + i;
+            r[q] = rewards[k]; v[q] = values[k]; d[q] = dones[k];
+        }
+#pragma unroll
+        for (int q = 0; q < CHK; q++) {
+            const int t = t1 - 1 - q;
+            if (t < 0) break;
+            const size_t k = (size_t)t * n + i;
+            const float nt = __fsub_rn(1.0f, d[q] ? 1.0f : 0.0f);
+            const float delta = __fsub_rn(__fadd_rn(r[q], __fmul_rn(__fmul_rn(gamma, next_v), nt)), v[q]);
+            gae = __fadd_rn(delta, __fmul_rn(__fmul_rn(gamma_lambda, nt), gae));
+            adv[k] = gae;
+            if (returns) returns[k] = __fadd_rn(gae, v[q]);
+            next_v = v[q];
+        }
     }
 }
 
@@ -2078,7 +2136,7 @@ int ewn_policy_forward(const ewn_policy_net* net, const int16_t* board, const in
             done[dev] = true;
         }
     }
-    k_policy_forward<<<grid, 2 * PH, sm, (cudaStream_t)stream>>>(board, dice, n, NN, D, pn, seed, step, reinterpret_cast<const unsigned long long*>(step_dev),
+    k_policy_forward<<<grid, PT, sm, (cudaStream_t)stream>>>(board, dice, n, NN, D, pn, seed, step, reinterpret_cast<const unsigned long long*>(step_dev),
                                                                  env_id0, deterministic, actions, values, logp, logits);
     LAUNCHED("k_policy_forward");
     return EWN_OK;
