@@ -373,6 +373,11 @@ k_step(const __grid_constant__ StepKArgs ka) {
     const int lane = tid & 31, warp = tid >> 5;
     const bool mine = i < n;
     const bool compact = a.term_count != nullptr;
+    // programmatic dependent launch (as k_vstep): the next kernel of the stream / graph may be scheduled while this grid runs, and nothing
+    // here touches global memory before the previous grid has completed.  A rollout of small batches is a chain of launch gaps: this
+    // shortens every one of them.  No-ops without the launch attribute.
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (tid == 0) {
         s_tot = 0;
         if (a.term_count_clear && blockIdx.x == 0) *a.term_count_clear = 0u;
@@ -2036,9 +2041,12 @@ int ewn_step(const ewn_step_args* a, void* stream) {
 #define LAUNCH_STEP(C, NT)                                                                           \
     do {                                                                                             \
         size_t sm = need_smem ? step_smem(ka.p.geo) : 0;                                             \
-        if (vec) k_step<C, NT, false, false, true><<<grid, STPB, sm, st>>>(ka);                       \
-        else if (replay) { if (a->shaped) k_step<C, NT, true, true, false><<<grid, STPB, sm, st>>>(ka); else k_step<C, NT, true, false, false><<<grid, STPB, sm, st>>>(ka); } \
-        else        { if (a->shaped) k_step<C, NT, false, true, false><<<grid, STPB, sm, st>>>(ka); else k_step<C, NT, false, false, false><<<grid, STPB, sm, st>>>(ka); } \
+        const bool pdl_ = !(a->flags & EWN_STEP_NO_PDL);                                             \
+        cudaError_t le_;                                                                             \
+        if (vec) le_ = launch_k(k_step<C, NT, false, false, true>, grid, STPB, sm, st, pdl_, ka);     \
+        else if (replay) { if (a->shaped) le_ = launch_k(k_step<C, NT, true, true, false>, grid, STPB, sm, st, pdl_, ka); else le_ = launch_k(k_step<C, NT, true, false, false>, grid, STPB, sm, st, pdl_, ka); } \
+        else        { if (a->shaped) le_ = launch_k(k_step<C, NT, false, true, false>, grid, STPB, sm, st, pdl_, ka); else le_ = launch_k(k_step<C, NT, false, false, false>, grid, STPB, sm, st, pdl_, ka); } \
+        if (le_ != cudaSuccess) return cuda_fail(le_, "k_step");                                     \
     } while (0)
     const int N = a->board_size;
     // the VecEnv surface with compacted (or no) terminal observations runs on the persistent kernel
