@@ -757,6 +757,9 @@ k_vstep(const __grid_constant__ StepKArgs ka, const int cap) {
     const int u_end = n_units;
 #endif
     while (u < u_end) {                                            // block-uniform
+#if defined(EWN_EXP_VSYNC)       /* experiment build: the block's warps walk in lock step (the warp scheduler is not fair: profiles/r2_k1_timeline.txt) */
+        __syncthreads();
+#endif
         asm volatile("cp.async.wait_all;" ::: "memory");
 #if defined(EWN_EXP_TIMELINE)
         if (it_ < 8) EWN_TL(2 + it_);
