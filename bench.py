@@ -493,9 +493,9 @@ def run_ours(args, rank, world, local_rank):
         try:
             from ewn_gym_b200.device_env import EWNDeviceVecEnv
             from ewn_gym_b200.train import A2C
-            for key, fused in (("with_policy", True), ("with_policy_eager", False)):
+            for key, fused, persistent in (("with_policy", True, True), ("with_policy_graph", True, False), ("with_policy_eager", False, False)):
                 penv = EWNDeviceVecEnv(n7, 7, 3, seed=SEED + 7, shaped=True, env_id0=rank * n7, engine=e7)
-                a2c = A2C("MultiInputPolicy", penv, n_steps=T, seed=rank, fused=fused)
+                a2c = A2C("MultiInputPolicy", penv, n_steps=T, seed=rank, fused=fused, persistent=persistent)
                 a2c.collect_rollouts(); a2c.train(); torch.cuda.synchronize()
                 if dist: dist.barrier()
                 reps = 20 if fused else 3
@@ -511,10 +511,13 @@ def run_ours(args, rank, world, local_rank):
                     tt = torch.tensor([pms, tms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); pms, tms = tt.tolist()
                 rollout[key] = {"ms_per_rollout": pms, "env_steps_per_s": n7 * world * T / (pms / 1e3), "a2c_update_ms": tms,
                                 "policy": "MultiInputPolicy (board + one-hot dice -> 64-64 Tanh towers)",
-                                "collector": ("one CUDA graph per rollout: per step ewn_policy_forward (forward + categorical draw, one launch) and the env "
+                                "collector": ("ONE launch per rollout (ewn_rollout): policy forward + categorical draw and env step alternate on chip for all "
+                                              "128 steps, games in registers, parameters staged once, then V(last) and GAE; buffers bit-identical to the "
+                                              "two-launches-per-step graph" if persistent else
+                                              "one CUDA graph per rollout: per step ewn_policy_forward (forward + categorical draw, one launch) and the env "
                                               "step kernel writing straight into the rollout buffer, then V(last), ewn_gae" if fused else
-                                              "eager torch modules between env.step calls (the round-1/2 path, kept for policies of another shape)"),
-                                "launches_per_rollout": 2 * T + 7 if fused else None,
+                                              "eager torch modules between env.step calls (kept for policies of another shape)"),
+                                "launches_per_rollout": 6 if persistent else 2 * T + 7 if fused else None,
                                 "episodes_last_rollout": a2c.logger.get("rollout/episodes")}
                 penv.close()
         except Exception as err:                     # noqa: BLE001

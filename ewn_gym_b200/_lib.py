@@ -45,6 +45,15 @@ class PolicyNet(C.Structure):
         "pi_w1", "pi_b1", "pi_w2", "pi_b2", "vf_w1", "vf_b1", "vf_w2", "vf_b2", "action_w", "action_b", "value_w", "value_b")]
 
 
+class RolloutArgs(C.Structure):
+    """struct ewn_rollout_args"""
+    _fields_ = [("state", p_void), ("n", i64), ("board_size", i32), ("cube_layer", i32), ("T", i32), ("shaped", i32), ("net", C.POINTER(PolicyNet)),
+                ("board", p_void), ("dice", p_void), ("actions", p_void), ("rewards", p_void), ("dones", p_void), ("values", p_void), ("logp", p_void),
+                ("last_values", p_void), ("advantages", p_void), ("returns", p_void), ("tolerance", p_void), ("prev_score", p_void), ("stats", p_void),
+                ("reward", C.c_double), ("illegal_move_reward", C.c_double), ("seed", u64), ("step", u64), ("env_id0", u64), ("step_dev", p_void),
+                ("policy_seed", u64), ("gamma", C.c_double), ("gae_lambda", C.c_double)]
+
+
 class VecConfig(C.Structure):
     """struct ewn_vec_config"""
     _fields_ = [
@@ -88,6 +97,7 @@ PROTOTYPES = {
     "ewn_step_dice": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, u64, u64, u64, p_void, p_void]),
     "ewn_policy_forward": (C.c_int, [C.POINTER(PolicyNet), p_void, p_void, i64, C.c_int, C.c_int, u64, u64, p_void, u64, C.c_int, p_void, p_void, p_void,
                                      p_void, p_void]),
+    "ewn_rollout": (C.c_int, [C.POINTER(RolloutArgs), p_void]),
     "ewn_gae": (C.c_int, [p_void, p_void, p_void, p_void, C.c_int, i64, C.c_double, C.c_double, p_void, p_void, p_void]),
     "ewn_evaluate": (C.c_int, [p_void, p_void, i64, C.c_int, C.c_int, C.c_int, p_void]),
     "ewn_expectiminimax_workspace": (C.c_size_t, [i64, C.c_int]),
@@ -117,7 +127,7 @@ PROTOTYPES = {
 # entry points a host simulator (tests/hostsim) does not provide
 _VEC_ONLY = {"ewn_vec_create", "ewn_vec_destroy", "ewn_vec_reset", "ewn_vec_step", "ewn_vec_step2", "ewn_vec_set_seed", "ewn_host_alloc", "ewn_host_free",
              "ewn_vec_state", "ewn_vec_step_index", "ewn_device_pci_bus_id",
-             "ewn_mc_static_max_roots", "ewn_mc_predict_static", "ewn_policy_forward", "ewn_gae"}          # (device-memory entry points: the test-only host build has none)
+             "ewn_mc_static_max_roots", "ewn_mc_predict_static", "ewn_policy_forward", "ewn_gae", "ewn_rollout"}          # (device-memory entry points: the test-only host build has none)
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

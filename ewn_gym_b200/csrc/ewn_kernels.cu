@@ -1510,28 +1510,31 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 #ifndef EWN_PT
 #define EWN_PT 256
 #endif
-constexpr int PE = 32, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PEV = 4 (2) envs per thread at 256 (512) threads   // PWS: row stride of a transposed weight tile (16-byte aligned rows)
+constexpr int PE = 32, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PWS: row stride of a transposed weight
+                                                                   // tile (16-byte aligned rows); PEV = 4 (2) envs per thread at 256 (512) threads
 struct PolicyNet {
     const float *w1[2], *b1[2], *w2[2], *b2[2];      // [0] = pi tower, [1] = vf tower: Linear(F, 64), Linear(64, 64)
     const float *wa, *ba, *wv, *bv;                  // action_net Linear(64, 5), value_net Linear(64, 1)
 };
 enum { TAG_POLICY = 3 };
-inline size_t policy_smem(int F) { return ((size_t)F * PE + 2 * (size_t)PO * PE + 6 * PE + 10 * PH + 8 + (size_t)(F + PH) * PWS) * sizeof(float); }
-__global__ void __launch_bounds__(PT) k_policy_forward(const int16_t* board, const int64_t* dice, int64_t n, int NN, int D, PolicyNet net,
-                                                       u64 seed, u64 step, const unsigned long long* step_dev, u64 env_id0, int deterministic,
-                                                       int64_t* actions, float* values, float* logp, float* logits_out) {
-    extern __shared__ float4 pol_smem[];
-    const int F = NN + D;
-    float* const wt1 = reinterpret_cast<float*>(pol_smem);       // [F][PWS]   layer 1, both towers, transposed
-    float* const wt2 = wt1 + (size_t)F * PWS;                      // [PH][PWS]  layer 2
-    float* const x = wt2 + (size_t)PH * PWS;                       // [F][PE]    features, feature-major
-    float* const h1 = x + (size_t)F * PE;                          // [PO][PE]   row = tower * 64 + unit
-    float* const h2 = h1 + (size_t)PO * PE;                        // [PO][PE]
-    float* const outv = h2 + (size_t)PO * PE;                      // [6][PE]: five logits and the value
-    float* const small = outv + 6 * PE;                            // b1[2][64], b2[2][64], action_net w[5][64], value_net w[64], their six biases
+// shared memory of one block: the two layers' weights of both towers (transposed), features, activations, head outputs, small parameters
+struct PolSmem { float *wt1, *wt2, *x, *h1, *h2, *outv, *small; };
+constexpr int POL_SMALL = 10 * PH + 8;               // b1[2][64], b2[2][64], action_net w[5][64], value_net w[64], their six biases
+inline size_t policy_smem(int F) { return ((size_t)F * PE + 2 * (size_t)PO * PE + 6 * PE + POL_SMALL + (size_t)(F + PH) * PWS) * sizeof(float); }
+__device__ __forceinline__ PolSmem pol_carve(float* base, int F) {
+    PolSmem m;
+    m.wt1 = base;                                    // [F][PWS]   layer 1, both towers, transposed
+    m.wt2 = m.wt1 + (size_t)F * PWS;                 // [PH][PWS]  layer 2
+    m.x = m.wt2 + (size_t)PH * PWS;                  // [F][PE]    features, feature-major
+    m.h1 = m.x + (size_t)F * PE;                     // [PO][PE]   row = tower * 64 + unit
+    m.h2 = m.h1 + (size_t)PO * PE;                   // [PO][PE]
+    m.outv = m.h2 + (size_t)PO * PE;                 // [6][PE]: five logits and the value
+    m.small = m.outv + 6 * PE;
+    return m;
+}
+// request all parameters (no wait: cp.async.wait_all + __syncthreads by the caller)
+__device__ __forceinline__ void pol_stage(const PolSmem& m, const PolicyNet& net, int F) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t e0 = (int64_t)blockIdx.x * PE;
-    const int ne = (int)min((int64_t)PE, n - e0);
     // W[tower][unit][k] -> dst[k][tower * 64 + unit].  Rows of a multiple of four floats (7x7: 56, 5x5: 32, layer 2: 64): a thread takes
     // 16-byte pieces of ONE output row (lanes = adjacent rows: 32 sectors per load, twice the minimum, but conflict-free transposed
     // stores), all loads of a layer in flight before the first store.  Other widths: 4-byte cp.async, a warp per row.
@@ -1562,24 +1565,17 @@ __global__ void __launch_bounds__(PT) k_policy_forward(const int16_t* board, con
         const float* src = idx < PH ? net.b1[0] + idx : idx < 2 * PH ? net.b1[1] + (idx - PH) : idx < 3 * PH ? net.b2[0] + (idx - 2 * PH)
                          : idx < 4 * PH ? net.b2[1] + (idx - 3 * PH) : idx < 9 * PH ? net.wa + (idx - 4 * PH) : idx < 10 * PH ? net.wv + (idx - 9 * PH)
                          : idx < 10 * PH + 5 ? net.ba + (idx - 10 * PH) : net.bv;
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(small + idx)), "l"(src) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(m.small + idx)), "l"(src) : "memory");
     }
 #if !defined(EWN_EXP_POL_NOSTAGE)
-    stage(wt1, net.w1[0], net.w1[1], F);
-    stage(wt2, net.w2[0], net.w2[1], PH);
+    stage(m.wt1, net.w1[0], net.w1[1], F);
+    stage(m.wt2, net.w2[0], net.w2[1], PH);
 #endif
-    for (int idx = tid; idx < PE * NN; idx += PT) {              // Flatten(board) as float: SB3 does not rescale a non-image Box
-        const int e = idx / NN, k = idx - e * NN;
-        x[k * PE + e] = e < ne ? (float)board[(e0 + e) * NN + k] : 0.f;
-    }
-    for (int idx = tid; idx < PE * D; idx += PT) {               // one-hot(Discrete(cube_num + 1, start = 1)): index dice - 1
-        const int e = idx / D, d = idx - e * D;
-        int v = e < ne ? (int)dice[e0 + e] - 1 : -1;
-        v = v < 0 ? 0 : (v > D - 1 ? D - 1 : v);
-        x[(NN + d) * PE + e] = (e < ne && d == v) ? 1.f : 0.f;
-    }
-    asm volatile("cp.async.wait_all;" ::: "memory");
-    __syncthreads();
+}
+// x (features of the block's PE envs) and the parameters are in shared memory and visible: two hidden layers of both towers and the
+// heads -> m.outv[6][PE].  Ends with a block barrier.
+__device__ __forceinline__ void pol_layers(const PolSmem& m, int F) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tower = lane >> 4;                                   // this thread's four units: rows 4 * lane .. 4 * lane + 3 of the output
     static_assert(PEV == 2 || PEV == 4, "one float2 / float4 of activations per k step");
     float acc[4][PEV];
@@ -1617,50 +1613,202 @@ __global__ void __launch_bounds__(PT) k_policy_forward(const int16_t* board, con
             if (PEV == 4) *reinterpret_cast<float4*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float4(th(acc[j][0]), th(acc[j][1]), th(acc[j][PEV - 2]), th(acc[j][PEV - 1]));
             else *reinterpret_cast<float2*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float2(th(acc[j][0]), th(acc[j][1]));
     };
-    layer(wt1, small, x, F);
-    squash(h1);
+    layer(m.wt1, m.small, m.x, F);
+    squash(m.h1);
     __syncthreads();
-    layer(wt2, small + 2 * PH, h1 + (size_t)tower * PH * PE, PH);
-    squash(h2);
+    layer(m.wt2, m.small + 2 * PH, m.h1 + (size_t)tower * PH * PE, PH);
+    squash(m.h2);
     __syncthreads();
     for (int idx = tid; idx < 6 * PE; idx += PT) {               // heads: (output o, env e)
         const int o = idx / PE, e = idx - o * PE;
-        const float* w = small + 4 * PH + o * PH;                 // action_net rows 0..4, then value_net
-        const float* in = h2 + (size_t)(o < 5 ? 0 : PH) * PE + e;
-        float a = small[10 * PH + o];
+        const float* w = m.small + 4 * PH + o * PH;               // action_net rows 0..4, then value_net
+        const float* in = m.h2 + (size_t)(o < 5 ? 0 : PH) * PE + e;
+        float a = m.small[10 * PH + o];
 #pragma unroll 8
         for (int k = 0; k < PH; k++) a = fmaf(w[k], in[(size_t)k * PE], a);
-        outv[o * PE + e] = a;
+        m.outv[o * PE + e] = a;
     }
     __syncthreads();
+}
+// the draw for env e of the block (global index i) from m.outv: Categorical(logits) x 2 (normalised logits = logits - logsumexp, probs =
+// softmax: torch.distributions), Philox block of (seed; env id, step), tag POLICY.  -> action pair, log-probability
+__device__ __forceinline__ void pol_draw(const float* outv, int e, u64 env, u64 seed, u64 st, int deterministic, int& a0, int& a1, float& lp) {
+    const float l0 = outv[e], l1 = outv[PE + e], m0 = outv[2 * PE + e], m1 = outv[3 * PE + e], m2 = outv[4 * PE + e];
+    const float mx = fmaxf(l0, l1), z = mx + logf(expf(l0 - mx) + expf(l1 - mx));
+    const float my = fmaxf(m0, fmaxf(m1, m2)), zy = my + logf(expf(m0 - my) + expf(m1 - my) + expf(m2 - my));
+    if (deterministic) {                                          // probs.argmax: the first maximum
+        a0 = l1 > l0 ? 1 : 0;
+        a1 = (m1 > m0 ? (m2 > m1 ? 2 : 1) : (m2 > m0 ? 2 : 0));
+    } else {
+        u32 blk[4];
+        philox4x32_10((u32)env, (u32)(env >> 32), (u32)st, ((u32)(st >> 32) & 0x0FFFFFFFu) | ((u32)TAG_POLICY << 28), (u32)seed, (u32)(seed >> 32), blk);
+        const float r0 = (float)(blk[0] >> 8) * (1.0f / 16777216.0f), r1 = (float)(blk[1] >> 8) * (1.0f / 16777216.0f);   // [0, 1)
+        a0 = r0 < expf(l0 - z) ? 0 : 1;
+        const float q0 = expf(m0 - zy), q1 = expf(m1 - zy);
+        a1 = r1 < q0 ? 0 : (r1 < q0 + q1 ? 1 : 2);
+    }
+    lp = ((a0 ? l1 : l0) - z) + ((a1 == 0 ? m0 : a1 == 1 ? m1 : m2) - zy);
+}
+
+__global__ void __launch_bounds__(PT) k_policy_forward(const int16_t* board, const int64_t* dice, int64_t n, int NN, int D, PolicyNet net,
+                                                       u64 seed, u64 step, const unsigned long long* step_dev, u64 env_id0, int deterministic,
+                                                       int64_t* actions, float* values, float* logp, float* logits_out) {
+    extern __shared__ float4 pol_smem[];
+    const int F = NN + D;
+    const PolSmem m = pol_carve(reinterpret_cast<float*>(pol_smem), F);
+    const int tid = threadIdx.x;
+    const int64_t e0 = (int64_t)blockIdx.x * PE;
+    const int ne = (int)min((int64_t)PE, n - e0);
+    pol_stage(m, net, F);
+    for (int idx = tid; idx < PE * NN; idx += PT) {              // Flatten(board) as float: SB3 does not rescale a non-image Box
+        const int e = idx / NN, k = idx - e * NN;
+        m.x[k * PE + e] = e < ne ? (float)board[(e0 + e) * NN + k] : 0.f;
+    }
+    for (int idx = tid; idx < PE * D; idx += PT) {               // one-hot(Discrete(cube_num + 1, start = 1)): index dice - 1
+        const int e = idx / D, d = idx - e * D;
+        int v = e < ne ? (int)dice[e0 + e] - 1 : -1;
+        v = v < 0 ? 0 : (v > D - 1 ? D - 1 : v);
+        m.x[(NN + d) * PE + e] = (e < ne && d == v) ? 1.f : 0.f;
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    pol_layers(m, F);
     if (tid < ne) {
         const int e = tid;
         const int64_t i = e0 + e;
-        const float l0 = outv[e], l1 = outv[PE + e], m0 = outv[2 * PE + e], m1 = outv[3 * PE + e], m2 = outv[4 * PE + e];
-        if (values) values[i] = outv[5 * PE + e];
-        if (logits_out) { float* q = logits_out + 5 * i; q[0] = l0; q[1] = l1; q[2] = m0; q[3] = m1; q[4] = m2; }
+        if (values) values[i] = m.outv[5 * PE + e];
+        if (logits_out) { float* q = logits_out + 5 * i; for (int o = 0; o < 5; o++) q[o] = m.outv[o * PE + e]; }
         if (actions) {
-            // Categorical(logits): normalised logits = logits - logsumexp, probs = softmax (torch.distributions)
-            const float mx = fmaxf(l0, l1), z = mx + logf(expf(l0 - mx) + expf(l1 - mx));
-            const float my = fmaxf(m0, fmaxf(m1, m2)), zy = my + logf(expf(m0 - my) + expf(m1 - my) + expf(m2 - my));
-            int a0, a1;
-            if (deterministic) {                                  // probs.argmax: the first maximum
-                a0 = l1 > l0 ? 1 : 0;
-                a1 = (m1 > m0 ? (m2 > m1 ? 2 : 1) : (m2 > m0 ? 2 : 0));
-            } else {
-                u32 blk[4];
-                const u64 st = step + (step_dev ? *step_dev : 0ull);
-                philox4x32_10((u32)(env_id0 + (u64)i), (u32)((env_id0 + (u64)i) >> 32), (u32)st, ((u32)(st >> 32) & 0x0FFFFFFFu) | ((u32)TAG_POLICY << 28),
-                              (u32)seed, (u32)(seed >> 32), blk);
-                const float r0 = (float)(blk[0] >> 8) * (1.0f / 16777216.0f), r1 = (float)(blk[1] >> 8) * (1.0f / 16777216.0f);   // [0, 1)
-                a0 = r0 < expf(l0 - z) ? 0 : 1;
-                const float q0 = expf(m0 - zy), q1 = expf(m1 - zy);
-                a1 = r1 < q0 ? 0 : (r1 < q0 + q1 ? 1 : 2);
-            }
+            int a0, a1; float lp;
+            pol_draw(m.outv, e, env_id0 + (u64)i, seed, step + (step_dev ? *step_dev : 0ull), deterministic, a0, a1, lp);
             actions[2 * i] = a0; actions[2 * i + 1] = a1;
-            if (logp) logp[i] = ((a0 ? l1 : l0) - z) + ((a1 == 0 ? m0 : a1 == 1 ? m1 : m2) - zy);
+            if (logp) logp[i] = lp;
         }
     }
+}
+
+// K5p: the whole rollout of a block's 32 envs in ONE launch.  The games of one block never need another block's data, so policy forward
+// and env step alternate on chip for all T steps: parameters staged once, no launch gaps (two dependent launches per step cost ~7 us of
+// gaps alone at this size), games / tolerance / previous score in the registers of warp 0 (lane = env) from the first step to the last.
+// Per step: warp 0 stages its 32 boards (the observation of step t) and writes them to the rollout buffer; all threads turn the tile
+// into features; layers + heads (pol_layers); warp 0 draws the actions, plays the env step (step_one_cfg: the same function, Philox
+// blocks and arithmetic as k_step) and writes actions / values / log-probs / rewards / dones of step t.  After the last step: the
+// observation and V of slot T, the games back to HBM, GAE over the block's own columns.  The buffers are bit-identical to the
+// two-launches-per-step collector's (tests/test_policy_kernel.py).
+struct RolloutArgs {
+    u64* state; int64_t n; int T;
+    int16_t* board; int64_t* dice;                   // [T + 1][n][N][N], [T + 1][n]
+    int64_t* actions; float* rewards; uint8_t* dones; float* values; float* logp;    // [T][n][2], [T][n] ...
+    float* last_values; float* adv; float* ret;      // [n], [T][n], [T][n]
+    int32_t* tolerance; double* prev_score; unsigned long long* stats;
+    const unsigned long long* step_dev;
+    u64 policy_seed; float gamma, gamma_lambda;
+};
+template <class C, int NT, bool SHAPED> __global__ void __launch_bounds__(PT)
+k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepParams sp, const __grid_constant__ PolicyNet net, const int D) {
+    extern __shared__ float4 pol_smem[];
+    Geo geo = sp.geo;
+    if (NT) { geo.N = NT; geo.corner = C::cell(NT - 1, NT - 1); }
+    const int NN = geo.N * geo.N, F = NN + D;
+    const PolSmem m = pol_carve(reinterpret_cast<float*>(pol_smem), F);
+    int16_t* const tile = reinterpret_cast<int16_t*>(m.small + POL_SMALL);            // [32][NN] int16 (16-byte aligned: every part before it is)
+    int* const s_dice = reinterpret_cast<int*>(reinterpret_cast<char*>(tile) + (((size_t)32 * NN * 2 + 15) & ~(size_t)15));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t n = ra.n, e0 = (int64_t)blockIdx.x * PE, i = e0 + lane;
+    const bool mine = warp == 0 && i < n;
+    const u64 step0 = sp.step + (ra.step_dev ? *ra.step_dev : 0ull);
+    pol_stage(m, net, F);
+    Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
+    int tol = 0; double prev = 0.0;
+    unsigned won = 0, lost = 0, fin_n = 0;
+    if (mine) {
+        unpack(g, ra.state, i, sp.geo);
+        if (SHAPED) { tol = ra.tolerance[i]; prev = ra.prev_score[i]; }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    for (int t = 0; t <= ra.T; t++) {
+        if (warp == 0) {                                          // observation of slot t: the block's 32 rows are contiguous in the buffer
+            stage_rows<C, NT>(g, mine, geo, tile, lane);
+            write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, e0, n, geo, tile, lane);
+            if (mine) ra.dice[(size_t)t * n + i] = g.dice;
+            s_dice[lane] = mine ? g.dice : 0;
+        }
+        __syncthreads();
+        for (int idx = tid; idx < PE * NN; idx += PT) {          // x[k][e] = board[e][k] (rows of envs beyond n are zero)
+            const int k = idx >> 5, e = idx & 31;
+            m.x[idx] = (float)tile[e * NN + k];
+        }
+        for (int idx = tid; idx < PE * D; idx += PT) {
+            const int d = idx >> 5, e = idx & 31;
+            int v = s_dice[e] - 1;
+            const bool live = v >= 0;
+            v = v < 0 ? 0 : (v > D - 1 ? D - 1 : v);
+            m.x[(NN + d) * PE + e] = (live && d == v) ? 1.f : 0.f;
+        }
+        __syncthreads();
+        pol_layers(m, F);
+        if (t == ra.T) {                                          // V of the observation after the last step
+            if (mine) ra.last_values[i] = m.outv[5 * PE + lane];
+            break;
+        }
+        if (mine) {
+            const size_t k = (size_t)t * n + i;
+            int a0, a1; float lp;
+            pol_draw(m.outv, lane, sp.env_id0 + (u64)i, ra.policy_seed, step0 + (u64)t, 0, a0, a1, lp);
+            ra.actions[2 * k] = a0; ra.actions[2 * k + 1] = a1;
+            ra.values[k] = m.outv[5 * PE + lane]; ra.logp[k] = lp;
+            Game<C> term = g;
+            StepOut out; out.term = 0; out.code = CODE_ONGOING;
+            StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
+            step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, 0, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
+            ra.rewards[k] = (float)out.reward;
+            ra.dones[k] = (uint8_t)out.term;
+            if (out.term) { fin_n++; won += out.code == CODE_AGENT_WON; lost += out.code == CODE_AGENT_LOST; }
+        }
+        // (the next iteration's first barrier orders this step's reads of m.outv before the next pol_layers writes it)
+    }
+    if (warp != 0) return;
+    if (mine) {
+        pack(g, ra.state, i, sp.geo);
+        if (SHAPED) { ra.tolerance[i] = tol; ra.prev_score[i] = prev; }
+        // RolloutBuffer.compute_returns_and_advantage over this env's column (k_gae's arithmetic; the thread reads its own stores)
+        float gae = 0.f, next_v = m.outv[5 * PE + lane];
+        for (int t = ra.T - 1; t >= 0; t--) {
+            const size_t k = (size_t)t * n + i;
+            const float nt = __fsub_rn(1.0f, ra.dones[k] ? 1.0f : 0.0f), v = ra.values[k];
+            const float delta = __fsub_rn(__fadd_rn(ra.rewards[k], __fmul_rn(__fmul_rn(ra.gamma, next_v), nt)), v);
+            gae = __fadd_rn(delta, __fmul_rn(__fmul_rn(ra.gamma_lambda, nt), gae));
+            ra.adv[k] = gae;
+            ra.ret[k] = __fadd_rn(gae, v);
+            next_v = v;
+        }
+    }
+    if (ra.stats) {
+        const unsigned f = __reduce_add_sync(0xffffffffu, fin_n), w = __reduce_add_sync(0xffffffffu, won), l = __reduce_add_sync(0xffffffffu, lost);
+        if (lane < 4 && f) {
+            const unsigned v = lane == 0 ? w : lane == 1 ? l : lane == 2 ? f - w - l : f;
+            if (v) atomicAdd(ra.stats + lane, (unsigned long long)v);
+        }
+    }
+}
+inline size_t rollout_smem(int NN, int D) { return policy_smem(NN + D) + (((size_t)32 * NN * 2 + 15) & ~(size_t)15) + 32 * sizeof(int); }
+template <class C, int NT, bool SHAPED> int launch_rollout(const RolloutArgs& ra, const StepParams& sp, const PolicyNet& pn, int D, cudaStream_t st) {
+    const int NN = sp.geo.N * sp.geo.N;
+    const size_t sm = rollout_smem(NN, D);
+    {   // more than the 48 KB default: opt in once per device and instantiation
+        static std::mutex mu;
+        static bool done[64] = {false};
+        int dev = 0;
+        CU(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lock(mu);
+        if (dev >= 0 && dev < 64 && !done[dev]) {
+            CU(cudaFuncSetAttribute(k_rollout<C, NT, SHAPED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rollout_smem(EWN_MAX_BOARD * EWN_MAX_BOARD, 7)));
+            done[dev] = true;
+        }
+    }
+    k_rollout<C, NT, SHAPED><<<(unsigned)((ra.n + PE - 1) / PE), PT, sm, st>>>(ra, sp, pn, D);
+    LAUNCHED("k_rollout");
+    return EWN_OK;
 }
 
 // RolloutBuffer.compute_returns_and_advantage (GAE; A2C: lambda = 1) for rewards / values / dones laid out [T][n]; dones[t] = the
@@ -2151,6 +2299,43 @@ int ewn_policy_forward(const ewn_policy_net* net, const int16_t* board, const in
                                                                  env_id0, deterministic, actions, values, logp, logits);
     LAUNCHED("k_policy_forward");
     return EWN_OK;
+}
+
+int ewn_rollout(const ewn_rollout_args* a, void* stream) {
+    if (!a || !a->state || !a->net || a->n < 0 || a->T < 1 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
+    if (!a->board || !a->dice || !a->actions || !a->rewards || !a->dones || !a->values || !a->logp || !a->last_values || !a->advantages || !a->returns)
+        return EWN_EARG;
+    if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
+    const ewn_policy_net* net = a->net;
+    if (net->hidden != PH || codec_of(a->board_size, a->cube_layer) == 2) return EWN_ENOSUP;
+    if (!net->pi_w1 || !net->pi_b1 || !net->pi_w2 || !net->pi_b2 || !net->vf_w1 || !net->vf_b1 || !net->vf_w2 || !net->vf_b2 || !net->action_w ||
+        !net->action_b || !net->value_w || !net->value_b) return EWN_EARG;
+    if (a->n == 0) return EWN_OK;
+    PolicyNet pn;
+    pn.w1[0] = net->pi_w1; pn.b1[0] = net->pi_b1; pn.w2[0] = net->pi_w2; pn.b2[0] = net->pi_b2;
+    pn.w1[1] = net->vf_w1; pn.b1[1] = net->vf_b1; pn.w2[1] = net->vf_w2; pn.b2[1] = net->vf_b2;
+    pn.wa = net->action_w; pn.ba = net->action_b; pn.wv = net->value_w; pn.bv = net->value_b;
+    StepParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.geo = make_geo(a->board_size, a->cube_layer);
+    sp.reward = a->reward; sp.illegal_move_reward = a->illegal_move_reward;
+    sp.seed = a->seed; sp.step = a->step; sp.env_id0 = a->env_id0; sp.rk = make_round_keys(a->seed);
+    sp.agent_random = 0; sp.autoreset = 1; sp.shaped = a->shaped != 0; sp.replay = 0;
+    RolloutArgs ra;
+    ra.state = a->state; ra.n = a->n; ra.T = a->T;
+    ra.board = a->board; ra.dice = a->dice; ra.actions = a->actions; ra.rewards = a->rewards; ra.dones = a->dones; ra.values = a->values;
+    ra.logp = a->logp; ra.last_values = a->last_values; ra.adv = a->advantages; ra.ret = a->returns;
+    ra.tolerance = a->tolerance; ra.prev_score = a->prev_score; ra.stats = reinterpret_cast<unsigned long long*>(a->stats);
+    ra.step_dev = reinterpret_cast<const unsigned long long*>(a->step_dev);
+    ra.policy_seed = a->policy_seed; ra.gamma = (float)a->gamma; ra.gamma_lambda = (float)(a->gamma * a->gae_lambda);
+    const int N = a->board_size, D = a->cube_layer * (a->cube_layer + 1) / 2 + 1;
+    cudaStream_t st = (cudaStream_t)stream;
+#define ROLL(C, NT) (a->shaped ? launch_rollout<C, NT, true>(ra, sp, pn, D, st) : launch_rollout<C, NT, false>(ra, sp, pn, D, st))
+    if (N == 5) return ROLL(P5, 5);
+    if (use_p5(N)) return ROLL(P5, 0);
+    if (N == 7) return ROLL(P8, 7);
+    return ROLL(P8, 0);
+#undef ROLL
 }
 
 int ewn_gae(const float* rewards, const float* values, const uint8_t* dones, const float* last_values, int T, int64_t n, double gamma,

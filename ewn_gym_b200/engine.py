@@ -311,6 +311,31 @@ class Engine:
                                               xp.ptr(out["logits"]), xp.stream()), "ewn_policy_forward")
         return {k: v for k, v in out.items() if v is not None}
 
+    def rollout_plan(self, net, state, T, bufs, *, seed, env_id0=0, step_dev=None, policy_seed=0, reward=1.0, shaped=False,
+                     illegal_move_reward=-1.0, tolerance=None, prev_score=None, stats=None, gamma=0.99, gae_lambda=1.0):
+        """A bound ewn_rollout call (the whole T-step collection in one launch) -> callable(step) that enqueues it.  `bufs`: dict with
+        board [T+1,n,N,N] i16, dice [T+1,n] i64, actions [T,n,2] i64, rewards / values / log_probs / adv / ret [T,n] f32, dones [T,n] u8,
+        last_values [n] f32."""
+        from ._lib import RolloutArgs
+        xp = self.xp
+        a = RolloutArgs()
+        a.state, a.n, a.board_size, a.cube_layer, a.T, a.shaped = xp.ptr(state), self._n(state), self.N, self.L, int(T), int(bool(shaped))
+        a.net = C.pointer(net)
+        for field, key in (("board", "board"), ("dice", "dice"), ("actions", "actions"), ("rewards", "rewards"), ("dones", "dones"),
+                           ("values", "values"), ("logp", "log_probs"), ("last_values", "last_values"), ("advantages", "adv"), ("returns", "ret")):
+            setattr(a, field, xp.ptr(bufs[key]))
+        a.tolerance, a.prev_score, a.stats = xp.ptr(tolerance), xp.ptr(prev_score), xp.ptr(stats)
+        a.reward, a.illegal_move_reward = float(reward), float(illegal_move_reward)
+        a.seed, a.step, a.env_id0, a.step_dev, a.policy_seed = int(seed), 0, int(env_id0), xp.ptr(step_dev), int(policy_seed)
+        a.gamma, a.gae_lambda = float(gamma), float(gae_lambda)
+        keep = (net, state, bufs, tolerance, prev_score, stats, step_dev)
+        fn, ref = self.lib.ewn_rollout, C.byref(a)
+
+        def launch(step=0, _keep=keep, _a=a):
+            _a.step = int(step)
+            self._chk(fn(ref, xp.stream()), "ewn_rollout")
+        return launch
+
     def gae(self, rewards, values, dones, last_values, gamma=0.99, gae_lambda=1.0, advantages=None, returns=None):
         """RolloutBuffer.compute_returns_and_advantage over [T][n] tensors (ewn_gae) -> (advantages, returns)"""
         xp = self.xp

@@ -118,7 +118,7 @@ class A2C:
 
     def __init__(self, policy: str, env, n_steps: int = 5, learning_rate: float = 7e-4, gamma: float = 0.99, gae_lambda: float = 1.0,
                  ent_coef: float = 0.0, vf_coef: float = 0.5, max_grad_norm: float = 0.5, policy_kwargs: Dict[str, Any] | None = None,
-                 seed: int | None = None, device=None, fused: bool | None = None, **_ignored):
+                 seed: int | None = None, device=None, fused: bool | None = None, persistent: bool | None = None, **_ignored):
         assert policy == "MultiInputPolicy", "the reference trains MultiInputPolicy only (train.py:41,53)"
         self.env, self.n_steps, self.gamma, self.gae_lambda = env, int(n_steps), float(gamma), float(gae_lambda)
         self.ent_coef, self.vf_coef, self.max_grad_norm = float(ent_coef), float(vf_coef), float(max_grad_norm)
@@ -144,6 +144,9 @@ class A2C:
         # fused collection (policy forward and env step as two launches per step, the whole rollout one CUDA graph) when the env is the
         # device-resident one with its in-kernel opponent and the policy has the default 64-wide towers; the generic loop otherwise
         self.fused = fused if fused is not None else self._can_fuse()
+        # ... and, for the six-cube layouts, the whole rollout as ONE launch (ewn_rollout: policy forward and env step alternate on chip;
+        # bit-identical buffers); persistent=False keeps the two-launches-per-step graph
+        self.persistent = self.fused and (persistent if persistent is not None else env.cube_layer <= 3)
         self._graph = None
 
     # ------------------------------------------------------------------ fused collection (K5: ewn_policy_forward + ewn_step + ewn_gae)
@@ -175,6 +178,13 @@ class A2C:
         self._ctr = th.zeros(1, dtype=th.int64, device=dev)
         self._ctr_host = None
         self._net = e.policy_net(self.policy)
+        if self.persistent:
+            self._roll = e.rollout_plan(self._net, env.state, T, f, seed=env.seed_value, env_id0=env.env_id0, step_dev=self._ctr,
+                                        policy_seed=self.policy_seed, reward=env.reward, shaped=env.shaped,
+                                        illegal_move_reward=env.illegal_move_reward, tolerance=getattr(env, "_tol", None),
+                                        prev_score=getattr(env, "_prev", None), stats=env.stats, gamma=self.gamma, gae_lambda=self.gae_lambda)
+            self._graph = "persistent"
+            return
         # first launches load the kernels: not inside a capture
         e.policy_forward(self._net, f["board"][0], f["dice"][0], actions=f["actions"][0], values=f["values"][0], logp=f["log_probs"][0])
         e.gae(f["rewards"], f["values"], f["dones"], f["last_values"], self.gamma, self.gae_lambda, f["adv"], f["ret"])
@@ -212,15 +222,24 @@ class A2C:
 
     @th.no_grad()
     def _collect_fused(self):
+        if self._graph is not None and self._bound_seed != self.env.seed_value:
+            self._graph = None                          # env.seed(s) + reset(): the bound launches carry the old Philox key
         if self._graph is None:
             self._build_fused()
+            self._bound_seed = self.env.seed_value
         env, f, T = self.env, self.fb, self.n_steps
         if self._ctr_host != env.step_index:            # the env was stepped or reset behind the graph's back: re-seat the counter and
             self._ctr.fill_(env.step_index)             # take the env's latest observation as the rollout's first
             if self._ctr_host is not None:
                 last = env._obs(env._last)
                 f["board"][T].copy_(last["board"]); f["dice"][T].copy_(last["dice_roll"])
-        self._graph.replay()
+        if self.persistent:
+            self._roll(0)                               # one launch: all T steps of every env, V(last), GAE
+            f["sums"][0] = f["dones"].sum(); f["sums"][1] = f["rewards"].mean()
+            e_ = env.e
+            e_.counter_add(self._ctr, T)
+        else:
+            self._graph.replay()
         env.advance(T, obs=(f["board"][T], f["dice"][T]))
         self._ctr_host = env.step_index
         self._last_obs = {"board": f["board"][T], "dice_roll": f["dice"][T]}

@@ -218,6 +218,29 @@ typedef struct ewn_policy_net {
 EWN_API int ewn_policy_forward(const ewn_policy_net *net, const int16_t *board, const int64_t *dice, int64_t n, int board_size, int cube_layer,
                        uint64_t seed, uint64_t step, const uint64_t *step_dev, uint64_t env_id0, int deterministic, int64_t *actions,
                        float *values, float *logp, float *logits, void *stream);
+/* The WHOLE rollout of train.py:144-155 (collect_rollouts: T x (policy forward, draw, env.step, buffer add), V of the last
+ * observation, returns and advantages) in ONE launch: the games of a block of 32 envs never need another block's data, so policy
+ * forward and env step alternate on chip with the parameters staged once.  Same Philox schedule as T calls of ewn_policy_forward
+ * (policy_seed; env, step + t) and ewn_step (seed; env, step + t): the buffers are bit-identical to that sequence.  In-kernel random
+ * opponent, auto-reset, MultiDiscrete actions from the policy; six-cube layouts and 64-wide towers (EWN_ENOSUP otherwise).
+ * board int16 [T + 1][n][N][N] and dice int64 [T + 1][n]: slot t = the observation step t's action was computed from, slot T = the one
+ * after the last step; actions int64 [T][n][2]; rewards / values / logp / advantages / returns f32 [T][n]; dones u8 [T][n]; last_values
+ * f32 [n]; tolerance / prev_score as in ewn_step_args (required when shaped); stats as there (or NULL). */
+typedef struct ewn_rollout_args {
+    uint64_t *state;              /* in/out, n games, agent to move */
+    int64_t n;
+    int32_t board_size, cube_layer, T, shaped;
+    const ewn_policy_net *net;
+    int16_t *board; int64_t *dice; int64_t *actions;
+    float *rewards; uint8_t *dones; float *values, *logp, *last_values, *advantages, *returns;
+    int32_t *tolerance; double *prev_score; unsigned long long *stats;
+    double reward, illegal_move_reward;
+    uint64_t seed, step, env_id0; /* env Philox key / first step index / first env id */
+    const uint64_t *step_dev;     /* optional device counter added to `step` (CUDA-graph replays) */
+    uint64_t policy_seed;
+    double gamma, gae_lambda;
+} ewn_rollout_args;
+EWN_API int ewn_rollout(const ewn_rollout_args *args, void *stream);
 /* RolloutBuffer.compute_returns_and_advantage of the same loop (GAE(gamma, lambda); A2C's default lambda = 1 gives the n-step return):
  * rewards / values f32[T][n], dones u8[T][n] (the episode ended AT step t), last_values f32[n] = V of the observation after the last
  * step -> advantages f32[T][n], returns f32[T][n] (or NULL).  fp32, in the operation order of the reference's tensor loop. */

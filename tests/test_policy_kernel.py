@@ -122,8 +122,9 @@ def test_gae_equals_the_tensor_loop(T, n, lam):
     assert th.equal(adv, ref) and th.equal(ret, ref + values)
 
 
+@pytest.mark.parametrize("persistent", [False, True])
 @pytest.mark.parametrize("N,L,shaped", [(7, 3, True), (5, 3, False)])
-def test_fused_rollouts_are_consistent_and_continue_across_replays(N, L, shaped):
+def test_fused_rollouts_are_consistent_and_continue_across_replays(N, L, shaped, persistent):
     """the graph-replayed collector: observations / rewards / dones of the buffer are what the env produces for the stored actions
     (replayed through a second env from the same seed), values and log-probs are the torch module's, the rollouts join up, stepping
     the env by hand in between is picked up, and a training step changes what the next replay computes (parameters read in place)"""
@@ -133,8 +134,8 @@ def test_fused_rollouts_are_consistent_and_continue_across_replays(N, L, shaped)
     n, T, seed = 1000, 16, 21
     env = EWNDeviceVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_tolerance=3)
     twin = EWNDeviceVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_tolerance=3)
-    model = A2C("MultiInputPolicy", env, n_steps=T, seed=2)
-    assert model.fused
+    model = A2C("MultiInputPolicy", env, n_steps=T, seed=2, persistent=persistent)
+    assert model.fused and model.persistent == persistent
     obs = twin.reset()
     tb, td = obs["board"].clone(), obs["dice_roll"].clone()
     for rollout in range(4):
@@ -162,6 +163,33 @@ def test_fused_rollouts_are_consistent_and_continue_across_replays(N, L, shaped)
         assert model.logger["rollout/episodes"] == float(b["dones"].sum())
         model.train()                                             # RMSprop updates the parameters in place: the graph reads the new ones
     assert env.step_index == twin.step_index and model.num_timesteps == 4 * T * n
+
+
+@pytest.mark.parametrize("N,L,shaped,n", [(7, 3, True, 4096), (5, 3, False, 1000 + 13), (6, 3, True, 77), (9, 3, False, 300)])
+def test_one_launch_rollout_equals_two_launches_per_step(N, L, shaped, n):
+    """ewn_rollout (the whole rollout in one launch, games in registers) against the graph of ewn_policy_forward + ewn_step launches:
+    every buffer bit for bit (observations, actions, values, log-probs, rewards, dones, V(last), advantages, returns), the games and the
+    env statistics afterwards, over several rollouts with training steps in between"""
+    import torch as th
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.train import A2C
+    T, seed = 12, 8
+    envs = [EWNDeviceVecEnv(n, N, L, seed=seed, shaped=shaped, illegal_move_tolerance=2, env_id0=5000) for _ in (0, 1)]
+    a = A2C("MultiInputPolicy", envs[0], n_steps=T, seed=4, persistent=False)
+    b = A2C("MultiInputPolicy", envs[1], n_steps=T, seed=4, persistent=True)
+    assert a.fused and b.fused and b.persistent and not a.persistent
+    b.policy.load_state_dict(a.policy.state_dict())
+    for rollout in range(4):
+        a.collect_rollouts(); b.collect_rollouts()
+        for k in ("board", "dice", "actions", "values", "log_probs", "rewards", "dones", "last_values", "adv", "ret"):
+            assert th.equal(a.fb[k], b.fb[k]), (rollout, k)
+        assert th.equal(envs[0].state, envs[1].state) and th.equal(envs[0].stats, envs[1].stats)
+        assert a.logger["rollout/episodes"] == b.logger["rollout/episodes"]
+        if shaped:
+            assert th.equal(envs[0]._tol, envs[1]._tol) and th.equal(envs[0]._prev, envs[1]._prev)
+        a.train()
+        b.policy.load_state_dict(a.policy.state_dict())           # (autograd's reductions need not be bitwise repeatable: keep the twins in step)
+    assert int(envs[0].stats[3]) > 0
 
 
 def test_generic_collector_still_runs_on_cuda():
