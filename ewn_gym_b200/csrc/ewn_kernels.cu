@@ -1512,6 +1512,13 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 #endif
 constexpr int PE = 32, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PWS: row stride of a transposed weight
                                                                    // tile (16-byte aligned rows); PEV = 4 (2) envs per thread at 256 (512) threads
+constexpr int PHS = PE + 4;                                        // row stride of the activation tiles h1 / h2 (see pol_row)
+// Output row (tower * 64 + unit) number j of lane l: the four rows of a thread are 16 apart inside ONE tower and adjacent lanes own
+// adjacent rows, so that the 16-byte activation stores of a quarter-warp fall 36 words apart -- eight different bank groups -- instead of
+// 128 words apart (rows 4 l + j: a 32-way conflict on every store, 1 us of the 8.9 us step of k_rollout).  The weight tiles hold the
+// column of row pol_row(l, j) at position 4 l + j, so a thread's four weights of a k step are still one 16-byte load.
+__host__ __device__ __forceinline__ constexpr int pol_row(int l, int j) { return (l >> 4) * PH + (l & 15) + 16 * j; }
+__host__ __device__ __forceinline__ constexpr int pol_col(int r) { return 4 * ((r / PH) * 16 + (r % PH) % 16) + (r % PH) / 16; }
 struct PolicyNet {
     const float *w1[2], *b1[2], *w2[2], *b2[2];      // [0] = pi tower, [1] = vf tower: Linear(F, 64), Linear(64, 64)
     const float *wa, *ba, *wv, *bv;                  // action_net Linear(64, 5), value_net Linear(64, 1)
@@ -1520,15 +1527,15 @@ enum { TAG_POLICY = 3 };
 // shared memory of one block: the two layers' weights of both towers (transposed), features, activations, head outputs, small parameters
 struct PolSmem { float *wt1, *wt2, *x, *h1, *h2, *outv, *small; };
 constexpr int POL_SMALL = 10 * PH + 8;               // b1[2][64], b2[2][64], action_net w[5][64], value_net w[64], their six biases
-inline size_t policy_smem(int F) { return ((size_t)F * PE + 2 * (size_t)PO * PE + 6 * PE + POL_SMALL + (size_t)(F + PH) * PWS) * sizeof(float); }
+inline size_t policy_smem(int F) { return ((size_t)F * PE + 2 * (size_t)PO * PHS + 6 * PE + POL_SMALL + (size_t)(F + PH) * PWS) * sizeof(float); }
 __device__ __forceinline__ PolSmem pol_carve(float* base, int F) {
     PolSmem m;
     m.wt1 = base;                                    // [F][PWS]   layer 1, both towers, transposed
     m.wt2 = m.wt1 + (size_t)F * PWS;                 // [PH][PWS]  layer 2
     m.x = m.wt2 + (size_t)PH * PWS;                  // [F][PE]    features, feature-major
-    m.h1 = m.x + (size_t)F * PE;                     // [PO][PE]   row = tower * 64 + unit
-    m.h2 = m.h1 + (size_t)PO * PE;                   // [PO][PE]
-    m.outv = m.h2 + (size_t)PO * PE;                 // [6][PE]: five logits and the value
+    m.h1 = m.x + (size_t)F * PE;                     // [PO][PHS]  row = tower * 64 + unit
+    m.h2 = m.h1 + (size_t)PO * PHS;                  // [PO][PHS]
+    m.outv = m.h2 + (size_t)PO * PHS;                // [6][PE]: five logits and the value
     m.small = m.outv + 6 * PE;
     return m;
 }
@@ -1549,12 +1556,12 @@ __device__ __forceinline__ void pol_stage(const PolSmem& m, const PolicyNet& net
 #pragma unroll
             for (int q = 0; q < NQ; q++) {
                 const int c = c0 + TPR * q;
-                if (c < nc) { float* d = dst + (size_t)(4 * c) * PWS + r; d[0] = v[q].x; d[PWS] = v[q].y; d[2 * PWS] = v[q].z; d[3 * PWS] = v[q].w; }
+                if (c < nc) { float* d = dst + (size_t)(4 * c) * PWS + pol_col(r); d[0] = v[q].x; d[PWS] = v[q].y; d[2 * PWS] = v[q].z; d[3 * PWS] = v[q].w; }
             }
         } else {
             for (int r = warp; r < PO; r += PT / 32) {
                 const float* src = (r < PH ? wa_ + (size_t)r * K : wb_ + (size_t)(r - PH) * K);
-                const unsigned d = (unsigned)__cvta_generic_to_shared(dst + r);
+                const unsigned d = (unsigned)__cvta_generic_to_shared(dst + pol_col(r));
                 for (int k = lane; k < K; k += 32) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + (unsigned)(k * PWS * 4)), "l"(src + k) : "memory");
             }
         }
@@ -1576,13 +1583,13 @@ __device__ __forceinline__ void pol_stage(const PolSmem& m, const PolicyNet& net
 // heads -> m.outv[6][PE].  Ends with a block barrier.
 __device__ __forceinline__ void pol_layers(const PolSmem& m, int F) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tower = lane >> 4;                                   // this thread's four units: rows 4 * lane .. 4 * lane + 3 of the output
+    const int tower = lane >> 4;                                   // this thread's four units: rows pol_row(lane, 0..3), all in this tower
     static_assert(PEV == 2 || PEV == 4, "one float2 / float4 of activations per k step");
     float acc[4][PEV];
-    auto layer = [&](const float* wl, const float* bias, const float* in, int K) {
+    auto layer = [&](const float* wl, const float* bias, const float* in, int K, int stride) {
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float b = bias[4 * lane + j];
+            const float b = bias[pol_row(lane, j)];
 #pragma unroll
             for (int e = 0; e < PEV; e++) acc[j][e] = b;
         }
@@ -1595,8 +1602,8 @@ __device__ __forceinline__ void pol_layers(const PolSmem& m, int F) {
         for (int k = 0; k < K; k++) {
             const float4 w4 = *reinterpret_cast<const float4*>(w + (size_t)k * PWS);
             float av[PEV];
-            if (PEV == 4) { const float4 a0 = *reinterpret_cast<const float4*>(in + (size_t)k * PE); av[0] = a0.x; av[1] = a0.y; av[PEV - 2] = a0.z; av[PEV - 1] = a0.w; }
-            else { const float2 a0 = *reinterpret_cast<const float2*>(in + (size_t)k * PE); av[0] = a0.x; av[1] = a0.y; }
+            if (PEV == 4) { const float4 a0 = *reinterpret_cast<const float4*>(in + (size_t)k * stride); av[0] = a0.x; av[1] = a0.y; av[PEV - 2] = a0.z; av[PEV - 1] = a0.w; }
+            else { const float2 a0 = *reinterpret_cast<const float2*>(in + (size_t)k * stride); av[0] = a0.x; av[1] = a0.y; }
             const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
             for (int j = 0; j < 4; j++)
@@ -1610,22 +1617,22 @@ __device__ __forceinline__ void pol_layers(const PolSmem& m, int F) {
     auto squash = [&](float* h) {                                  // tanh of the sums -> h[tower * 64 + unit][env]
 #pragma unroll
         for (int j = 0; j < 4; j++)
-            if (PEV == 4) *reinterpret_cast<float4*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float4(th(acc[j][0]), th(acc[j][1]), th(acc[j][PEV - 2]), th(acc[j][PEV - 1]));
-            else *reinterpret_cast<float2*>(h + (size_t)(4 * lane + j) * PE + PEV * warp) = make_float2(th(acc[j][0]), th(acc[j][1]));
+            if (PEV == 4) *reinterpret_cast<float4*>(h + (size_t)pol_row(lane, j) * PHS + PEV * warp) = make_float4(th(acc[j][0]), th(acc[j][1]), th(acc[j][PEV - 2]), th(acc[j][PEV - 1]));
+            else *reinterpret_cast<float2*>(h + (size_t)pol_row(lane, j) * PHS + PEV * warp) = make_float2(th(acc[j][0]), th(acc[j][1]));
     };
-    layer(m.wt1, m.small, m.x, F);
+    layer(m.wt1, m.small, m.x, F, PE);
     squash(m.h1);
     __syncthreads();
-    layer(m.wt2, m.small + 2 * PH, m.h1 + (size_t)tower * PH * PE, PH);
+    layer(m.wt2, m.small + 2 * PH, m.h1 + (size_t)tower * PH * PHS, PH, PHS);
     squash(m.h2);
     __syncthreads();
     for (int idx = tid; idx < 6 * PE; idx += PT) {               // heads: (output o, env e)
         const int o = idx / PE, e = idx - o * PE;
         const float* w = m.small + 4 * PH + o * PH;               // action_net rows 0..4, then value_net
-        const float* in = m.h2 + (size_t)(o < 5 ? 0 : PH) * PE + e;
+        const float* in = m.h2 + (size_t)(o < 5 ? 0 : PH) * PHS + e;
         float a = m.small[10 * PH + o];
 #pragma unroll 8
-        for (int k = 0; k < PH; k++) a = fmaf(w[k], in[(size_t)k * PE], a);
+        for (int k = 0; k < PH; k++) a = fmaf(w[k], in[(size_t)k * PHS], a);
         m.outv[o * PE + e] = a;
     }
     __syncthreads();
