@@ -1510,7 +1510,10 @@ template <class C> __global__ void __launch_bounds__(TPB) k_mc_best_peers(const 
 #ifndef EWN_PT
 #define EWN_PT 256
 #endif
-constexpr int PE = 32, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PWS: row stride of a transposed weight
+#ifndef EWN_PE
+#define EWN_PE 32
+#endif
+constexpr int PE = EWN_PE, PH = 64, PO = 2 * PH, PWS = PO + 4, PT = EWN_PT, PEV = PE / (PT / 32);   // PWS: row stride of a transposed weight
                                                                    // tile (16-byte aligned rows); PEV = 4 (2) envs per thread at 256 (512) threads
 constexpr int PHS = PE + 4;                                        // row stride of the activation tiles h1 / h2 (see pol_row)
 // Output row (tower * 64 + unit) number j of lane l: the four rows of a thread are 16 apart inside ONE tower and adjacent lanes own
@@ -1598,7 +1601,11 @@ __device__ __forceinline__ void pol_layers(const PolSmem& m, int F) {
 #if defined(EWN_EXP_POL_NOLAYER)
         K = 0;
 #endif
-#pragma unroll 4
+#ifndef EWN_POL_UNROLL
+#define EWN_POL_UNROLL 8
+#endif
+        constexpr int PUN = EWN_POL_UNROLL;
+#pragma unroll PUN
         for (int k = 0; k < K; k++) {
             const float4 w4 = *reinterpret_cast<const float4*>(w + (size_t)k * PWS);
             float av[PEV];
@@ -1722,7 +1729,7 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
     int* const s_dice = reinterpret_cast<int*>(reinterpret_cast<char*>(tile) + (((size_t)32 * NN * 2 + 15) & ~(size_t)15));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t n = ra.n, e0 = (int64_t)blockIdx.x * PE, i = e0 + lane;
-    const bool mine = warp == 0 && i < n;
+    const bool mine = warp == 0 && lane < PE && i < n;
     const u64 step0 = sp.step + (ra.step_dev ? *ra.step_dev : 0ull);
     pol_stage(m, net, F);
     Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
@@ -1736,17 +1743,17 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
     for (int t = 0; t <= ra.T; t++) {
         if (warp == 0) {                                          // observation of slot t: the block's 32 rows are contiguous in the buffer
             stage_rows<C, NT>(g, mine, geo, tile, lane);
-            write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, e0, n, geo, tile, lane);
+            write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, e0, min(n, e0 + PE), geo, tile, lane);
             if (mine) ra.dice[(size_t)t * n + i] = g.dice;
             s_dice[lane] = mine ? g.dice : 0;
         }
         __syncthreads();
         for (int idx = tid; idx < PE * NN; idx += PT) {          // x[k][e] = board[e][k] (rows of envs beyond n are zero)
-            const int k = idx >> 5, e = idx & 31;
+            const int k = idx / PE, e = idx % PE;
             m.x[idx] = (float)tile[e * NN + k];
         }
         for (int idx = tid; idx < PE * D; idx += PT) {
-            const int d = idx >> 5, e = idx & 31;
+            const int d = idx / PE, e = idx % PE;
             int v = s_dice[e] - 1;
             const bool live = v >= 0;
             v = v < 0 ? 0 : (v > D - 1 ? D - 1 : v);
