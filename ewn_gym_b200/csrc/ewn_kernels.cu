@@ -1259,10 +1259,23 @@ inline Div31 make_div31(u32 d) {
 // of round-robin -- a warp that draws short games takes more chunks, so all warps finish within about one game of each other; the next
 // chunk's number is fetched one chunk ahead (the atomic's result is first read when the current chunk runs out).  Which warp plays a
 // game does not matter: results depend only on (root id, child, playout index).
+#ifndef EWN_MC_TAIL
+#define EWN_MC_TAIL 1
+#endif
+#ifndef EWN_MC_TAIL_R
+#define EWN_MC_TAIL_R 2
+#endif
+constexpr int MC_TAIL_R = EWN_MC_TAIL_R;
+struct TailRec { u64 tl, br; u32 rid, sc, pidx, j; };           // a live game on its way to another lane
 template <class C, bool DIRECT, bool DYN> __global__ void __launch_bounds__(TPB) k_playouts(const void* pairs, const u32* root_ids, const int* n_pairs_dev,
                                                                                   u32 n_pairs_host, u32 first, u32 count, Div31 dv, u32* wins,
                                                                                   unsigned long long* plies, Geo geo, const RoundKeys rk, int* reset_hdr) {
     __shared__ __align__(16) unsigned char s_dirs[3 * C::LUT];
+#if EWN_MC_TAIL
+    __shared__ unsigned s_tailw, s_cnt[2][TPB / 32];
+    __shared__ TailRec s_rec[TPB];
+    if (threadIdx.x == 0) s_tailw = 0;
+#endif
     asm volatile("griddepcontrol.launch_dependents;");
     const GeoLut geol = make_geo_lut<C, TPB>(geo, s_dirs);       // legal directions of a cube: one LDS (two cubes per ply)
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -1288,18 +1301,36 @@ template <class C, bool DIRECT, bool DYN> __global__ void __launch_bounds__(TPB)
     const u32 my_chunks = n_chunks > warp_id ? (n_chunks - warp_id + n_warps - 1) / n_warps : 0;
     u32 tnext = 0;                                             // warp-uniform cursor over the warp's local game indices
     const u32 tend = my_chunks * CH;
+#if !EWN_MC_TAIL
     if (tend == 0) { finish(); return; }
+#endif
     constexpr u32 NONE = 0xFFFFFFFFu;
     u32 base0 = warp_id * CH, used = 0, pending = 0;           // DYN: current chunk (first: chunk warp_id), games dealt from it, next chunk's ticket
     auto fetch = [&]() { if (lane == 0) pending = atomicAdd(reinterpret_cast<unsigned*>(reset_hdr) + 2, 1u); };
-    if (DYN) fetch();
+    if (DYN && tend != 0) fetch();
 
     Game<C> g; g.tl = C::ALL; g.br = C::ALL; g.dice = 1; g.player = SIDE_BR;
     bool busy = false;
     u32 rid = 0, child = 0, slot = 0, pidx = 0, j = 0;
     unsigned long long my_plies = 0;
     const unsigned lt = (1u << lane) - 1u;
-    for (;;) {
+    auto play = [&]() {                                            // one iteration (two plies) of this lane's game
+        u32 blk[4];
+        playout_block_rk(rk, rid, child, pidx, j++, blk);
+        g.dice = 1 + (int)bounded(blk[0], 6u);
+        bool over = random_ply<C, SIDE_BR>(g, geol, blk[1], nullptr, nullptr);
+        my_plies++;
+        if (!over) {
+            g.dice = 1 + (int)bounded(blk[2], 6u);
+            over = random_ply<C, SIDE_TL>(g, geol, blk[3], nullptr, nullptr);
+            my_plies++;
+        }
+        if (over) {
+            if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
+            busy = false;
+        }
+    };
+    for (; tend != 0;) {
         const unsigned need = __ballot_sync(0xffffffffu, !busy);
         if (need) {
             u32 gi = NONE;                                         // global game index this lane picks up
@@ -1340,25 +1371,58 @@ template <class C, bool DIRECT, bool DYN> __global__ void __launch_bounds__(TPB)
                 }
             }
             tnext += (u32)__popc(need);
+#if EWN_MC_TAIL
+            if (DYN ? base0 == NONE : tnext >= tend) break;        // no fresh games left for this warp: its live games go on in the tail
+#else
             if (!__ballot_sync(0xffffffffu, busy) && (DYN ? base0 == NONE : tnext >= tend)) break;
+#endif
         }
-        if (busy) {
-            u32 blk[4];
-            playout_block_rk(rk, rid, child, pidx, j++, blk);
-            g.dice = 1 + (int)bounded(blk[0], 6u);
-            bool over = random_ply<C, SIDE_BR>(g, geol, blk[1], nullptr, nullptr);
-            my_plies++;
-            if (!over) {
-                g.dice = 1 + (int)bounded(blk[2], 6u);
-                over = random_ply<C, SIDE_TL>(g, geol, blk[3], nullptr, nullptr);
-                my_plies++;
+        if (busy) play();
+    }
+#if EWN_MC_TAIL
+    // Tail.  Once every warp of the block has run out of fresh games, the block's live games are packed into as few warps as hold them
+    // every MC_TAIL_R iterations (through shared memory: a game is its two side words, its Philox coordinates and its slot), and the
+    // warps left without a game retire: at the 8-GPU share of a decision (eight games per lane) a third of the kernel used to be warps
+    // iterating for one or two long games.  Which lane plays a game changes nothing: counters are atomics, streams are keyed by game.
+    {
+        constexpr int NW = TPB / 32;
+        if (lane == 0) atomicAdd(&s_tailw, 1u);
+        while (*reinterpret_cast<volatile unsigned*>(&s_tailw) < (unsigned)NW) {       // the others still deal fresh games: play on
+            if (__ballot_sync(0xffffffffu, busy)) { if (busy) play(); } else __nanosleep(200);
+        }
+        const int warp = threadIdx.x >> 5;
+        int nw = NW;                                               // warps still taking part (warps 0 .. nw-1)
+        for (unsigned round = 0;; round++) {
+            const unsigned live = __ballot_sync(0xffffffffu, busy);
+            unsigned* cnt = s_cnt[round & 1];
+            if (lane == 0) cnt[warp] = (unsigned)__popc(live);
+            asm volatile("bar.sync 1, %0;" ::"r"(32 * nw) : "memory");
+            unsigned before = 0, total = 0;
+            for (int w = 0; w < nw; w++) { const unsigned c = cnt[w]; before += w < warp ? c : 0u; total += c; }
+            if (total == 0) break;
+            const int nw_new = (int)((total + 31u) >> 5);
+            if (nw_new < nw) {                                     // packing frees at least one warp
+                if (busy) {
+                    TailRec& r = s_rec[before + (unsigned)__popc(live & lt)];
+                    r.tl = (u64)g.tl; r.br = (u64)g.br; r.rid = rid; r.sc = (slot << 3) | child; r.pidx = pidx; r.j = j;
+                }
+                asm volatile("bar.sync 1, %0;" ::"r"(32 * nw) : "memory");
+                const unsigned t = (unsigned)(warp * 32 + lane);
+                busy = t < total;
+                if (busy) {
+                    const TailRec& r = s_rec[t];
+                    g.tl = (typename C::W)r.tl; g.br = (typename C::W)r.br; rid = r.rid; child = r.sc & 7u; slot = r.sc >> 3; pidx = r.pidx; j = r.j;
+                }
+                if (warp >= nw_new) break;
+                nw = nw_new;
             }
-            if (over) {
-                if (tl_won<C>(g, geo)) atomicAdd(&wins[slot], 1u);
-                busy = false;
+            for (int it = 0; it < MC_TAIL_R; it++) {
+                if (!__ballot_sync(0xffffffffu, busy)) break;
+                if (busy) play();
             }
         }
     }
+#endif
     if (plies) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) my_plies += __shfl_xor_sync(0xffffffffu, my_plies, o);
