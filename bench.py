@@ -520,6 +520,22 @@ def run_ours(args, rank, world, local_rank):
                                 "launches_per_rollout": 6 if persistent else 2 * T + 7 if fused else None,
                                 "episodes_last_rollout": a2c.logger.get("rollout/episodes")}
                 penv.close()
+            if world > 1:
+                # A rollout is 128 dependent steps of ~8 us each: giving a rank FEWER envs does not shorten it (configs[4]'s 4096 envs over
+                # 8 GPUs = 512 per rank: the same 1.0 ms).  What scales is envs: the same collection with 4096 envs on EVERY rank.
+                penv = EWNDeviceVecEnv(4096, 7, 3, seed=SEED + 7, shaped=True, env_id0=rank * 4096, engine=e7)
+                a2c = A2C("MultiInputPolicy", penv, n_steps=T, seed=rank)
+                a2c.collect_rollouts(); torch.cuda.synchronize()
+                dist.barrier()
+                p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                p0.record()
+                for _ in range(20):
+                    a2c.collect_rollouts()
+                p1.record(); torch.cuda.synchronize()
+                tt = torch.tensor([p0.elapsed_time(p1) / 20], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                rollout["with_policy_4096_per_gpu"] = {"ms_per_rollout": float(tt[0]), "envs_per_gpu": 4096,
+                                                       "env_steps_per_s": 4096 * world * T / (float(tt[0]) / 1e3), "scaling": "weak"}
+                penv.close()
         except Exception as err:                     # noqa: BLE001
             rollout["with_policy"] = {"unavailable": str(err)[:200]}
 
