@@ -485,6 +485,40 @@ def run_ours(args, rank, world, local_rank):
             res[name] = {"ms_per_rollout": ms, "env_steps_per_s": n7 * world * T / (ms / 1e3), "allreduce_us": 1e3 * ar,
                          "allreduce_alone_us": 1e3 * a3.elapsed_time(a4) if dist else None,
                          "episodes": int(tot[3].item()) // reps}
+        # the same collection as ONE launch (ewn_rollout without a network: the pooled actions are read from a [T][n][2] tensor, the games stay
+        # in registers for all 128 steps; identical to the step launches: tests/test_policy_kernel.py::test_rollout_without_a_policy_equals_step_calls)
+        try:
+            st7p = e7.reset(n7, seed=SEED + 3, env_id0=rank * n7)
+            tolp, prevp = torch.full((n7,), 10, dtype=torch.int32, device=dev), e7.evaluate(st7p, "hybrid")
+            stp, ctrp = torch.zeros(4, dtype=torch.int64, device=dev), torch.zeros(1, dtype=torch.int64, device=dev)
+            bufp = {"board": torch.zeros((T + 1, n7, 7, 7), dtype=torch.int16, device=dev), "dice": torch.zeros((T + 1, n7), dtype=torch.int64, device=dev),
+                    "actions": torch.stack([pool[t % 8] for t in range(T)]).contiguous(), "rewards": torch.zeros((T, n7), device=dev),
+                    "dones": torch.zeros((T, n7), dtype=torch.uint8, device=dev)}
+            with torch.cuda.stream(side):
+                roll = e7.rollout_plan(None, st7p, T, bufp, seed=SEED + 3, env_id0=rank * n7, step_dev=ctrp, shaped=True, illegal_move_reward=-1.0,
+                                       tolerance=tolp, prev_score=prevp, stats=stp)
+
+                def rollout_one_launch():
+                    roll(1); e7.counter_add(ctrp, T)
+                rollout_one_launch(); torch.cuda.synchronize()
+                stp.zero_(); torch.cuda.synchronize()
+                if dist: dist.barrier()
+                q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                q0.record()
+                for _ in range(20):
+                    rollout_one_launch()
+                q1.record()
+            torch.cuda.synchronize()
+            qms = q0.elapsed_time(q1) / 20
+            if dist:
+                tt = torch.tensor([qms], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); qms = float(tt[0])
+                tot = stp.clone(); dist.all_reduce(tot)
+            else:
+                tot = stp
+            res["one_launch"] = {"ms_per_rollout": qms, "env_steps_per_s": n7 * world * T / (qms / 1e3), "episodes": int(tot[3].item()) // 20,
+                                 "kernel": "k_rollout without a network (ewn_rollout, net = NULL): 128 steps of every game in one launch"}
+        except Exception as err:                     # noqa: BLE001
+            res["one_launch"] = {"unavailable": str(err)[:200]}
         rollout = {"workload": "7x7 MiniMaxHeuristicEnv (tolerance 10, illegal_move_reward -1) rollout collection, 4096 envs x 128 steps, "
                                "policy stub = pooled uniform actions, stats all-reduce after the rollouts", "envs_per_gpu": n7, **res}
 

@@ -1795,7 +1795,12 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
     const int64_t n = ra.n, e0 = (int64_t)blockIdx.x * PE, i = e0 + lane;
     const bool mine = warp == 0 && lane < PE && i < n;
     const u64 step0 = sp.step + (ra.step_dev ? *ra.step_dev : 0ull);
-    pol_stage(m, net, F);
+    // without a network (ewn_rollout_args.net == NULL) the actions are READ from the buffer -- a pooled / pre-sampled action tensor, the
+    // "policy stub" of a throughput run -- and the env steps of a warp's 32 games follow one another with no launch in between: warp 0
+    // of every block works alone, no barrier is needed
+    const bool has_net = net.w1[0] != nullptr;
+    if (!has_net && warp != 0) return;
+    if (has_net) pol_stage(m, net, F);
     Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
     int tol = 0; double prev = 0.0;
     unsigned won = 0, lost = 0, fin_n = 0;
@@ -1810,6 +1815,22 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
             write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, e0, min(n, e0 + PE), geo, tile, lane);
             if (mine) ra.dice[(size_t)t * n + i] = g.dice;
             s_dice[lane] = mine ? g.dice : 0;
+        }
+        if (!has_net) {
+            if (t == ra.T) break;
+            if (mine) {
+                const size_t k = (size_t)t * n + i;
+                const longlong2 v = reinterpret_cast<const longlong2*>(ra.actions)[k];
+                const int a0 = (int)v.x, a1 = (v.y < 0 || v.y > 2) ? 3 : (int)v.y;          // as k_step reads an int64 action pair
+                Game<C> term = g;
+                StepOut out; out.term = 0; out.code = CODE_ONGOING;
+                StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
+                step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, 0, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
+                ra.rewards[k] = (float)out.reward;
+                ra.dones[k] = (uint8_t)out.term;
+                if (out.term) { fin_n++; won += out.code == CODE_AGENT_WON; lost += out.code == CODE_AGENT_LOST; }
+            }
+            continue;
         }
         __syncthreads();
         for (int idx = tid; idx < PE * NN; idx += PT) {          // x[k][e] = board[e][k] (rows of envs beyond n are zero)
@@ -1850,8 +1871,8 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
         pack(g, ra.state, i, sp.geo);
         if (SHAPED) { ra.tolerance[i] = tol; ra.prev_score[i] = prev; }
         // RolloutBuffer.compute_returns_and_advantage over this env's column (k_gae's arithmetic; the thread reads its own stores)
-        float gae = 0.f, next_v = m.outv[5 * PE + lane];
-        for (int t = ra.T - 1; t >= 0; t--) {
+        float gae = 0.f, next_v = has_net ? m.outv[5 * PE + lane] : 0.f;
+        for (int t = has_net ? ra.T - 1 : -1; t >= 0; t--) {
             const size_t k = (size_t)t * n + i;
             const float nt = __fsub_rn(1.0f, ra.dones[k] ? 1.0f : 0.0f), v = ra.values[k];
             const float delta = __fsub_rn(__fadd_rn(ra.rewards[k], __fmul_rn(__fmul_rn(ra.gamma, next_v), nt)), v);
@@ -2380,19 +2401,22 @@ int ewn_policy_forward(const ewn_policy_net* net, const int16_t* board, const in
 }
 
 int ewn_rollout(const ewn_rollout_args* a, void* stream) {
-    if (!a || !a->state || !a->net || a->n < 0 || a->T < 1 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
-    if (!a->board || !a->dice || !a->actions || !a->rewards || !a->dones || !a->values || !a->logp || !a->last_values || !a->advantages || !a->returns)
-        return EWN_EARG;
+    if (!a || !a->state || a->n < 0 || a->T < 1 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
+    if (!a->board || !a->dice || !a->actions || !a->rewards || !a->dones) return EWN_EARG;
+    if (a->net && (!a->values || !a->logp || !a->last_values || !a->advantages || !a->returns)) return EWN_EARG;
     if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
     const ewn_policy_net* net = a->net;
-    if (net->hidden != PH || codec_of(a->board_size, a->cube_layer) == 2) return EWN_ENOSUP;
-    if (!net->pi_w1 || !net->pi_b1 || !net->pi_w2 || !net->pi_b2 || !net->vf_w1 || !net->vf_b1 || !net->vf_w2 || !net->vf_b2 || !net->action_w ||
-        !net->action_b || !net->value_w || !net->value_b) return EWN_EARG;
+    if ((net && net->hidden != PH) || codec_of(a->board_size, a->cube_layer) == 2) return EWN_ENOSUP;
+    if (net && (!net->pi_w1 || !net->pi_b1 || !net->pi_w2 || !net->pi_b2 || !net->vf_w1 || !net->vf_b1 || !net->vf_w2 || !net->vf_b2 || !net->action_w ||
+                !net->action_b || !net->value_w || !net->value_b)) return EWN_EARG;
     if (a->n == 0) return EWN_OK;
     PolicyNet pn;
-    pn.w1[0] = net->pi_w1; pn.b1[0] = net->pi_b1; pn.w2[0] = net->pi_w2; pn.b2[0] = net->pi_b2;
-    pn.w1[1] = net->vf_w1; pn.b1[1] = net->vf_b1; pn.w2[1] = net->vf_w2; pn.b2[1] = net->vf_b2;
-    pn.wa = net->action_w; pn.ba = net->action_b; pn.wv = net->value_w; pn.bv = net->value_b;
+    memset(&pn, 0, sizeof(pn));
+    if (net) {
+        pn.w1[0] = net->pi_w1; pn.b1[0] = net->pi_b1; pn.w2[0] = net->pi_w2; pn.b2[0] = net->pi_b2;
+        pn.w1[1] = net->vf_w1; pn.b1[1] = net->vf_b1; pn.w2[1] = net->vf_w2; pn.b2[1] = net->vf_b2;
+        pn.wa = net->action_w; pn.ba = net->action_b; pn.wv = net->value_w; pn.bv = net->value_b;
+    }
     StepParams sp;
     memset(&sp, 0, sizeof(sp));
     sp.geo = make_geo(a->board_size, a->cube_layer);

@@ -315,15 +315,16 @@ class Engine:
                      illegal_move_reward=-1.0, tolerance=None, prev_score=None, stats=None, gamma=0.99, gae_lambda=1.0):
         """A bound ewn_rollout call (the whole T-step collection in one launch) -> callable(step) that enqueues it.  `bufs`: dict with
         board [T+1,n,N,N] i16, dice [T+1,n] i64, actions [T,n,2] i64, rewards / values / log_probs / adv / ret [T,n] f32, dones [T,n] u8,
-        last_values [n] f32."""
+        last_values [n] f32.  net=None: no policy, the actions are read from bufs["actions"] (values / log_probs / ... not needed)."""
         from ._lib import RolloutArgs
         xp = self.xp
         a = RolloutArgs()
         a.state, a.n, a.board_size, a.cube_layer, a.T, a.shaped = xp.ptr(state), self._n(state), self.N, self.L, int(T), int(bool(shaped))
-        a.net = C.pointer(net)
+        if net is not None:
+            a.net = C.pointer(net)
         for field, key in (("board", "board"), ("dice", "dice"), ("actions", "actions"), ("rewards", "rewards"), ("dones", "dones"),
                            ("values", "values"), ("logp", "log_probs"), ("last_values", "last_values"), ("advantages", "adv"), ("returns", "ret")):
-            setattr(a, field, xp.ptr(bufs[key]))
+            setattr(a, field, xp.ptr(bufs.get(key)))
         a.tolerance, a.prev_score, a.stats = xp.ptr(tolerance), xp.ptr(prev_score), xp.ptr(stats)
         a.reward, a.illegal_move_reward = float(reward), float(illegal_move_reward)
         a.seed, a.step, a.env_id0, a.step_dev, a.policy_seed = int(seed), 0, int(env_id0), xp.ptr(step_dev), int(policy_seed)

@@ -225,7 +225,9 @@ EWN_API int ewn_policy_forward(const ewn_policy_net *net, const int16_t *board, 
  * opponent, auto-reset, MultiDiscrete actions from the policy; six-cube layouts and 64-wide towers (EWN_ENOSUP otherwise).
  * board int16 [T + 1][n][N][N] and dice int64 [T + 1][n]: slot t = the observation step t's action was computed from, slot T = the one
  * after the last step; actions int64 [T][n][2]; rewards / values / logp / advantages / returns f32 [T][n]; dones u8 [T][n]; last_values
- * f32 [n]; tolerance / prev_score as in ewn_step_args (required when shaped); stats as there (or NULL). */
+ * f32 [n]; tolerance / prev_score as in ewn_step_args (required when shaped); stats as there (or NULL).
+ * net == NULL: no policy -- the actions are READ from `actions` (a pooled / pre-sampled tensor) and only board / dice / rewards / dones are
+ * written (the other outputs may be NULL): T env steps of every game in one launch, identical to T calls of ewn_step. */
 typedef struct ewn_rollout_args {
     uint64_t *state;              /* in/out, n games, agent to move */
     int64_t n;

@@ -192,6 +192,41 @@ def test_one_launch_rollout_equals_two_launches_per_step(N, L, shaped, n):
     assert int(envs[0].stats[3]) > 0
 
 
+@pytest.mark.parametrize("N,L,shaped,n", [(7, 3, True, 4096), (5, 3, False, 2000 + 5), (9, 3, True, 100)])
+def test_rollout_without_a_policy_equals_step_calls(N, L, shaped, n):
+    """ewn_rollout with net == NULL (actions read from a pre-filled tensor): T env steps of every game in one launch against T ewn_step
+    calls -- observations of every slot, rewards, dones, the games, tolerance / previous score and the statistics"""
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    e = Engine(N, L)
+    T, seed, env_id0 = 16, 31, 700
+    g = th.Generator(device="cuda"); g.manual_seed(3)
+    acts = th.stack([th.randint(0, 2, (T, n), generator=g, device="cuda"), th.randint(-1, 4, (T, n), generator=g, device="cuda")], 2).contiguous()
+    sa, sb = e.reset(n, seed=seed, env_id0=env_id0), e.reset(n, seed=seed, env_id0=env_id0)
+    kw = {}
+    if shaped:
+        ta, tb = (th.full((n,), 2, dtype=th.int32, device="cuda") for _ in (0, 1))
+        pa, pb = e.evaluate(sa, "hybrid"), e.evaluate(sb, "hybrid")
+        kw = dict(shaped=True, illegal_move_reward=-1.0)
+    stats_a, stats_b = th.zeros(4, dtype=th.int64, device="cuda"), th.zeros(4, dtype=th.int64, device="cuda")
+    bufs = {"board": th.zeros((T + 1, n, N, N), dtype=th.int16, device="cuda"), "dice": th.zeros((T + 1, n), dtype=th.int64, device="cuda"),
+            "actions": acts, "rewards": th.zeros((T, n), device="cuda"), "dones": th.zeros((T, n), dtype=th.uint8, device="cuda")}
+    ctr = th.full((1,), 5, dtype=th.int64, device="cuda")
+    roll = e.rollout_plan(None, sb, T, bufs, seed=seed, env_id0=env_id0, step_dev=ctr, stats=stats_b,
+                          tolerance=tb if shaped else None, prev_score=pb if shaped else None, **kw)
+    b0, d0 = e.decode(sa)
+    roll(1)
+    assert th.equal(bufs["board"][0], b0) and th.equal(bufs["dice"][0], d0)
+    for t in range(T):
+        r = e.step(sa, acts[t], seed=seed, step=6 + t, env_id0=env_id0, stats=stats_a, tolerance=ta if shaped else None,
+                   prev_score=pa if shaped else None, want=("reward_f32", "terminated", "truncated", "obs_board", "obs_dice"), **kw)
+        assert th.equal(bufs["board"][t + 1], r["obs_board"]) and th.equal(bufs["dice"][t + 1], r["obs_dice"]), t
+        assert th.equal(bufs["rewards"][t], r["reward_f32"]) and th.equal(bufs["dones"][t], r["terminated"]), t
+    assert th.equal(sa, sb) and th.equal(stats_a, stats_b) and (n < 1000 or int(stats_a[3]) > 0)
+    if shaped:
+        assert th.equal(ta, tb) and th.equal(pa, pb)
+
+
 def test_generic_collector_still_runs_on_cuda():
     """fused=False keeps the torch loop (what a policy with another net_arch, or an env with a policy opponent, gets): same buffer
     contract; the learning run of tests/test_train.py covers the fused collector on this backend"""
