@@ -420,6 +420,44 @@ def run_ours(args, rank, world, local_rank):
         except Exception:
             pass
 
+    # ---- secondary: the headline batch with T = 32 env steps per LAUNCH (ewn_rollout without a network: pooled uniform actions read from a
+    # [T][n][2] tensor, the games stay in registers, every step's observation / reward / done written as the step launches write them)
+    rollout_5x5 = None
+    if not args.skip_rollout:
+        try:
+            T5 = 32
+            g5 = torch.Generator(device=dev); g5.manual_seed(77 + rank)
+            acts5 = torch.stack([torch.randint(0, 2, (T5, n), generator=g5, device=dev), torch.randint(0, 3, (T5, n), generator=g5, device=dev)], 2).contiguous()
+            st5 = e.reset(n, seed=SEED + 9, env_id0=rank * n)
+            buf5 = {"board": torch.empty((T5 + 1, n, 5, 5), dtype=torch.int16, device=dev), "dice": torch.empty((T5 + 1, n), dtype=torch.int64, device=dev),
+                    "actions": acts5, "rewards": torch.empty((T5, n), device=dev), "dones": torch.empty((T5, n), dtype=torch.uint8, device=dev)}
+            ctr5, stats5 = torch.zeros(1, dtype=torch.int64, device=dev), torch.zeros(4, dtype=torch.int64, device=dev)
+            roll5 = e.rollout_plan(None, st5, T5, buf5, seed=SEED + 9, env_id0=rank * n, step_dev=ctr5, stats=stats5)
+
+            def one5():
+                roll5(1); e.counter_add(ctr5, T5)
+            for _ in range(2): one5()
+            torch.cuda.synchronize()
+            if dist: dist.barrier()
+            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            r0.record()
+            for _ in range(4): one5()
+            r1.record(); torch.cuda.synchronize()
+            ms5 = r0.elapsed_time(r1) / 4
+            if dist:
+                tt = torch.tensor([ms5], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms5 = float(tt[0])
+            byt5 = 79 + 58 / T5
+            pk5, _src5 = peaks()
+            rollout_5x5 = {"workload": f"5x5, {n} games per GPU x {T5} env steps per launch, pooled uniform actions (ewn_rollout, net = NULL: k_rollout_env)",
+                           "ms_per_launch": ms5, "us_per_step_of_the_batch": 1e3 * ms5 / T5, "value": n * world * T5 / (ms5 / 1e3), "unit": "env steps/s",
+                           "roofline": {"bound": "hbm", "bytes_per_env_step": byt5, "achieved": n * T5 * byt5 / (ms5 / 1e3) / 1e9, "peak": pk5, "unit": "GB/s",
+                                        "frac": n * T5 * byt5 / (ms5 / 1e3) / 1e9 / pk5,
+                                        "note": "action 16 R + reward 4 + done 1 + board 50 + dice 8 W per env step, one more observation per launch; the "
+                                                "packed state is read and written once per launch, not per step"}}
+            del buf5, acts5, st5
+        except Exception as err:                     # noqa: BLE001
+            rollout_5x5 = {"unavailable": str(err)[:200]}
+
     # ---- secondary: configs[4], 7x7 MiniMaxHeuristicEnv rollout collection, 4096 envs x 128 steps over all ranks, counters all-reduced
     rollout = None
     if not args.skip_rollout:
@@ -720,7 +758,7 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": workload_config(args, n), "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu, "agent_uniform_legal": ar_run, "playouts": playout, "expectiminimax": emm, "rollout_7x7": rollout,
-            "device_env": device_env,
+            "rollout_5x5": rollout_5x5, "device_env": device_env,
             "episodes": {"agent_wins": st[0], "agent_losses": st[1], "illegal_endings": st[2], "finished": st[3],
                          "agent": "uniform over MultiDiscrete([2,3]) (host-supplied int64 actions; most games end on an illegal opening move -- "
                                   "the in-kernel legal agent run is `agent_uniform_legal`)"},

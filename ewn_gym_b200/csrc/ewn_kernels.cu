@@ -1795,11 +1795,7 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
     const int64_t n = ra.n, e0 = (int64_t)blockIdx.x * PE, i = e0 + lane;
     const bool mine = warp == 0 && lane < PE && i < n;
     const u64 step0 = sp.step + (ra.step_dev ? *ra.step_dev : 0ull);
-    // without a network (ewn_rollout_args.net == NULL) the actions are READ from the buffer -- a pooled / pre-sampled action tensor, the
-    // "policy stub" of a throughput run -- and the env steps of a warp's 32 games follow one another with no launch in between: warp 0
-    // of every block works alone, no barrier is needed
-    const bool has_net = net.w1[0] != nullptr;
-    if (!has_net && warp != 0) return;
+    constexpr bool has_net = true;                              // (without a network ewn_rollout runs k_rollout_env)
     if (has_net) pol_stage(m, net, F);
     Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
     int tol = 0; double prev = 0.0;
@@ -1815,22 +1811,6 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
             write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, e0, min(n, e0 + PE), geo, tile, lane);
             if (mine) ra.dice[(size_t)t * n + i] = g.dice;
             s_dice[lane] = mine ? g.dice : 0;
-        }
-        if (!has_net) {
-            if (t == ra.T) break;
-            if (mine) {
-                const size_t k = (size_t)t * n + i;
-                const longlong2 v = reinterpret_cast<const longlong2*>(ra.actions)[k];
-                const int a0 = (int)v.x, a1 = (v.y < 0 || v.y > 2) ? 3 : (int)v.y;          // as k_step reads an int64 action pair
-                Game<C> term = g;
-                StepOut out; out.term = 0; out.code = CODE_ONGOING;
-                StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
-                step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, 0, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
-                ra.rewards[k] = (float)out.reward;
-                ra.dones[k] = (uint8_t)out.term;
-                if (out.term) { fin_n++; won += out.code == CODE_AGENT_WON; lost += out.code == CODE_AGENT_LOST; }
-            }
-            continue;
         }
         __syncthreads();
         for (int idx = tid; idx < PE * NN; idx += PT) {          // x[k][e] = board[e][k] (rows of envs beyond n are zero)
@@ -1889,6 +1869,68 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
             if (v) atomicAdd(ra.stats + lane, (unsigned long long)v);
         }
     }
+}
+// ewn_rollout without a network at any batch size: a thread owns a game for all T steps (actions read from the buffer), a warp stages and
+// writes its 32 observation rows per step exactly as k_step does -- T env steps per launch, the games in registers, no per-step launch
+// ramp / tail and no state round trip through HBM (79 B per env step on 5x5 instead of 96).
+constexpr int RTPB = 128;
+template <class C, int NT, bool SHAPED> __global__ void __launch_bounds__(RTPB)
+k_rollout_env(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepParams sp) {
+    extern __shared__ uint4 smem_raw[];
+    Geo geo = sp.geo;
+    if (NT) { geo.N = NT; geo.corner = C::cell(NT - 1, NT - 1); }
+    const int NN = geo.N * geo.N;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int16_t* const tile = reinterpret_cast<int16_t*>(smem_raw) + (size_t)warp * 32 * NN;
+    const int64_t n = ra.n, i = (int64_t)blockIdx.x * RTPB + tid, warp_env0 = i - lane;
+    if (warp_env0 >= n) return;                                   // warp-uniform
+    const bool mine = i < n;
+    const u64 step0 = sp.step + (ra.step_dev ? *ra.step_dev : 0ull);
+    Game<C> g; g.tl = C::all(); g.br = C::all(); g.dice = 1; g.player = 0;
+    int tol = 0; double prev = 0.0;
+    unsigned won = 0, lost = 0, fin_n = 0;
+    if (mine) {
+        unpack(g, ra.state, i, sp.geo);
+        if (SHAPED) { tol = ra.tolerance[i]; prev = ra.prev_score[i]; }
+    }
+    longlong2 act = make_longlong2(0, 0);
+    if (mine) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + i);
+    for (int t = 0; t <= ra.T; t++) {
+        stage_rows<C, NT>(g, mine, geo, tile, lane);
+        write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, warp_env0, n, geo, tile, lane);
+        if (mine) __stcs(reinterpret_cast<long long*>(ra.dice) + (size_t)t * n + i, (long long)g.dice);
+        if (t == ra.T) break;
+        if (mine) {
+            const size_t k = (size_t)t * n + i;
+            const int a0 = (int)act.x, a1 = (act.y < 0 || act.y > 2) ? 3 : (int)act.y;              // as k_step reads an int64 action pair
+            if (t + 1 < ra.T) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + k + n);   // the next step's action: in flight during this step
+            Game<C> term = g;
+            StepOut out; out.term = 0; out.code = CODE_ONGOING;
+            StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
+            step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, 0, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
+            __stcs(ra.rewards + k, (float)out.reward);
+            __stcs(ra.dones + k, (uint8_t)out.term);
+            if (out.term) { fin_n++; won += out.code == CODE_AGENT_WON; lost += out.code == CODE_AGENT_LOST; }
+        }
+    }
+    if (mine) {
+        pack(g, ra.state, i, sp.geo);
+        if (SHAPED) { ra.tolerance[i] = tol; ra.prev_score[i] = prev; }
+    }
+    if (ra.stats) {
+        const unsigned f = __reduce_add_sync(0xffffffffu, fin_n), w = __reduce_add_sync(0xffffffffu, won), l = __reduce_add_sync(0xffffffffu, lost);
+        if (lane < 4 && f) {
+            const unsigned v = lane == 0 ? w : lane == 1 ? l : lane == 2 ? f - w - l : f;
+            if (v) atomicAdd(ra.stats + lane, (unsigned long long)v);
+        }
+    }
+}
+template <class C, int NT, bool SHAPED> int launch_rollout_env(const RolloutArgs& ra, const StepParams& sp, cudaStream_t st) {
+    const int NN = sp.geo.N * sp.geo.N;
+    const size_t sm = (size_t)RTPB * NN * sizeof(int16_t);
+    k_rollout_env<C, NT, SHAPED><<<(unsigned)((ra.n + RTPB - 1) / RTPB), RTPB, sm, st>>>(ra, sp);
+    LAUNCHED("k_rollout_env");
+    return EWN_OK;
 }
 inline size_t rollout_smem(int NN, int D) { return policy_smem(NN + D) + (((size_t)32 * NN * 2 + 15) & ~(size_t)15) + 32 * sizeof(int); }
 template <class C, int NT, bool SHAPED> int launch_rollout(const RolloutArgs& ra, const StepParams& sp, const PolicyNet& pn, int D, cudaStream_t st) {
@@ -2432,7 +2474,8 @@ int ewn_rollout(const ewn_rollout_args* a, void* stream) {
     ra.policy_seed = a->policy_seed; ra.gamma = (float)a->gamma; ra.gamma_lambda = (float)(a->gamma * a->gae_lambda);
     const int N = a->board_size, D = a->cube_layer * (a->cube_layer + 1) / 2 + 1;
     cudaStream_t st = (cudaStream_t)stream;
-#define ROLL(C, NT) (a->shaped ? launch_rollout<C, NT, true>(ra, sp, pn, D, st) : launch_rollout<C, NT, false>(ra, sp, pn, D, st))
+#define ROLL(C, NT) (!net ? (a->shaped ? launch_rollout_env<C, NT, true>(ra, sp, st) : launch_rollout_env<C, NT, false>(ra, sp, st)) \
+                          : (a->shaped ? launch_rollout<C, NT, true>(ra, sp, pn, D, st) : launch_rollout<C, NT, false>(ra, sp, pn, D, st)))
     if (N == 5) return ROLL(P5, 5);
     if (use_p5(N)) return ROLL(P5, 0);
     if (N == 7) return ROLL(P8, 7);
