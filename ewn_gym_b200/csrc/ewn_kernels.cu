@@ -1873,7 +1873,10 @@ k_rollout(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepPa
 // ewn_rollout without a network at any batch size: a thread owns a game for all T steps (actions read from the buffer), a warp stages and
 // writes its 32 observation rows per step exactly as k_step does -- T env steps per launch, the games in registers, no per-step launch
 // ramp / tail and no state round trip through HBM (79 B per env step on 5x5 instead of 96).
-constexpr int RTPB = 128;
+#ifndef EWN_RTPB
+#define EWN_RTPB 128
+#endif
+constexpr int RTPB = EWN_RTPB;
 template <class C, int NT, bool SHAPED> __global__ void __launch_bounds__(RTPB)
 k_rollout_env(const __grid_constant__ RolloutArgs ra, const __grid_constant__ StepParams sp) {
     extern __shared__ uint4 smem_raw[];
