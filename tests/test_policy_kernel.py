@@ -227,6 +227,31 @@ def test_rollout_without_a_policy_equals_step_calls(N, L, shaped, n):
         assert th.equal(ta, tb) and th.equal(pa, pb)
 
 
+@pytest.mark.parametrize("persistent", [False, True])
+def test_fused_collector_follows_env_seed_and_reset(persistent):
+    """train.py:135-136: env.seed(s); env.reset() after the collector has bound its launches -- the next rollout must play the re-seeded
+    games (the bound launches carry the Philox key: the collector rebinds)"""
+    import torch as th
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    from ewn_gym_b200.train import A2C
+    n, T = 500, 6
+    env = EWNDeviceVecEnv(n, 5, 3, seed=1)                             # (plain env: the shaped one carries tolerance / previous score over a reset)
+    model = A2C("MultiInputPolicy", env, n_steps=T, seed=9, persistent=persistent)
+    model.collect_rollouts()
+    env.seed(42); first = env.reset()
+    b0 = first["board"].clone()
+    model.collect_rollouts()
+    assert th.equal(model.buf["board"][0], b0)
+    twin = EWNDeviceVecEnv(n, 5, 3, seed=42)
+    twin._t = env.step_index - T - 1                                  # the same step counter as the re-seeded env had at its reset
+    obs = twin.reset()
+    assert th.equal(obs["board"], b0)
+    for t in range(T):
+        obs, r, d, _ = twin.step(model.buf["actions"][t].clone())
+        assert th.equal(model.buf["rewards"][t], r) and th.equal(model.buf["dones"][t].bool(), d), t
+    assert th.equal(model._last_obs["board"], obs["board"])
+
+
 def test_generic_collector_still_runs_on_cuda():
     """fused=False keeps the torch loop (what a policy with another net_arch, or an env with a policy opponent, gets): same buffer
     contract; the learning run of tests/test_train.py covers the fused collector on this backend"""
