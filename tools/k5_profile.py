@@ -11,7 +11,7 @@ from ewn_gym_b200.train import A2C
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 T = 128
 env = EWNDeviceVecEnv(n, 7, 3, seed=1, shaped=True)
-m = A2C("MultiInputPolicy", env, n_steps=T, seed=0)
+m = A2C("MultiInputPolicy", env, n_steps=T, seed=0, persistent=False)      # the graph collector: its plans are timed one by one below
 for _ in range(3): m.collect_rollouts()
 torch.cuda.synchronize()
 e, f = env.e, m.fb
