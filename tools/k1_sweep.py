@@ -30,7 +30,8 @@ if os.environ.get("EWN_K1_CHILD"):
 
     def plans(step_dev=None):
         return [[e.step_plan(S["state"], None if ar else S["act"], seed=SEED + s_i, step=0, autoreset=True, stats=stats, want=tuple(shapes), out=S["out"],
-                             agent_random=ar, step_dev=step_dev, term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b])) for b in (0, 1)]
+                             agent_random=ar, step_dev=step_dev, term_compact=(S["cnt"][b:b + 1], S["tidx"], S["cnt"][1 - b:2 - b]),
+                             block_kernel=os.environ.get("EWN_K1_BLOCK") == "1") for b in (0, 1)]
                 for s_i, S in enumerate(sets)]
 
     P = plans()
