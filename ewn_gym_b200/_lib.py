@@ -51,7 +51,7 @@ class RolloutArgs(C.Structure):
                 ("board", p_void), ("dice", p_void), ("actions", p_void), ("rewards", p_void), ("dones", p_void), ("values", p_void), ("logp", p_void),
                 ("last_values", p_void), ("advantages", p_void), ("returns", p_void), ("tolerance", p_void), ("prev_score", p_void), ("stats", p_void),
                 ("reward", C.c_double), ("illegal_move_reward", C.c_double), ("seed", u64), ("step", u64), ("env_id0", u64), ("step_dev", p_void),
-                ("policy_seed", u64), ("gamma", C.c_double), ("gae_lambda", C.c_double)]
+                ("policy_seed", u64), ("gamma", C.c_double), ("gae_lambda", C.c_double), ("agent_random", i32), ("reserved", i32)]
 
 
 class VecConfig(C.Structure):

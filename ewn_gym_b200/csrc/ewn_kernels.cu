@@ -1896,8 +1896,9 @@ k_rollout_env(const __grid_constant__ RolloutArgs ra, const __grid_constant__ St
         unpack(g, ra.state, i, sp.geo);
         if (SHAPED) { tol = ra.tolerance[i]; prev = ra.prev_score[i]; }
     }
+    const int ar = sp.agent_random;                               // the agent plays uniformly over its legal list inside the kernel: `actions` is written
     longlong2 act = make_longlong2(0, 0);
-    if (mine) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + i);
+    if (mine && !ar) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + i);
     for (int t = 0; t <= ra.T; t++) {
         stage_rows<C, NT>(g, mine, geo, tile, lane);
         write_rows_dense<C, NT>(ra.board + (size_t)t * n * NN, warp_env0, n, geo, tile, lane);
@@ -1906,11 +1907,12 @@ k_rollout_env(const __grid_constant__ RolloutArgs ra, const __grid_constant__ St
         if (mine) {
             const size_t k = (size_t)t * n + i;
             const int a0 = (int)act.x, a1 = (act.y < 0 || act.y > 2) ? 3 : (int)act.y;              // as k_step reads an int64 action pair
-            if (t + 1 < ra.T) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + k + n);   // the next step's action: in flight during this step
+            if (!ar && t + 1 < ra.T) act = __ldcs(reinterpret_cast<const longlong2*>(ra.actions) + k + n);   // the next step's action: in flight during this step
             Game<C> term = g;
             StepOut out; out.term = 0; out.code = CODE_ONGOING;
             StepInject inj; inj.dice_opp = 1; inj.o_larger = 0; inj.o_dir = 0; inj.dice_next = 1;
-            step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, 0, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
+            step_one_cfg<C>(g, term, sp, geo, 0, SHAPED ? 1 : 0, ar, step0 + (u64)t, (long)i, a0, a1, inj, &tol, &prev, out);
+            if (ar && ra.actions) __stcs(reinterpret_cast<longlong2*>(ra.actions) + k, make_longlong2(out.a_larger, out.a_dir));
             __stcs(ra.rewards + k, (float)out.reward);
             __stcs(ra.dones + k, (uint8_t)out.term);
             if (out.term) { fin_n++; won += out.code == CODE_AGENT_WON; lost += out.code == CODE_AGENT_LOST; }
@@ -2447,7 +2449,8 @@ int ewn_policy_forward(const ewn_policy_net* net, const int16_t* board, const in
 
 int ewn_rollout(const ewn_rollout_args* a, void* stream) {
     if (!a || !a->state || a->n < 0 || a->T < 1 || !config_ok(a->board_size, a->cube_layer)) return EWN_EARG;
-    if (!a->board || !a->dice || !a->actions || !a->rewards || !a->dones) return EWN_EARG;
+    if (!a->board || !a->dice || !a->rewards || !a->dones) return EWN_EARG;
+    if (a->agent_random ? a->net != nullptr : !a->actions) return EWN_EARG;       // in-kernel random agent: no network, actions optional (written)
     if (a->net && (!a->values || !a->logp || !a->last_values || !a->advantages || !a->returns)) return EWN_EARG;
     if (a->shaped && !(a->tolerance && a->prev_score)) return EWN_EARG;
     const ewn_policy_net* net = a->net;
@@ -2467,7 +2470,7 @@ int ewn_rollout(const ewn_rollout_args* a, void* stream) {
     sp.geo = make_geo(a->board_size, a->cube_layer);
     sp.reward = a->reward; sp.illegal_move_reward = a->illegal_move_reward;
     sp.seed = a->seed; sp.step = a->step; sp.env_id0 = a->env_id0; sp.rk = make_round_keys(a->seed);
-    sp.agent_random = 0; sp.autoreset = 1; sp.shaped = a->shaped != 0; sp.replay = 0;
+    sp.agent_random = a->agent_random != 0; sp.autoreset = 1; sp.shaped = a->shaped != 0; sp.replay = 0;
     RolloutArgs ra;
     ra.state = a->state; ra.n = a->n; ra.T = a->T;
     ra.board = a->board; ra.dice = a->dice; ra.actions = a->actions; ra.rewards = a->rewards; ra.dones = a->dones; ra.values = a->values;

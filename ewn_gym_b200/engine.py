@@ -312,7 +312,7 @@ class Engine:
         return {k: v for k, v in out.items() if v is not None}
 
     def rollout_plan(self, net, state, T, bufs, *, seed, env_id0=0, step_dev=None, policy_seed=0, reward=1.0, shaped=False,
-                     illegal_move_reward=-1.0, tolerance=None, prev_score=None, stats=None, gamma=0.99, gae_lambda=1.0):
+                     illegal_move_reward=-1.0, tolerance=None, prev_score=None, stats=None, gamma=0.99, gae_lambda=1.0, agent_random=False):
         """A bound ewn_rollout call (the whole T-step collection in one launch) -> callable(step) that enqueues it.  `bufs`: dict with
         board [T+1,n,N,N] i16, dice [T+1,n] i64, actions [T,n,2] i64, rewards / values / log_probs / adv / ret [T,n] f32, dones [T,n] u8,
         last_values [n] f32.  net=None: no policy, the actions are read from bufs["actions"] (values / log_probs / ... not needed)."""
@@ -329,6 +329,7 @@ class Engine:
         a.reward, a.illegal_move_reward = float(reward), float(illegal_move_reward)
         a.seed, a.step, a.env_id0, a.step_dev, a.policy_seed = int(seed), 0, int(env_id0), xp.ptr(step_dev), int(policy_seed)
         a.gamma, a.gae_lambda = float(gamma), float(gae_lambda)
+        a.agent_random = int(bool(agent_random))           # net=None only: the in-kernel uniform-over-legal agent; bufs["actions"] receives its moves
         keep = (net, state, bufs, tolerance, prev_score, stats, step_dev)
         fn, ref = self.lib.ewn_rollout, C.byref(a)
 

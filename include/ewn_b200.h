@@ -241,6 +241,8 @@ typedef struct ewn_rollout_args {
     const uint64_t *step_dev;     /* optional device counter added to `step` (CUDA-graph replays) */
     uint64_t policy_seed;
     double gamma, gae_lambda;
+    int32_t agent_random;         /* net == NULL only: TOP_LEFT plays uniformly over its legal list inside the kernel (random_policy.py:11-15,  */
+    int32_t reserved;             /* as ewn_step_args.agent_random); `actions` (may be NULL) then RECEIVES the moves played                 */
 } ewn_rollout_args;
 EWN_API int ewn_rollout(const ewn_rollout_args *args, void *stream);
 /* RolloutBuffer.compute_returns_and_advantage of the same loop (GAE(gamma, lambda); A2C's default lambda = 1 gives the n-step return):

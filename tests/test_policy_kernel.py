@@ -252,6 +252,29 @@ def test_fused_collector_follows_env_seed_and_reset(persistent):
     assert th.equal(model._last_obs["board"], obs["board"])
 
 
+@pytest.mark.parametrize("N,n", [(5, 3000 + 1), (7, 1500)])
+def test_rollout_with_the_in_kernel_random_agent_equals_step_calls(N, n):
+    """ewn_rollout, net == NULL, agent_random: random-vs-random games (eval_random.py's loop) T steps per launch against T ewn_step calls with
+    the in-kernel agent -- observations, rewards, dones, the moves played, the games and the statistics"""
+    import torch as th
+    from ewn_gym_b200.engine import Engine
+    e = Engine(N, 3)
+    T, seed = 24, 5
+    sa, sb = e.reset(n, seed=seed), e.reset(n, seed=seed)
+    stats_a, stats_b = th.zeros(4, dtype=th.int64, device="cuda"), th.zeros(4, dtype=th.int64, device="cuda")
+    bufs = {"board": th.zeros((T + 1, n, N, N), dtype=th.int16, device="cuda"), "dice": th.zeros((T + 1, n), dtype=th.int64, device="cuda"),
+            "actions": th.full((T, n, 2), -7, dtype=th.int64, device="cuda"), "rewards": th.zeros((T, n), device="cuda"),
+            "dones": th.zeros((T, n), dtype=th.uint8, device="cuda")}
+    e.rollout_plan(None, sb, T, bufs, seed=seed, stats=stats_b, agent_random=True)(1)
+    for t in range(T):
+        r = e.step(sa, None, seed=seed, step=1 + t, agent_random=True, stats=stats_a,
+                   want=("reward_f32", "terminated", "truncated", "obs_board", "obs_dice", "action_out"), block_kernel=True)
+        assert th.equal(bufs["board"][t + 1], r["obs_board"]) and th.equal(bufs["dice"][t + 1], r["obs_dice"]), t
+        assert th.equal(bufs["rewards"][t], r["reward_f32"]) and th.equal(bufs["dones"][t], r["terminated"]), t
+        assert th.equal(bufs["actions"][t, :, 0] * 3 + bufs["actions"][t, :, 1], r["action_out"].long()), t
+    assert th.equal(sa, sb) and th.equal(stats_a, stats_b) and int(stats_a[0]) > 0 and int(stats_a[2]) == 0     # wins happen, illegal endings do not
+
+
 def test_generic_collector_still_runs_on_cuda():
     """fused=False keeps the torch loop (what a policy with another net_arch, or an env with a policy opponent, gets): same buffer
     contract; the learning run of tests/test_train.py covers the fused collector on this backend"""
