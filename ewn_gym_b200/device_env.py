@@ -266,6 +266,33 @@ class EWNDeviceVecEnv:
             self._copy_into(self._outs[self._last]["obs_board"], obs[0])
             self._copy_into(self._outs[self._last]["obs_dice"], obs[1])
 
+    def rollout(self, actions=None, n_steps=None, agent_random=False):
+        """T env steps of every game in ONE launch (ewn_rollout without a network): `actions` int64[T, n, 2] on the device (e.g. pooled
+        or pre-sampled), or `agent_random=True` for the in-kernel uniform-over-the-legal-list agent (n_steps = T; the moves it played
+        come back in the result).  Same games, dice and statistics as T `step` calls.  -> dict with `board` int16[T + 1, n, N, N] and
+        `dice_roll` int64[T + 1, n] (slot t = the observation step t acted on, slot T = the one after the last step), `actions`,
+        `rewards` f32[T, n], `dones` bool[T, n].  In-kernel random opponent and six-cube layouts only; no terminal observations."""
+        if self.opponent is not None or self.torch is None:
+            raise RuntimeError("rollout: the device env with its in-kernel random opponent only")
+        if self.state is None:
+            self.reset()
+        th, n, N = self.torch, self.num_envs, self.board_size
+        dev = self.state.device
+        if agent_random:
+            T = int(n_steps)
+            acts = th.empty((T, n, 2), dtype=th.int64, device=dev)
+        else:
+            acts = th.as_tensor(actions, device=dev).to(th.int64).reshape(-1, n, 2).contiguous()
+            T = int(acts.shape[0])
+        bufs = {"board": th.empty((T + 1, n, N, N), dtype=th.int16, device=dev), "dice": th.empty((T + 1, n), dtype=th.int64, device=dev),
+                "actions": acts, "rewards": th.empty((T, n), device=dev), "dones": th.empty((T, n), dtype=th.uint8, device=dev)}
+        launch = self.e.rollout_plan(None, self.state, T, bufs, seed=self.seed_value, env_id0=self.env_id0, reward=self.reward, shaped=self.shaped,
+                                     illegal_move_reward=self.illegal_move_reward, tolerance=getattr(self, "_tol", None),
+                                     prev_score=getattr(self, "_prev", None), stats=self.stats, agent_random=agent_random)
+        launch(self._t)
+        self.advance(T, obs=(bufs["board"][T], bufs["dice"][T]))
+        return {"board": bufs["board"], "dice_roll": bufs["dice"], "actions": acts, "rewards": bufs["rewards"], "dones": bufs["dones"].view(th.bool)}
+
     @property
     def step_index(self) -> int:
         """the step counter the NEXT step will use (the Philox counter of its dice)"""

@@ -275,6 +275,30 @@ def test_rollout_with_the_in_kernel_random_agent_equals_step_calls(N, n):
     assert th.equal(sa, sb) and th.equal(stats_a, stats_b) and int(stats_a[0]) > 0 and int(stats_a[2]) == 0     # wins happen, illegal endings do not
 
 
+def test_env_rollout_equals_env_steps():
+    """EWNDeviceVecEnv.rollout (one launch) against the same env class stepped T times: pre-sampled actions and the in-kernel agent"""
+    import torch as th
+    from ewn_gym_b200.device_env import EWNDeviceVecEnv
+    n, T = 777, 10
+    a, b = EWNDeviceVecEnv(n, 7, 3, seed=6, shaped=True), EWNDeviceVecEnv(n, 7, 3, seed=6, shaped=True)
+    oa, ob = a.reset(), b.reset()
+    g = th.Generator(device="cuda"); g.manual_seed(1)
+    acts = th.stack([th.randint(0, 2, (T, n), generator=g, device="cuda"), th.randint(0, 3, (T, n), generator=g, device="cuda")], 2)
+    r = a.rollout(acts)
+    assert th.equal(r["board"][0], ob["board"]) and th.equal(r["dice_roll"][0], ob["dice_roll"])
+    for t in range(T):
+        o, rew, done, _ = b.step(acts[t].clone())
+        assert th.equal(r["board"][t + 1], o["board"]) and th.equal(r["rewards"][t], rew) and th.equal(r["dones"][t], done), t
+    assert th.equal(a.state, b.state) and th.equal(a.stats, b.stats) and a.step_index == b.step_index
+    o2, rew2, done2, _ = a.step(acts[0].clone())                      # the env carries on from the rollout's last observation
+    o3, rew3, done3, _ = b.step(acts[0].clone())
+    assert th.equal(o2["board"], o3["board"]) and th.equal(rew2, rew3)
+    illegal_before = int(a.stats[2])
+    rr = a.rollout(n_steps=5, agent_random=True)
+    assert rr["actions"].shape == (5, n, 2) and int(rr["actions"].min()) >= 0 and int(rr["actions"][..., 1].max()) <= 2
+    assert int(a.stats[2]) == illegal_before                         # a legal-list agent never ends a game on an illegal move
+
+
 def test_generic_collector_still_runs_on_cuda():
     """fused=False keeps the torch loop (what a policy with another net_arch, or an env with a policy opponent, gets): same buffer
     contract; the learning run of tests/test_train.py covers the fused collector on this backend"""
